@@ -1,0 +1,266 @@
+"""TEST INFRASTRUCTURE — ctypes loaders for the two CPU checkers.
+
+* :class:`Port`  — ``oracle/liboracle_port.so`` (oracle/port.c, the plain-C restatement).
+* :class:`RefEngine` — ``oracle/_ref/libref_engine.so``: the UNMODIFIED reference collision path
+  compiled from ``/root/reference`` (oracle/Makefile).  Present wherever the build container's
+  snapshot travels; ``RefEngine.available()`` says whether it is.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
+reference`` legs may import this module.  ``engine_b200`` never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "liboracle_port.so")
+REF_SO = os.path.join(HERE, "_ref", "libref_engine.so")
+
+# Layouts of the reference's PODs (include/system_collisions.h:13-24,40-48; component_collider.h:7-10)
+RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3)])
+RAYCAST_DTYPE = np.dtype(
+    [("location", "<f4", 3), ("normal", "<f4", 3), ("hit_entity", "<u4"), ("distance", "<f4"), ("hit", "u1"), ("pad", "u1", 3)]
+)
+AABB_DTYPE = np.dtype([("min", "<f4", 3), ("max", "<f4", 3)])
+NODE_DTYPE = np.dtype(
+    [("box1", AABB_DTYPE), ("box2", AABB_DTYPE), ("index1", "<u4"), ("index2", "<u4"), ("type1", "u1"), ("type2", "u1"), ("pad", "u1", 2)]
+)
+assert RAY_DTYPE.itemsize == 24 and RAYCAST_DTYPE.itemsize == 36 and AABB_DTYPE.itemsize == 24 and NODE_DTYPE.itemsize == 60
+
+TYPE_BV, TYPE_ENTITY, TYPE_EMPTY = 0, 1, 2
+
+
+def build(force: bool = False) -> None:
+    """(Re)build the checkers with oracle/Makefile. Building the checker is not using it."""
+    if force or not os.path.exists(PORT_SO) or (os.path.isdir("/root/reference") and not os.path.exists(REF_SO)):
+        subprocess.check_call(["make", "-C", HERE, "all"], stdout=subprocess.DEVNULL)
+
+
+def _p(a: np.ndarray | None):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+def as_rays(rays) -> np.ndarray:
+    """Accept (n,6) float32 or RAY_DTYPE; return contiguous RAY_DTYPE view."""
+    rays = np.ascontiguousarray(rays)
+    if rays.dtype != RAY_DTYPE:
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6).view(RAY_DTYPE).reshape(-1)
+    return rays
+
+
+def as_aabbs(b) -> np.ndarray:
+    b = np.ascontiguousarray(b)
+    if b.dtype != AABB_DTYPE:
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 6).view(AABB_DTYPE).reshape(-1)
+    return b
+
+
+class Port:
+    """oracle/port.c"""
+
+    def __init__(self):
+        build()
+        self.lib = C.CDLL(PORT_SO)
+        L = self.lib
+        L.orc_build_binned_sah.restype = C.c_size_t
+        L.orc_tree_leaves_dfs.restype = C.c_size_t
+        L.orc_ray_box.restype = C.c_int
+
+    # -- transform ---------------------------------------------------------------------------
+    def transform_update(self, parent, pos, rot_xyzw, scl, world_prev=None) -> np.ndarray:
+        """Arrays indexed by entity ID (row 0 unused). Returns (n+1,16) column-major matrices."""
+        parent = np.ascontiguousarray(parent, dtype=np.uint32)
+        n = parent.shape[0] - 1
+        pos, rot, scl = _f32(pos, (n + 1, 3)), _f32(rot_xyzw, (n + 1, 4)), _f32(scl, (n + 1, 3))
+        world = np.zeros((n + 1, 16), np.float32) if world_prev is None else np.array(world_prev, np.float32, copy=True)
+        self.lib.orc_transform_update(C.c_size_t(n), _p(parent), _p(pos), _p(rot), _p(scl), _p(world))
+        return world
+
+    def refit(self, entity, local_aabb, world16) -> np.ndarray:
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        local = as_aabbs(local_aabb)
+        world16 = _f32(world16)
+        out = np.zeros(entity.shape[0], AABB_DTYPE)
+        self.lib.orc_refit(C.c_size_t(entity.shape[0]), _p(entity), _p(local), _p(world16), _p(out))
+        return out
+
+    def transform_box(self, aabb6, mat16) -> np.ndarray:
+        a, m = _f32(aabb6, (6,)), _f32(mat16, (16,))
+        out = np.zeros(6, np.float32)
+        self.lib.orc_transform_box(_p(a), _p(m), _p(out))
+        return out
+
+    # -- queries -----------------------------------------------------------------------------
+    def ray_box(self, ray6, aabb6, T=1000.0):
+        r, a = _f32(ray6, (6,)), _f32(aabb6, (6,))
+        t, side = C.c_float(), C.c_int()
+        hit = self.lib.orc_ray_box(_p(r), _p(a), C.c_float(T), C.byref(t), C.byref(side))
+        return bool(hit), np.float32(t.value), side.value
+
+    def normalize(self, v3) -> np.ndarray:
+        v = _f32(v3, (3,))
+        out = np.zeros(3, np.float32)
+        self.lib.orc_normalize(_p(v), _p(out))
+        return out
+
+    def raycast_tree(self, nodes, rays, nthreads=1) -> np.ndarray:
+        nodes = np.ascontiguousarray(nodes, dtype=NODE_DTYPE)
+        rays = as_rays(rays)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        self.lib.orc_raycast_batch(_p(nodes), C.c_size_t(nodes.shape[0]), _p(rays), C.c_size_t(rays.shape[0]), _p(out), C.c_int(nthreads))
+        return out
+
+    def raycast_brute(self, entity, boxes, rays, nthreads=1, want_ties=False):
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        boxes = as_aabbs(boxes)
+        rays = as_rays(rays)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        ties = np.zeros(rays.shape[0], np.uint32)
+        self.lib.orc_brute_batch(
+            _p(entity), _p(boxes), C.c_size_t(entity.shape[0]), _p(rays), C.c_size_t(rays.shape[0]), _p(out), _p(ties), C.c_int(nthreads)
+        )
+        return (out, ties) if want_ties else out
+
+    # -- trees -------------------------------------------------------------------------------
+    def build_binned_sah(self, entity, boxes) -> np.ndarray:
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        boxes = as_aabbs(boxes)
+        n = entity.shape[0]
+        nodes = np.zeros(max(2 * n - 1, 0), NODE_DTYPE)
+        k = self.lib.orc_build_binned_sah(_p(entity), _p(boxes), C.c_size_t(n), _p(nodes))
+        return nodes[:k].copy()
+
+    def tree_leaves_dfs(self, nodes):
+        nodes = np.ascontiguousarray(nodes, dtype=NODE_DTYPE)
+        cap = 2 * nodes.shape[0]
+        ent = np.zeros(cap, np.uint32)
+        box = np.zeros(cap, AABB_DTYPE)
+        k = self.lib.orc_tree_leaves_dfs(_p(nodes), C.c_size_t(nodes.shape[0]), _p(ent), _p(box))
+        return ent[:k].copy(), box[:k].copy()
+
+
+class RefEngine:
+    """The real reference (engine::Scene + TransformSystem + CollisionSystem) behind oracle/ref_harness.cpp."""
+
+    @staticmethod
+    def available() -> bool:
+        if not os.path.exists(REF_SO) and os.path.isdir("/root/reference"):
+            build()
+        return os.path.exists(REF_SO)
+
+    def __init__(self):
+        if not self.available():
+            raise RuntimeError("oracle/_ref/libref_engine.so not built (needs /root/reference)")
+        self.lib = C.CDLL(REF_SO)
+        L = self.lib
+        L.refh_create.restype = C.c_void_p
+        L.refh_sizeof.restype = C.c_size_t
+        L.refh_create_entities.restype = C.c_uint32
+        L.refh_scene_update.restype = C.c_double
+        L.refh_transform_update.restype = C.c_double
+        L.refh_refit.restype = C.c_size_t
+        L.refh_bvh_size.restype = C.c_size_t
+        L.refh_raycast.restype = C.c_double
+        L.refh_ray_box.restype = C.c_int
+        self.h = C.c_void_p(L.refh_create())
+        self.n_entities = 0
+
+    def close(self):
+        if self.h:
+            self.lib.refh_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def hw_threads(self) -> int:
+        return int(self.lib.refh_hw_threads())
+
+    def create_entities(self, parent, pos, rot_xyzw, scl) -> np.ndarray:
+        """Rows are NEW entities in creation order (no dummy row 0). Returns their IDs."""
+        parent = np.ascontiguousarray(parent, dtype=np.uint32)
+        n = parent.shape[0]
+        pos, rot, scl = _f32(pos, (n, 3)), _f32(rot_xyzw, (n, 4)), _f32(scl, (n, 3))
+        first = self.lib.refh_create_entities(self.h, C.c_size_t(n), _p(parent), _p(pos), _p(rot), _p(scl))
+        self.n_entities += n
+        return np.arange(first, first + n, dtype=np.uint32)
+
+    def add_colliders(self, entity, local_aabb) -> None:
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        local = as_aabbs(local_aabb)
+        self.lib.refh_add_colliders(self.h, C.c_size_t(entity.shape[0]), _p(entity), _p(local))
+
+    def set_trs(self, entity, pos, rot_xyzw, scl) -> None:
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        n = entity.shape[0]
+        pos, rot, scl = _f32(pos, (n, 3)), _f32(rot_xyzw, (n, 4)), _f32(scl, (n, 3))
+        self.lib.refh_set_trs(self.h, C.c_size_t(n), _p(entity), _p(pos), _p(rot), _p(scl))
+
+    def scene_update(self) -> float:
+        return float(self.lib.refh_scene_update(self.h))
+
+    def transform_update(self) -> float:
+        return float(self.lib.refh_transform_update(self.h))
+
+    def refit(self, n_colliders: int):
+        ent = np.zeros(n_colliders, np.uint32)
+        box = np.zeros(n_colliders, AABB_DTYPE)
+        secs = C.c_double()
+        k = self.lib.refh_refit(self.h, _p(ent), _p(box), C.byref(secs))
+        assert k == n_colliders, (k, n_colliders)
+        return ent, box, secs.value
+
+    def world_matrices(self, entity) -> np.ndarray:
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        out = np.zeros((entity.shape[0], 16), np.float32)
+        self.lib.refh_get_world_matrices(self.h, C.c_size_t(entity.shape[0]), _p(entity), _p(out))
+        return out
+
+    def bvh(self) -> np.ndarray:
+        n = self.lib.refh_bvh_size(self.h)
+        out = np.zeros(n, NODE_DTYPE)
+        self.lib.refh_bvh_get(self.h, _p(out))
+        out["pad"] = 0  # the two tail padding bytes are indeterminate in the reference
+        return out
+
+    def set_bvh(self, nodes) -> None:
+        nodes = np.ascontiguousarray(nodes, dtype=NODE_DTYPE)
+        self.lib.refh_bvh_set(self.h, _p(nodes), C.c_size_t(nodes.shape[0]))
+
+    def raycast(self, rays, nthreads=1, want_secs=False):
+        rays = as_rays(rays)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        secs = self.lib.refh_raycast(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(out), C.c_int(nthreads))
+        return (out, float(secs)) if want_secs else out
+
+    def ray_box(self, ray6, aabb6, T=1000.0):
+        r, a = _f32(ray6, (6,)), _f32(aabb6, (6,))
+        t, side = C.c_float(), C.c_int()
+        hit = self.lib.refh_ray_box(_p(r), _p(a), C.c_float(T), C.byref(t), C.byref(side))
+        return bool(hit), np.float32(t.value), side.value
+
+    def transform_box(self, aabb6, mat16) -> np.ndarray:
+        a, m = _f32(aabb6, (6,)), _f32(mat16, (16,))
+        out = np.zeros(6, np.float32)
+        self.lib.refh_transform_box(_p(a), _p(m), _p(out))
+        return out
+
+    def normalize(self, v3) -> np.ndarray:
+        v = _f32(v3, (3,))
+        out = np.zeros(3, np.float32)
+        self.lib.refh_normalize(_p(v), _p(out))
+        return out
