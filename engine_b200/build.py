@@ -1,0 +1,48 @@
+"""Build libb2col.so (the C-ABI CUDA library) in-tree for sm_100a with nvcc.
+
+    python -m engine_b200.build [--force]
+
+The .so is git-ignored but travels to the GPU box with the repo snapshot.  nvcc cross-compiles
+without a GPU.  -fmad=false: the parity-critical arithmetic already uses the _rn intrinsics, the
+flag additionally keeps ptxas from contracting anything else on this path into FMAs.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libb2col.so")
+SOURCES = ["b2col.cu"]
+HEADERS = ["b2col_math.cuh", "b2col_bvh.cuh", "b2col_sort.cuh", "../../include/b2col.h"]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
+    "-Xcompiler", "-fPIC", "-shared",
+    "--expt-relaxed-constexpr",
+]
+
+
+def stale() -> bool:
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not stale():
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES], "-lcudart"]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,876 @@
+// b2col.cu — kernels and C ABI of the B200 collision-query backend (see include/b2col.h).
+// sm_100a only; no CPU path.  Build: engine_b200/build.py (nvcc -gencode arch=compute_100a,code=sm_100a).
+#include "../../include/b2col.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "b2col_bvh.cuh"
+#include "b2col_math.cuh"
+#include "b2col_sort.cuh"
+
+using namespace b2;
+
+static_assert(sizeof(b2col_ray) == 24 && sizeof(b2col_raycast) == 36 && sizeof(b2col_aabb) == 24 && sizeof(b2col_bitreenode) == 60,
+              "POD layouts must equal the reference's (include/system_collisions.h:13-24,40-48)");
+
+// =================================================================================================
+// device-side policy for the shared kernel bodies in b2col_bvh.cuh
+// =================================================================================================
+struct DevOps {
+    static __device__ __forceinline__ void store_slot(Slot* p, const Slot& s)
+    {
+        float4* q = reinterpret_cast<float4*>(p);
+        q[0] = make_float4(s.lo[0], s.lo[1], s.lo[2], s.hi[0]);
+        q[1] = make_float4(s.hi[1], s.hi[2], __uint_as_float(s.ref), __uint_as_float(s.aux));
+    }
+    static __device__ __forceinline__ Slot unpack(const float4& a, const float4& b)
+    {
+        Slot s;
+        s.lo[0] = a.x; s.lo[1] = a.y; s.lo[2] = a.z;
+        s.hi[0] = a.w; s.hi[1] = b.x; s.hi[2] = b.y;
+        s.ref = __float_as_uint(b.z);
+        s.aux = __float_as_uint(b.w);
+        return s;
+    }
+    static __device__ __forceinline__ Slot load_slot(const Slot* p)
+    {
+        const float4* q = reinterpret_cast<const float4*>(p);
+        return unpack(__ldg(q), __ldg(q + 1));
+    }
+    static __device__ __forceinline__ Slot load_slot_coherent(const Slot* p)
+    {  // written by another SM during this kernel: read at L2, never from this SM's L1
+        const float4* q = reinterpret_cast<const float4*>(p);
+        return unpack(__ldcg(q), __ldcg(q + 1));
+    }
+    static __device__ __forceinline__ void fence() { __threadfence(); }
+    static __device__ __forceinline__ uint32_t exch(uint32_t* p, uint32_t v) { return atomicExch(p, v); }
+};
+
+// Contents of the first 256 bytes of the BVH blob (device memory).
+struct BlobHeader {
+    uint32_t magic, n_leaves, n_nodes, root;
+    uint32_t bounds_min_inv[3];  // ~ordered(min centroid): zero-initialised, raised with atomicMax
+    uint32_t bounds_max[3];      //  ordered(max centroid)
+    uint32_t reserved[54];
+};
+static_assert(sizeof(BlobHeader) == 256, "blob header");
+constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
+
+// =================================================================================================
+// kernels
+// =================================================================================================
+
+// TransformSystem::onUpdate (reference src/system_transform.cpp:12-38), one hierarchy level per launch:
+// entities of depth k only depend on depth k-1, which the previous launch finished.
+// world: 16 floats per entity, column-major, indexed by entity ID.
+__global__ void __launch_bounds__(256)
+k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent,
+                  const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t e = level_entities[i];
+    const float4 q4 = __ldg(rot4 + e);
+    const float p[3] = {__ldg(pos3 + 3 * (size_t)e), __ldg(pos3 + 3 * (size_t)e + 1), __ldg(pos3 + 3 * (size_t)e + 2)};
+    const float s[3] = {__ldg(scl3 + 3 * (size_t)e), __ldg(scl3 + 3 * (size_t)e + 1), __ldg(scl3 + 3 * (size_t)e + 2)};
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+    float L[16], W[16];
+    local_matrix(p, q, s, L);
+    const uint32_t par = __ldg(parent + e);
+    if (par != 0u) {
+        float P[16];
+        const float4* pw = world + 4 * (size_t)par;  // written by the previous launch
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float4 v = __ldcg(pw + c);
+            P[4 * c] = v.x; P[4 * c + 1] = v.y; P[4 * c + 2] = v.z; P[4 * c + 3] = v.w;
+        }
+        mat_mul(P, L, W);
+    }
+    else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) W[k] = L[k];
+    }
+    float4* ow = world + 4 * (size_t)e;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
+}
+
+// Refit loop (reference src/system_collisions.cpp:123-132): world AABB = transformBox(local, world_matrix).
+// Also reduces the centroid bounds of the scene (for the Morton grid) into the blob header.
+__global__ void __launch_bounds__(256)
+k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
+        Aabb24* __restrict__ world_aabb, BlobHeader* hdr)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float cmin[3] = {B2_INF, B2_INF, B2_INF}, cmax[3] = {-B2_INF, -B2_INF, -B2_INF};
+    if (i < n) {
+        const uint32_t e = __ldg(col_entity + i);
+        float M[16];
+        const float4* pw = world + 4 * (size_t)e;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float4 v = pw[c];
+            M[4 * c] = v.x; M[4 * c + 1] = v.y; M[4 * c + 2] = v.z; M[4 * c + 3] = v.w;
+        }
+        const float2* lp = reinterpret_cast<const float2*>(col_local + i);
+        const float2 l0 = __ldg(lp), l1 = __ldg(lp + 1), l2 = __ldg(lp + 2);
+        const float lmin[3] = {l0.x, l0.y, l1.x}, lmax[3] = {l1.y, l2.x, l2.y};
+        const Box b = transform_box(lmin, lmax, M);
+        float2* op = reinterpret_cast<float2*>(world_aabb + i);
+        op[0] = make_float2(b.lo[0], b.lo[1]);
+        op[1] = make_float2(b.lo[2], b.hi[0]);
+        op[2] = make_float2(b.hi[1], b.hi[2]);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float c = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
+            if (isfinite(c)) {
+                cmin[k] = c;
+                cmax[k] = c;
+            }
+        }
+    }
+    // block reduction: warp shuffles, then one atomic per warp and axis
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cmin[k] = fminf(cmin[k], __shfl_xor_sync(0xffffffffu, cmin[k], o));
+            cmax[k] = fmaxf(cmax[k], __shfl_xor_sync(0xffffffffu, cmax[k], o));
+        }
+    }
+    __shared__ float smin[8][3], smax[8][3];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            smin[warp][k] = cmin[k];
+            smax[warp][k] = cmax[k];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int k = threadIdx.x;
+        float a = smin[0][k], b = smax[0][k];
+        for (int w = 1; w < 8; ++w) {
+            a = fminf(a, smin[w][k]);
+            b = fmaxf(b, smax[w][k]);
+        }
+        if (a <= b) {  // false when the block saw no finite centroid
+            atomicMax(&hdr->bounds_min_inv[k], ~float_to_ordered(a));
+            atomicMax(&hdr->bounds_max[k], float_to_ordered(b));
+        }
+    }
+}
+
+// Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
+// registers here anyway), and reset of the per-node arrival words used by k_build.
+__global__ void __launch_bounds__(256)
+k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int passes, uint64_t* __restrict__ keys,
+         uint32_t* __restrict__ vals, uint32_t* __restrict__ other_bound, uint32_t* ghist)
+{
+    __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
+    for (int p = 0; p < passes; ++p) shist[p][threadIdx.x] = 0u;
+    __syncthreads();
+    float smin[3], sinv[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float lo = ordered_to_float(~hdr->bounds_min_inv[k]);
+        const float hi = ordered_to_float(hdr->bounds_max[k]);
+        const float ext = hi - lo;
+        smin[k] = lo;
+        sinv[k] = (ext > 0.0f && isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
+    }
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float2* bp = reinterpret_cast<const float2*>(world_aabb + i);
+        const float2 b0 = bp[0], b1 = bp[1], b2 = bp[2];
+        const float lo[3] = {b0.x, b0.y, b1.x}, hi[3] = {b1.y, b2.x, b2.y};
+        const uint64_t key = morton_key(lo, hi, smin, sinv, bits);
+        keys[i] = key;
+        vals[i] = i;
+        other_bound[i] = UNVISITED;
+        for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int p = 0; p < passes; ++p) {
+        const uint32_t c = shist[p][threadIdx.x];
+        if (c) atomicAdd(&ghist[p * RS_RADIX + threadIdx.x], c);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        hdr->magic = BLOB_MAGIC;
+        hdr->n_leaves = n;
+        hdr->n_nodes = n > 1u ? n - 1u : 1u;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
+        const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, uint32_t* leaf_entity, BlobHeader* hdr)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    build_from_leaf<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, nodes, other_bound, leaf_entity, &hdr->root);
+}
+
+__device__ __forceinline__ RayPre load_ray(const b2col_ray* rays, size_t i)
+{
+    const float2* rp = reinterpret_cast<const float2*>(rays + i);  // 24-byte records are 8-byte aligned
+    const float2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+    const float o[3] = {a.x, a.y, b.x}, d[3] = {b.y, c.x, c.y};
+    return ray_prepare(o, d);
+}
+
+// GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
+__global__ void __launch_bounds__(128)
+k_trace_lbvh(const b2col_ray* __restrict__ rays, size_t n_rays, b2col_raycast* __restrict__ out, const BlobHeader* __restrict__ hdr,
+             const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity, float T)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rays) return;
+    const RayPre r = load_ray(rays, i);
+    uint32_t* o9 = reinterpret_cast<uint32_t*>(out + i);
+    if (hdr->n_leaves == 0u) {  // empty tree: value-initialised Raycast (:164-167)
+        write_raycast(o9, r, false, 0.0f, 0, 0u);
+        return;
+    }
+    const Hit h = trace_lbvh<DevOps>(r, nodes, hdr->root, T);
+    const bool hit = h.leaf >= 0;
+    write_raycast(o9, r, hit, h.t, h.side, hit ? __ldg(leaf_entity + h.leaf) : 0u);
+}
+
+// Same query, walking an uploaded reference-format tree with the reference's exact semantics.
+__global__ void __launch_bounds__(128)
+k_trace_reftopo(const b2col_ray* __restrict__ rays, size_t n_rays, b2col_raycast* __restrict__ out, const uint32_t* __restrict__ words,
+                uint32_t n_nodes, float T, uint32_t* overflow_flag)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rays) return;
+    const RayPre r = load_ray(rays, i);
+    const RefHit h = trace_reftopo(r, words, n_nodes, T);
+    if (h.overflow) atomicExch(overflow_flag, 1u);
+    write_raycast(reinterpret_cast<uint32_t*>(out + i), r, h.hit, h.t, h.side, h.entity);
+}
+
+__global__ void __launch_bounds__(256)
+k_export(uint32_t n, const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity,
+         const Aabb24* __restrict__ world_aabb, const uint32_t* __restrict__ sorted_prim, BiTreeNode60* out, uint8_t* used)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) export_wrapper(i, world_aabb, sorted_prim, leaf_entity, out);
+    if (i + 1u < n) export_internal(i, n, hdr->root, nodes, leaf_entity, out, used);
+}
+
+// =================================================================================================
+// host side
+// =================================================================================================
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+};
+
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct b2col_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    b2col_config cfg{};
+    float T = 1000.0f;
+    int bits = 16;
+    int passes = 6;
+    std::string err;
+    uint64_t launches = 0;
+
+    // entities
+    uint32_t n_entities = 0;
+    bool have_hierarchy = false, have_trs = false, world_external = false;
+    std::vector<uint32_t> level_offsets;  // host; level k = [off[k], off[k+1]) in d_level_entities
+    DevBuf d_parent, d_level_entities, d_pos, d_rot, d_scl, d_world;
+    // colliders
+    uint32_t n_colliders = 0, max_col_entity = 0;
+    bool have_colliders = false;
+    DevBuf d_col_entity, d_col_local, d_world_aabb;
+    // build scratch
+    DevBuf d_keys[2], d_vals[2], d_other_bound, d_zero;  // d_zero: histograms, tickets, look-back words
+    size_t zero_bytes = 0;
+    int sorted_side = 0;
+    // traversal structure: one allocation [BlobHeader | nodes | leaf_entity]
+    DevBuf d_blob;
+    size_t blob_bytes = 0;
+    uint32_t tree_leaves = 0;  // leaves of the tree currently in the blob
+    bool have_tree = false;
+    // reference-topology tree
+    DevBuf d_ref_nodes, d_flag;
+    uint32_t n_ref_nodes = 0;
+    // staging for host-buffer queries
+    DevBuf d_rays, d_hits;
+    cudaEvent_t events[16] = {};
+};
+
+namespace {
+
+b2col_status fail(b2col_ctx* ctx, b2col_status st, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    else g_create_error = buf;
+    return st;
+}
+
+#define CU(call)                                                                                             \
+    do {                                                                                                     \
+        cudaError_t e_ = (call);                                                                             \
+        if (e_ != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+#define LAUNCH(ctx_, kern, grid, block, ...)                                              \
+    do {                                                                                  \
+        kern<<<(grid), (block), 0, (ctx_)->stream>>>(__VA_ARGS__);                        \
+        ++(ctx_)->launches;                                                               \
+        cudaError_t e_ = cudaGetLastError();                                              \
+        if (e_ != cudaSuccess)                                                            \
+            return fail((ctx_), B2COL_ERR_CUDA, "launch of %s failed: %s", #kern, cudaGetErrorString(e_)); \
+    } while (0)
+
+b2col_status ensure(b2col_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return B2COL_OK;
+    if (b.p) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    const size_t want = bytes + bytes / 8 + 256;  // slack: scenes grow a little every frame
+    CU(cudaMalloc(&b.p, want));
+    b.cap = want;
+    return B2COL_OK;
+}
+
+void release(DevBuf& b)
+{
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+inline uint32_t cdiv(size_t a, size_t b) { return (uint32_t)((a + b - 1) / b); }
+
+size_t blob_size_for(uint32_t n_leaves)
+{
+    const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
+    size_t leaf_bytes = ((size_t)n_leaves * 4 + 63) & ~(size_t)63;
+    return sizeof(BlobHeader) + n_nodes * sizeof(Node) + leaf_bytes;
+}
+inline BlobHeader* blob_hdr(const b2col_ctx* c) { return c->d_blob.as<BlobHeader>(); }
+inline Node* blob_nodes(const b2col_ctx* c) { return reinterpret_cast<Node*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader)); }
+inline uint32_t* blob_leaf_entity(const b2col_ctx* c, uint32_t n_leaves)
+{
+    const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
+    return reinterpret_cast<uint32_t*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader) + n_nodes * sizeof(Node));
+}
+
+#define GUARD(st_expr)                      \
+    do {                                    \
+        b2col_status s_ = (st_expr);        \
+        if (s_ != B2COL_OK) return s_;      \
+    } while (0)
+
+b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode)
+{
+    if (n == 0) return B2COL_OK;
+    if (mode == B2COL_MODE_LBVH) {
+        if (!ctx->have_tree) {
+            // frame-0 behaviour of the reference: bvh_ is empty before the first onUpdate, every query misses (:167)
+            CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
+            return B2COL_OK;
+        }
+        LAUNCH(ctx, k_trace_lbvh, cdiv(n, 128), 128, d_rays, n, d_out, blob_hdr(ctx), blob_nodes(ctx), blob_leaf_entity(ctx, ctx->tree_leaves), ctx->T);
+    }
+    else if (mode == B2COL_MODE_REFTOPO) {
+        GUARD(ensure(ctx, ctx->d_flag, 4));
+        CU(cudaMemsetAsync(ctx->d_flag.p, 0, 4, ctx->stream));
+        LAUNCH(ctx, k_trace_reftopo, cdiv(n, 128), 128, d_rays, n, d_out, ctx->d_ref_nodes.as<uint32_t>(), ctx->n_ref_nodes, ctx->T,
+               ctx->d_flag.as<uint32_t>());
+    }
+    else {
+        return fail(ctx, B2COL_ERR_INVALID, "unknown mode %d", mode);
+    }
+    return B2COL_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+int b2col_abi_version(void) { return B2COL_ABI_VERSION; }
+
+b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
+{
+    b2col_ctx* ctx = nullptr;  // for the CU/fail macros: errors before the ctx exists go to g_create_error
+    if (!out) return fail(nullptr, B2COL_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, B2COL_ERR_NO_DEVICE, "no CUDA device (%s); libb2col has no CPU path", e != cudaSuccess ? cudaGetErrorString(e) : "count = 0");
+    const int dev = cfg ? cfg->device : 0;
+    if (dev < 0 || dev >= count) return fail(nullptr, B2COL_ERR_INVALID, "device %d out of range (%d devices)", dev, count);
+    CU(cudaSetDevice(dev));
+    b2col_ctx* c = new (std::nothrow) b2col_ctx();
+    if (!c) return fail(nullptr, B2COL_ERR_INVALID, "out of host memory");
+    c->device = dev;
+    if (cfg) c->cfg = *cfg;
+    c->T = (cfg && cfg->max_distance > 0.0f) ? cfg->max_distance : 1000.0f;
+    c->bits = (cfg && cfg->morton_bits_per_axis > 0) ? cfg->morton_bits_per_axis : 16;
+    if (c->bits < 4 || c->bits > 21) {
+        delete c;
+        return fail(nullptr, B2COL_ERR_INVALID, "morton_bits_per_axis must be in [4,21]");
+    }
+    c->passes = (3 * c->bits + RS_BITS - 1) / RS_BITS;
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete c;
+        return fail(nullptr, B2COL_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+    }
+    for (auto& ev : c->events) cudaEventCreate(&ev);
+    *out = c;
+    return B2COL_OK;
+}
+
+void b2col_destroy(b2col_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
+                      &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
+                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits})
+        release(*b);
+    for (auto& ev : ctx->events)
+        if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* b2col_last_error(const b2col_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+b2col_status b2col_sync(b2col_ctx* ctx)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
+void* b2col_stream(b2col_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint32_t* h_parent)
+{
+    if (!ctx || (!h_parent && n_entities)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    const size_t rows = (size_t)n_entities + 1;
+    // depth of every entity; parents precede children, so one ascending pass suffices (this is the
+    // order TransformSystem::onUpdate itself relies on, reference src/system_transform.cpp:16,28-31)
+    std::vector<uint32_t> depth(rows, 0);
+    uint32_t max_depth = 0;
+    for (uint32_t e = 1; e <= n_entities; ++e) {
+        const uint32_t p = h_parent[e];
+        if (p >= e) return fail(ctx, B2COL_ERR_UNSUPPORTED, "entity %u has parent %u: parents must have smaller IDs than their children", e, p);
+        depth[e] = p ? depth[p] + 1 : 0;
+        max_depth = std::max(max_depth, depth[e]);
+    }
+    const uint32_t n_levels = n_entities ? max_depth + 1 : 0;
+    ctx->level_offsets.assign(n_levels + 1, 0);
+    for (uint32_t e = 1; e <= n_entities; ++e) ++ctx->level_offsets[depth[e] + 1];
+    for (uint32_t k = 0; k < n_levels; ++k) ctx->level_offsets[k + 1] += ctx->level_offsets[k];
+    std::vector<uint32_t> order(n_entities);
+    {
+        std::vector<uint32_t> cursor(ctx->level_offsets.begin(), ctx->level_offsets.end() - (n_levels ? 1 : 0));
+        for (uint32_t e = 1; e <= n_entities; ++e) order[cursor[depth[e]]++] = e;
+    }
+    GUARD(ensure(ctx, ctx->d_parent, rows * 4));
+    GUARD(ensure(ctx, ctx->d_level_entities, (size_t)n_entities * 4 + 4));
+    CU(cudaMemcpyAsync(ctx->d_parent.p, h_parent, rows * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (n_entities) CU(cudaMemcpyAsync(ctx->d_level_entities.p, order.data(), (size_t)n_entities * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));  // `order` is a local
+    ctx->n_entities = n_entities;
+    ctx->have_hierarchy = true;
+    ctx->have_trs = false;
+    return B2COL_OK;
+}
+
+static b2col_status set_trs_common(b2col_ctx* ctx, uint32_t n_entities, const float* pos3, const float* rot, const float* scl3, cudaMemcpyKind kind)
+{
+    if (!ctx || !pos3 || !rot || !scl3) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_hierarchy || n_entities != ctx->n_entities)
+        return fail(ctx, B2COL_ERR_STATE, "b2col_set_hierarchy must be called first with the same n_entities");
+    CU(cudaSetDevice(ctx->device));
+    const size_t rows = (size_t)n_entities + 1;
+    GUARD(ensure(ctx, ctx->d_pos, rows * 12));
+    GUARD(ensure(ctx, ctx->d_rot, rows * 16));
+    GUARD(ensure(ctx, ctx->d_scl, rows * 12));
+    CU(cudaMemcpyAsync(ctx->d_pos.p, pos3, rows * 12, kind, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_rot.p, rot, rows * 16, kind, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_scl.p, scl3, rows * 12, kind, ctx->stream));
+    ctx->have_trs = true;
+    ctx->world_external = false;
+    return B2COL_OK;
+}
+
+b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3)
+{
+    GUARD(set_trs_common(ctx, n_entities, h_pos3, h_rot_xyzw, h_scl3, cudaMemcpyHostToDevice));
+    CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse its buffers as soon as we return
+    return B2COL_OK;
+}
+
+b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3)
+{
+    return set_trs_common(ctx, n_entities, d_pos3, d_rot_xyzw, d_scl3, cudaMemcpyDeviceToDevice);
+}
+
+b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const float* h_world16)
+{
+    if (!ctx || !h_world16) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    const size_t rows = (size_t)n_entities + 1;
+    GUARD(ensure(ctx, ctx->d_world, rows * 64));
+    CU(cudaMemcpyAsync(ctx->d_world.p, h_world16, rows * 64, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->n_entities = n_entities;
+    ctx->world_external = true;
+    return B2COL_OK;
+}
+
+b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_entity, const b2col_aabb* h_local)
+{
+    if (!ctx || (n && (!h_entity || !h_local))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n >= 0x7fffffffu) return fail(ctx, B2COL_ERR_INVALID, "too many colliders");
+    CU(cudaSetDevice(ctx->device));
+    uint32_t max_e = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (h_entity[i] == 0u) return fail(ctx, B2COL_ERR_INVALID, "collider %u refers to entity 0, which is not a valid entity", i);
+        max_e = std::max(max_e, h_entity[i]);
+    }
+    ctx->max_col_entity = max_e;
+    GUARD(ensure(ctx, ctx->d_col_entity, (size_t)n * 4 + 4));
+    GUARD(ensure(ctx, ctx->d_col_local, (size_t)n * 24 + 8));
+    if (n) {
+        CU(cudaMemcpyAsync(ctx->d_col_entity.p, h_entity, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_col_local.p, h_local, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->n_colliders = n;
+    ctx->have_colliders = true;
+    return B2COL_OK;
+}
+
+b2col_status b2col_update(b2col_ctx* ctx)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (!ctx->have_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_set_colliders has not been called");
+    if (!ctx->world_external && !(ctx->have_hierarchy && ctx->have_trs))
+        return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
+    const size_t rows = (size_t)E + 1;
+
+    // ---- a1: world matrices -------------------------------------------------------------------
+    if (!ctx->world_external) {
+        GUARD(ensure(ctx, ctx->d_world, rows * 64));
+        const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
+        for (size_t k = 0; k < n_levels; ++k) {
+            const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
+            if (!cnt) continue;
+            LAUNCH(ctx, k_propagate_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+                   ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>());
+        }
+    }
+
+    // ---- allocate the frame's buffers -----------------------------------------------------------
+    const size_t blob_bytes = blob_size_for(n);
+    GUARD(ensure(ctx, ctx->d_blob, blob_bytes));
+    ctx->blob_bytes = blob_bytes;
+    ctx->tree_leaves = n;
+    CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
+    if (n == 0) {
+        ctx->have_tree = true;  // empty tree: header says n_leaves = 0, every query misses
+        return B2COL_OK;
+    }
+    if (ctx->max_col_entity > E)
+        return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, E);
+    GUARD(ensure(ctx, ctx->d_world_aabb, (size_t)n * 24 + 8));
+    GUARD(ensure(ctx, ctx->d_keys[0], (size_t)n * 8));
+    GUARD(ensure(ctx, ctx->d_keys[1], (size_t)n * 8));
+    GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
+    GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
+    GUARD(ensure(ctx, ctx->d_other_bound, (size_t)n * 4));
+    const uint32_t tiles = cdiv(n, RS_TILE);
+    const size_t hist_bytes = (size_t)RS_MAX_PASSES * RS_RADIX * 4;
+    const size_t ticket_bytes = 64;
+    const size_t lb_bytes = (size_t)ctx->passes * tiles * RS_RADIX * 4;
+    ctx->zero_bytes = hist_bytes + ticket_bytes + lb_bytes;
+    GUARD(ensure(ctx, ctx->d_zero, ctx->zero_bytes));
+    CU(cudaMemsetAsync(ctx->d_zero.p, 0, ctx->zero_bytes, ctx->stream));
+    uint32_t* ghist = ctx->d_zero.as<uint32_t>();
+    uint32_t* tickets = ghist + RS_MAX_PASSES * RS_RADIX;
+    uint32_t* lookback = tickets + 16;
+
+    // ---- a2: refit + centroid bounds ------------------------------------------------------------
+    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
+           ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx));
+
+    // ---- a4: LBVH build -------------------------------------------------------------------------
+    {
+        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->passes, ctx->d_keys[0].as<uint64_t>(),
+               ctx->d_vals[0].as<uint32_t>(), ctx->d_other_bound.as<uint32_t>(), ghist);
+    }
+    int side = 0;
+    for (int p = 0; p < ctx->passes; ++p) {
+        LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, p * RS_BITS, ghist + p * RS_RADIX,
+               lookback + (size_t)p * tiles * RS_RADIX, tickets + p);
+        side ^= 1;
+    }
+    ctx->sorted_side = side;
+    LAUNCH(ctx, k_build, cdiv(n, 256), 256, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
+           ctx->d_col_entity.as<uint32_t>(), blob_nodes(ctx), ctx->d_other_bound.as<uint32_t>(), blob_leaf_entity(ctx, n), blob_hdr(ctx));
+    ctx->have_tree = true;
+    return B2COL_OK;
+}
+
+b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode)
+{
+    if (!ctx || (n && (!d_rays || !d_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    return enqueue_trace(ctx, d_rays, n, d_out, mode);
+}
+
+b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode)
+{
+    if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n == 0) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
+    GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
+    CU(cudaMemcpyAsync(ctx->d_rays.p, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));
+    GUARD(enqueue_trace(ctx, ctx->d_rays.as<b2col_ray>(), n, ctx->d_hits.as<b2col_raycast>(), mode));
+    CU(cudaMemcpyAsync(h_out, ctx->d_hits.p, n * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (mode == B2COL_MODE_REFTOPO) {
+        uint32_t flag = 0;
+        CU(cudaMemcpy(&flag, ctx->d_flag.p, 4, cudaMemcpyDeviceToHost));
+        if (flag) return fail(ctx, B2COL_ERR_OVERFLOW, "reference-topology traversal stack overflow (tree deeper than %d)", REFTOPO_STACK);
+    }
+    return B2COL_OK;
+}
+
+b2col_status b2col_upload_ref_bvh(b2col_ctx* ctx, const b2col_bitreenode* h_nodes, size_t n_nodes)
+{
+    if (!ctx || (n_nodes && !h_nodes)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n_nodes >= 0xffffffffull) return fail(ctx, B2COL_ERR_INVALID, "too many nodes");
+    CU(cudaSetDevice(ctx->device));
+    // validate child indices so that a malformed tree cannot make the kernel read out of bounds
+    for (size_t i = 0; i < n_nodes; ++i) {
+        const b2col_bitreenode& nd = h_nodes[i];
+        if (nd.type1 > 2 || nd.type2 > 2) return fail(ctx, B2COL_ERR_INVALID, "node %zu has an invalid type", i);
+        if ((nd.type1 == B2COL_NODE_BOUNDING_VOLUME && nd.index1 >= n_nodes) || (nd.type2 == B2COL_NODE_BOUNDING_VOLUME && nd.index2 >= n_nodes))
+            return fail(ctx, B2COL_ERR_INVALID, "node %zu refers to a child outside the array", i);
+    }
+    GUARD(ensure(ctx, ctx->d_ref_nodes, n_nodes * 60 + 4));
+    if (n_nodes) {
+        CU(cudaMemcpyAsync(ctx->d_ref_nodes.p, h_nodes, n_nodes * 60, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->n_ref_nodes = (uint32_t)n_nodes;
+    return B2COL_OK;
+}
+
+b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, size_t capacity, size_t* n_out)
+{
+    if (!ctx || !n_out) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    *n_out = 0;
+    if (!ctx->have_tree || ctx->tree_leaves == 0) return B2COL_OK;  // empty bvh_
+    if (ctx->tree_leaves != ctx->n_colliders || !ctx->d_world_aabb.p)
+        return fail(ctx, B2COL_ERR_STATE, "export needs a tree built by b2col_update on this ctx");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t n = ctx->tree_leaves;
+    if (n == 1) {
+        if (capacity < 1 || !h_out) return fail(ctx, B2COL_ERR_INVALID, "capacity too small");
+        b2col_aabb box;
+        uint32_t ent;
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaMemcpy(&box, ctx->d_world_aabb.p, 24, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(&ent, blob_leaf_entity(ctx, 1), 4, cudaMemcpyDeviceToHost));
+        memset(h_out, 0, sizeof *h_out);
+        h_out[0].box1 = box;
+        h_out[0].index1 = ent;
+        h_out[0].type1 = B2COL_NODE_ENTITY;
+        h_out[0].type2 = B2COL_NODE_EMPTY;
+        *n_out = 1;
+        return B2COL_OK;
+    }
+    const size_t cand = 2 * (size_t)n - 1;
+    DevBuf d_nodes, d_used;
+    GUARD(ensure(ctx, d_nodes, cand * 60));
+    b2col_status st = ensure(ctx, d_used, cand);
+    if (st != B2COL_OK) {
+        release(d_nodes);
+        return st;
+    }
+    std::vector<b2col_bitreenode> tmp(cand);
+    std::vector<uint8_t> used(cand);
+    cudaError_t e = cudaMemsetAsync(d_used.p, 0, cand, ctx->stream);
+    if (e == cudaSuccess) {
+        k_export<<<cdiv(n, 256), 256, 0, ctx->stream>>>(n, blob_hdr(ctx), blob_nodes(ctx), blob_leaf_entity(ctx, n), ctx->d_world_aabb.as<Aabb24>(),
+                                                        ctx->d_vals[ctx->sorted_side].as<uint32_t>(), d_nodes.as<BiTreeNode60>(), d_used.as<uint8_t>());
+        ++ctx->launches;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp.data(), d_nodes.p, cand * 60, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(used.data(), d_used.p, cand, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    release(d_nodes);
+    release(d_used);
+    if (e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "export failed: %s", cudaGetErrorString(e));
+    static_assert(sizeof(BiTreeNode60) == sizeof(b2col_bitreenode), "export node layout");
+    const size_t kept = compact_export(reinterpret_cast<const BiTreeNode60*>(tmp.data()), used.data(), cand, reinterpret_cast<BiTreeNode60*>(h_out), capacity);
+    if (kept > capacity || !h_out) return fail(ctx, B2COL_ERR_INVALID, "capacity %zu too small, need %zu nodes", capacity, kept);
+    *n_out = kept;
+    return B2COL_OK;
+}
+
+b2col_status b2col_get_world_matrices(b2col_ctx* ctx, uint32_t first_entity, uint32_t count, float* h_out16)
+{
+    if (!ctx || (count && !h_out16)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if ((size_t)first_entity + count > (size_t)ctx->n_entities + 1 || !ctx->d_world.p) return fail(ctx, B2COL_ERR_INVALID, "entity range out of bounds");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(h_out16, ctx->d_world.as<float>() + 16 * (size_t)first_entity, (size_t)count * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out)
+{
+    if (!ctx || (ctx->n_colliders && !h_out)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_tree || ctx->tree_leaves != ctx->n_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_update has not run");
+    if (!ctx->n_colliders) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(h_out, ctx->d_world_aabb.p, (size_t)ctx->n_colliders * 24, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out)
+{
+    if (!ctx || (ctx->n_colliders && !h_out)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_tree || ctx->tree_leaves != ctx->n_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_update has not run");
+    if (!ctx->n_colliders) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(h_out, ctx->d_vals[ctx->sorted_side].p, (size_t)ctx->n_colliders * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out)
+{
+    if (!ctx || !out) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    memset(out, 0, sizeof *out);
+    out->n_entities = ctx->n_entities;
+    out->n_colliders = ctx->n_colliders;
+    out->n_levels = ctx->level_offsets.empty() ? 0 : (uint32_t)ctx->level_offsets.size() - 1;
+    out->sort_passes = (uint32_t)ctx->passes;
+    out->kernel_launches = ctx->launches;
+    if (ctx->have_tree && ctx->d_blob.p) {
+        CU(cudaSetDevice(ctx->device));
+        BlobHeader h;
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaMemcpy(&h, ctx->d_blob.p, sizeof h, cudaMemcpyDeviceToHost));
+        out->n_internal_nodes = h.n_nodes;
+        out->root = h.root;
+        out->bvh_bytes = ctx->blob_bytes;
+        for (int k = 0; k < 3; ++k) {
+            out->scene_min[k] = ordered_to_float(~h.bounds_min_inv[k]);
+            out->scene_max[k] = ordered_to_float(h.bounds_max[k]);
+        }
+    }
+    return B2COL_OK;
+}
+
+b2col_status b2col_bvh_blob(b2col_ctx* ctx, void** d_ptr, size_t* bytes)
+{
+    if (!ctx || !d_ptr || !bytes) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_tree) return fail(ctx, B2COL_ERR_STATE, "no tree: call b2col_update first");
+    *d_ptr = ctx->d_blob.p;
+    *bytes = ctx->blob_bytes;
+    return B2COL_OK;
+}
+
+b2col_status b2col_bvh_export_blob(b2col_ctx* ctx, void* d_dst, size_t bytes)
+{
+    if (!ctx || !d_dst) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_tree) return fail(ctx, B2COL_ERR_STATE, "no tree: call b2col_update first");
+    if (bytes != ctx->blob_bytes) return fail(ctx, B2COL_ERR_INVALID, "destination holds %zu bytes, blob is %zu", bytes, ctx->blob_bytes);
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(d_dst, ctx->d_blob.p, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t bytes)
+{
+    if (!ctx || !d_src || bytes < sizeof(BlobHeader)) return fail(ctx, B2COL_ERR_INVALID, "bad blob");
+    CU(cudaSetDevice(ctx->device));
+    BlobHeader h;
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaMemcpy(&h, d_src, sizeof h, cudaMemcpyDeviceToHost));
+    if (h.magic != BLOB_MAGIC && !(h.magic == 0 && h.n_leaves == 0)) return fail(ctx, B2COL_ERR_INVALID, "blob magic mismatch");
+    if (blob_size_for(h.n_leaves) != bytes) return fail(ctx, B2COL_ERR_INVALID, "blob size %zu does not match its header (%u leaves)", bytes, h.n_leaves);
+    GUARD(ensure(ctx, ctx->d_blob, bytes));
+    if (ctx->d_blob.p != d_src) CU(cudaMemcpyAsync(ctx->d_blob.p, d_src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    ctx->blob_bytes = bytes;
+    ctx->tree_leaves = h.n_leaves;
+    ctx->have_tree = true;
+    return B2COL_OK;
+}
+
+b2col_status b2col_event_record(b2col_ctx* ctx, int slot)
+{
+    if (!ctx || slot < 0 || slot >= 16) return fail(ctx, B2COL_ERR_INVALID, "bad event slot");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->events[slot], ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_event_elapsed_ms(b2col_ctx* ctx, int a, int b, float* ms)
+{
+    if (!ctx || !ms || a < 0 || a >= 16 || b < 0 || b >= 16) return fail(ctx, B2COL_ERR_INVALID, "bad event slot");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(ctx->events[b]));
+    CU(cudaEventElapsedTime(ms, ctx->events[a], ctx->events[b]));
+    return B2COL_OK;
+}
+
+}  // extern "C"

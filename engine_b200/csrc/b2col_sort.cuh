@@ -1,0 +1,178 @@
+// b2col_sort.cuh — hand-written LSD radix sort of (64-bit Morton key, 32-bit primitive index) pairs
+// for sm_100a: 8-bit digits, one kernel per digit ("onesweep": every tile ranks its keys locally
+// and obtains the number of equal-digit keys in all earlier tiles by decoupled look-back over a
+// per-tile status word, so each pass reads and writes every pair exactly once).  The per-pass digit
+// histograms are produced upstream by the Morton kernel (b2col.cu), which already touches every key.
+//
+// HBM traffic per pass: 12 B read + 12 B written per pair.  Stable, deterministic.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+constexpr int RS_BITS = 8;
+constexpr int RS_RADIX = 1 << RS_BITS;
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 pairs per tile
+constexpr int RS_MAX_PASSES = 8;
+
+constexpr uint32_t LB_FLAG_AGG = 1u << 30;     // tile's own digit count is posted
+constexpr uint32_t LB_FLAG_PREFIX = 2u << 30;  // inclusive count over tiles 0..this is posted
+constexpr uint32_t LB_VALUE_MASK = (1u << 30) - 1u;
+
+static_assert(RS_THREADS == RS_RADIX, "one thread per digit in the scan phases");
+
+// Exclusive scan of one value per thread across the 256-thread block. `warp_tot` is 8 words of smem.
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* warp_tot)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w)
+        if (w < warp) base += warp_tot[w];
+    __syncthreads();
+    return base + inc - v;
+}
+
+// One digit pass. Grid = number of tiles; tiles are claimed through `ticket` so that a tile can only
+// ever wait on tiles that already started (forward progress of the look-back).
+//   ghist    [256]  total count of each digit value in this pass (over all n keys)
+//   lookback [tiles][256] zero-initialised status words for this pass
+__global__ void __launch_bounds__(RS_THREADS)
+k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
+           uint32_t n, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
+{
+    __shared__ uint64_t skeys[RS_TILE];  // reused for the values after the keys are written out
+    __shared__ uint32_t whist[RS_WARPS][RS_RADIX];
+    __shared__ uint32_t sbase[RS_RADIX];  // first tile-local sorted position of each digit
+    __shared__ uint32_t gbase[RS_RADIX];  // global position of that first element
+    __shared__ uint32_t warp_tot[RS_WARPS];
+    __shared__ uint32_t s_tile;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) whist[w][tid] = 0u;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t tile_base = tile * (uint32_t)RS_TILE;
+    const uint32_t valid = min((uint32_t)RS_TILE, n - tile_base);
+
+    // ---- load, warp-striped: item k of lane l sits at warp*512 + k*32 + l (coalesced, order-preserving)
+    uint64_t key[RS_ITEMS];
+    uint32_t val[RS_ITEMS];
+    uint32_t rank[RS_ITEMS];
+    const uint32_t wbase = (uint32_t)warp * (RS_ITEMS * 32u) + (uint32_t)lane;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t idx = wbase + (uint32_t)k * 32u;
+        const bool ok = idx < valid;
+        key[k] = ok ? kin[tile_base + idx] : ~0ull;
+        val[k] = ok ? vin[tile_base + idx] : 0u;
+    }
+
+    // ---- rank within the warp: keys with equal digits find each other with match.any
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t idx = wbase + (uint32_t)k * 32u;
+        const bool ok = idx < valid;
+        const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
+        const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (uint32_t)RS_RADIX);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0u;
+        if (lane == leader && ok) {
+            old = whist[warp][d];
+            whist[warp][d] = old + __popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        rank[k] = old + __popc(peers & lt_mask);
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- thread d: digit d. Exclusive offsets of each warp inside the tile's digit-d run.
+    uint32_t tile_count = 0u;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+        const uint32_t c = whist[w][tid];
+        whist[w][tid] = tile_count;
+        tile_count += c;
+    }
+    // ---- publish the tile's count, then sum the counts of all earlier tiles (decoupled look-back)
+    uint32_t excl = 0u;
+    {
+        volatile uint32_t* lb = lookback;
+        if (tile == 0u) {
+            lb[tid] = LB_FLAG_PREFIX | tile_count;
+        }
+        else {
+            lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_AGG | tile_count;
+            int t = (int)tile - 1;
+            for (;;) {
+                const uint32_t v = lb[(size_t)t * RS_RADIX + tid];
+                const uint32_t f = v >> 30;
+                if (f == 0u) continue;  // not posted yet: that tile is running (ticket order)
+                excl += v & LB_VALUE_MASK;
+                if (f == 2u) break;
+                --t;
+            }
+            lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_PREFIX | (excl + tile_count);
+        }
+    }
+    const uint32_t g_excl = block_excl_scan_256(ghist[tid], warp_tot);    // keys with a smaller digit, globally
+    const uint32_t t_excl = block_excl_scan_256(tile_count, warp_tot);    // ... within this tile
+    sbase[tid] = t_excl;
+    gbase[tid] = g_excl + excl;
+    __syncthreads();
+
+    // ---- scatter keys to their tile-local sorted position
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t idx = wbase + (uint32_t)k * 32u;
+        if (idx < valid) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
+            rank[k] += sbase[d] + whist[warp][d];
+            skeys[rank[k]] = key[k];
+        }
+    }
+    __syncthreads();
+    // ---- write keys: consecutive threads write consecutive addresses within each digit run
+    uint32_t dst[RS_ITEMS];
+#pragma unroll
+    for (int m = 0; m < RS_ITEMS; ++m) {
+        const uint32_t j = (uint32_t)tid + (uint32_t)m * RS_THREADS;
+        if (j < valid) {
+            const uint64_t kk = skeys[j];
+            const uint32_t d = (uint32_t)(kk >> shift) & (RS_RADIX - 1);
+            dst[m] = gbase[d] + (j - sbase[d]);
+            kout[dst[m]] = kk;
+        }
+    }
+    __syncthreads();
+    uint32_t* svals = reinterpret_cast<uint32_t*>(skeys);
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t idx = wbase + (uint32_t)k * 32u;
+        if (idx < valid) svals[rank[k]] = val[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < RS_ITEMS; ++m) {
+        const uint32_t j = (uint32_t)tid + (uint32_t)m * RS_THREADS;
+        if (j < valid) vout[dst[m]] = svals[j];
+    }
+}
+
+}  // namespace b2

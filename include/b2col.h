@@ -1,0 +1,192 @@
+/* b2col.h — C ABI of the B200 collision-query backend (libb2col.so).
+ *
+ * Drop-in boundary for ONE path of bailwillharr/engine: the collision system's AABB BVH
+ *   world-matrix propagation   reference src/system_transform.cpp:12-38   (TransformSystem::onUpdate)
+ *   world-space AABB refit     reference src/system_collisions.cpp:14-41,123-132 (transformBox + refit loop)
+ *   BVH build                  reference src/system_collisions.cpp:205-376 (BuildNode; replaced by an LBVH)
+ *   nearest-hit ray queries    reference src/system_collisions.cpp:62-100,160-199,379-540
+ *                              (RayBoxIntersection, GetRaycast, RaycastTreeNode)
+ * The reference has no FFI for this path: the boundary is the C++ class engine::CollisionSystem
+ * (reference include/system_collisions.h:28-74).  engine_b200/shim/system_collisions.{h,cpp} is the
+ * replacement class a maintainer compiles instead of the reference's; its bodies call the entry
+ * points below.  Everything here is POD + plain pointers, extern "C", no
+ * exceptions cross the boundary.  There is no CPU fallback: without a CUDA device b2col_create
+ * fails with B2COL_ERR_NO_DEVICE.
+ *
+ * Conventions
+ *  - Entities are uint32 IDs, 0 is invalid, first valid ID is 1 (reference include/entity.h:7,
+ *    include/scene.h:141).  Per-entity arrays are indexed BY ENTITY ID and therefore hold
+ *    n_entities + 1 rows, row 0 ignored — the layout of the reference's ComponentArray<T>
+ *    (include/ecs.h:25-50).
+ *  - Quaternions are x,y,z,w (glm::quat memory order); matrices are 16 floats column-major
+ *    (glm::mat4 memory order).
+ *  - A context owns one CUDA stream; calls on one context are serialised on it.  A context is
+ *    not thread-safe.  One context per GPU.
+ *  - Pointers named h_* are host memory, d_* are device memory on the context's device.  The
+ *    caller owns every buffer it passes; nothing is retained after the call returns except
+ *    where a *_device call documents that the work is merely enqueued.
+ */
+#ifndef B2COL_H
+#define B2COL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2COL_ABI_VERSION 1
+
+typedef struct b2col_ctx b2col_ctx;
+
+typedef enum b2col_status {
+    B2COL_OK = 0,
+    B2COL_ERR_INVALID = 1,     /* bad argument */
+    B2COL_ERR_CUDA = 2,        /* a CUDA call failed; see b2col_last_error */
+    B2COL_ERR_NO_DEVICE = 3,   /* no usable CUDA device: this library has no CPU path */
+    B2COL_ERR_STATE = 4,       /* call sequence error (e.g. update before set_*) */
+    B2COL_ERR_UNSUPPORTED = 5, /* e.g. a parent whose ID is not smaller than its child's */
+    B2COL_ERR_OVERFLOW = 6     /* traversal stack overflow in reference-topology mode */
+} b2col_status;
+
+/* engine::Ray — reference include/system_collisions.h:13-16 (24 bytes) */
+typedef struct b2col_ray {
+    float origin[3];
+    float direction[3]; /* need not be normalised: GetRaycast normalises (:162) */
+} b2col_ray;
+
+/* engine::Raycast — reference include/system_collisions.h:18-24 (36 bytes; bool + 3 pad).
+ * A miss is all-zero (value-initialised, reference src/system_collisions.cpp:164-165). */
+typedef struct b2col_raycast {
+    float location[3];
+    float normal[3];
+    uint32_t hit_entity;
+    float distance; /* = tmin of the slab test; NEGATIVE when the origin is inside the box (:99) */
+    uint8_t hit;
+    uint8_t pad[3]; /* always written as 0 */
+} b2col_raycast;
+
+/* engine::AABB — reference include/component_collider.h:7-10 (24 bytes) */
+typedef struct b2col_aabb {
+    float min[3];
+    float max[3];
+} b2col_aabb;
+
+/* engine::CollisionSystem::BiTreeNode — reference include/system_collisions.h:40-48 (60 bytes, align 4) */
+enum { B2COL_NODE_BOUNDING_VOLUME = 0, B2COL_NODE_ENTITY = 1, B2COL_NODE_EMPTY = 2 };
+typedef struct b2col_bitreenode {
+    b2col_aabb box1, box2;
+    uint32_t index1, index2; /* node index or entity ID, depending on type */
+    uint8_t type1, type2;
+    uint8_t pad[2];
+} b2col_bitreenode;
+
+typedef struct b2col_config {
+    int device;              /* CUDA device ordinal */
+    float max_distance;      /* reference hard-codes T = 1000.0f (src/system_collisions.cpp:384); 0 => 1000 */
+    int morton_bits_per_axis; /* 10..21; 0 => 16 (48-bit keys, 6 radix passes) */
+    int use_cuda_graph;      /* 1: b2col_update replays a captured CUDA graph when shapes are unchanged */
+} b2col_config;
+
+typedef enum b2col_mode {
+    B2COL_MODE_LBVH = 0,    /* production: tree built on the GPU by b2col_update */
+    B2COL_MODE_REFTOPO = 1  /* walk a reference-format tree uploaded with b2col_upload_ref_bvh
+                               (exact reference semantics incl. tie winners; parity mode) */
+} b2col_mode;
+
+typedef struct b2col_stats {
+    uint32_t n_entities, n_colliders, n_levels;
+    uint32_t n_internal_nodes;  /* LBVH internal nodes (= max(n_colliders,2) - 1) */
+    uint32_t root;              /* index of the LBVH root node */
+    uint32_t sort_passes;
+    uint64_t kernel_launches;   /* cumulative count of this library's kernel launches on this ctx */
+    uint64_t bvh_bytes;         /* device bytes of the traversal structure (nodes + leaf entity table) */
+    float scene_min[3], scene_max[3]; /* centroid bounds used for the Morton grid */
+} b2col_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+int b2col_abi_version(void);
+/* replaces: CollisionSystem::CollisionSystem(Scene*) — reference src/system_collisions.cpp:104 */
+b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg /* may be NULL */);
+void b2col_destroy(b2col_ctx* ctx);
+/* message for the last non-OK status on this ctx (ctx may be NULL for create failures) */
+const char* b2col_last_error(const b2col_ctx* ctx);
+b2col_status b2col_sync(b2col_ctx* ctx);
+/* the context's cudaStream_t, for callers that time with their own events */
+void* b2col_stream(b2col_ctx* ctx);
+
+/* ---- scene input ---------------------------------------------------------------------------- */
+/* Hierarchy (TransformComponent::parent, reference include/component_transform.h:22).
+ * h_parent[0..n_entities]; parent 0 = root.  Every parent ID must be smaller than its child's (true
+ * for every entity-creating path of the reference: Scene::CreateEntity hands out ascending IDs,
+ * src/scene.cpp:37); otherwise B2COL_ERR_UNSUPPORTED. */
+b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint32_t* h_parent);
+/* TRS (TransformComponent::position/rotation/scale).  Rows 0..n_entities. */
+b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3);
+/* Same, from device memory (async on the ctx stream; buffers must stay valid until b2col_sync). */
+b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3);
+/* Alternative to hierarchy+TRS when the caller keeps the reference's CPU TransformSystem:
+ * upload TransformComponent::world_matrix directly (rows 0..n_entities, 16 floats each);
+ * b2col_update then skips propagation. */
+b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const float* h_world16);
+/* Collider set = CollisionSystem::m_entities + ColliderComponent::aabb
+ * (reference src/system_collisions.cpp:104,125-127).  Entities must be valid IDs; the reference
+ * iterates them in ascending order (std::set) and so should the caller, but any order is accepted. */
+b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n_colliders, const uint32_t* h_entity, const b2col_aabb* h_local);
+
+/* ---- per-frame update ----------------------------------------------------------------------- */
+/* replaces: TransformSystem::onUpdate (src/system_transform.cpp:12-38) followed by
+ * CollisionSystem::onUpdate (src/system_collisions.cpp:112-158): propagate world matrices, refit
+ * world AABBs, rebuild the BVH from scratch (the reference rebuilds every frame, :121).
+ * Enqueued on the ctx stream; returns without waiting.  n_colliders == 0 yields an empty tree and
+ * every query misses (the reference abort()s, :136 -> :208 — deliberate divergence). */
+b2col_status b2col_update(b2col_ctx* ctx);
+
+/* ---- queries -------------------------------------------------------------------------------- */
+/* replaces: CollisionSystem::GetRaycast (src/system_collisions.cpp:160-199), batched.
+ * Host buffers; copies in, traces, copies out, returns when h_out is complete. */
+b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode);
+/* Device buffers; enqueued on the ctx stream, returns without waiting. */
+b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode);
+
+/* ---- reference-topology mode / debug overlay ------------------------------------------------- */
+/* Upload a tree in the reference's own format (e.g. CollisionSystem::bvh_), root = LAST node
+ * (src/system_collisions.cpp:168). */
+b2col_status b2col_upload_ref_bvh(b2col_ctx* ctx, const b2col_bitreenode* h_nodes, size_t n_nodes);
+/* replaces: the public member CollisionSystem::bvh_ (include/system_collisions.h:58) read by the
+ * debug overlay (src/application.cpp:61-62,153-154).  Writes the GPU-built tree in the reference's
+ * format: {BoundingVolume,BoundingVolume} / {Entity,Entity} / {Entity,Empty} nodes only, children
+ * before parents, root last, so the reference's own GetRaycast can walk it.  capacity in nodes;
+ * 2*n_colliders is always enough.  *n_out = nodes written. */
+b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, size_t capacity, size_t* n_out);
+
+/* ---- read-back (parity tests; world_matrix write-back for MeshRenderSystem) ------------------ */
+/* rows first_entity .. first_entity+count-1, 16 floats each, column-major */
+b2col_status b2col_get_world_matrices(b2col_ctx* ctx, uint32_t first_entity, uint32_t count, float* h_out16);
+/* world AABBs in the order colliders were given to b2col_set_colliders */
+b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out);
+/* collider indices (into the b2col_set_colliders order) in BVH leaf order == Morton order ==
+ * depth-first leaf order of the tree, the order that decides tie winners */
+b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out);
+b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out);
+
+/* ---- multi-GPU replication ------------------------------------------------------------------- */
+/* The traversal structure lives in ONE contiguous device allocation so that it can be replicated
+ * with a single broadcast (NCCL over NVLink; the host side does the collective).  export returns the
+ * device pointer and size of the source rank's blob; import copies a received blob of identical
+ * size into this ctx and makes it the current tree. */
+b2col_status b2col_bvh_blob(b2col_ctx* ctx, void** d_ptr, size_t* bytes);
+/* copy the blob into caller-owned device memory (e.g. the tensor a collective will send); enqueued */
+b2col_status b2col_bvh_export_blob(b2col_ctx* ctx, void* d_dst, size_t bytes);
+b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t bytes);
+
+/* ---- timing helpers (CUDA events on the ctx stream) ------------------------------------------ */
+/* slot in [0,16) */
+b2col_status b2col_event_record(b2col_ctx* ctx, int slot);
+b2col_status b2col_event_elapsed_ms(b2col_ctx* ctx, int slot_begin, int slot_end, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2COL_H */

@@ -1,0 +1,143 @@
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE, never loaded by engine_b200.
+//
+// Runs the per-thread kernel bodies of engine_b200/csrc/b2col_{math,bvh}.cuh on the host, one
+// "thread" after another, so that the LOGIC of the GPU path (hierarchy emission, tie order, export,
+// both traversals, transform/refit arithmetic) can be checked against the oracle on machines
+// without a GPU (pytest -m "not gpu").  It cannot and does not stand in for the CUDA library:
+// the radix sort, reductions and everything launch-related only exist in b2col.cu and are only
+// tested on the GPU.  Build: g++ -O2 -ffp-contract=off (tests/test_emu_logic.py does it).
+#include <algorithm>
+#include <cstring>
+#include <numeric>
+#include <vector>
+
+#include "../../engine_b200/csrc/b2col_bvh.cuh"
+
+using namespace b2;
+
+struct HostOps {
+    static void store_slot(Slot* p, const Slot& s) { *p = s; }
+    static Slot load_slot(const Slot* p) { return *p; }
+    static Slot load_slot_coherent(const Slot* p) { return *p; }
+    static void fence() {}
+    static uint32_t exch(uint32_t* p, uint32_t v)
+    {
+        const uint32_t o = *p;
+        *p = v;
+        return o;
+    }
+};
+
+extern "C" {
+
+void emu_propagate(uint32_t n_entities, const uint32_t* parent, const float* pos3, const float* rot4, const float* scl3, float* world16)
+{
+    for (uint32_t e = 1; e <= n_entities; ++e) {  // ascending ID == level order because parents precede children
+        float L[16];
+        local_matrix(pos3 + 3 * (size_t)e, rot4 + 4 * (size_t)e, scl3 + 3 * (size_t)e, L);
+        if (parent[e]) mat_mul(world16 + 16 * (size_t)parent[e], L, world16 + 16 * (size_t)e);
+        else std::memcpy(world16 + 16 * (size_t)e, L, sizeof L);
+    }
+}
+
+void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, const float* world16, Aabb24* out)
+{
+    for (uint32_t i = 0; i < n; ++i) {
+        const Box b = transform_box(col_local[i].lo, col_local[i].hi, world16 + 16 * (size_t)col_entity[i]);
+        for (int k = 0; k < 3; ++k) {
+            out[i].lo[k] = b.lo[k];
+            out[i].hi[k] = b.hi[k];
+        }
+    }
+}
+
+// bounds -> Morton keys -> stable sort -> bottom-up hierarchy.  nodes: max(n-1,1) entries.
+// `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
+// that the result does not depend on thread scheduling.
+void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, Node* nodes, uint32_t* leaf_entity,
+               uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order)
+{
+    if (n == 0) return;
+    float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t i = 0; i < n; ++i)
+        for (int k = 0; k < 3; ++k) {
+            const float c = (world_aabb[i].lo[k] + world_aabb[i].hi[k]) * 0.5f;
+            if (std::isfinite(c)) {
+                smin[k] = fminf(smin[k], c);
+                smax[k] = fmaxf(smax[k], c);
+            }
+        }
+    float sinv[3];
+    for (int k = 0; k < 3; ++k) {
+        // same round trip through the order-preserving encoding as the device
+        smin[k] = ordered_to_float(~(~float_to_ordered(smin[k])));
+        const float ext = smax[k] - smin[k];
+        sinv[k] = (ext > 0.0f && std::isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
+    }
+    std::vector<uint64_t> keys(n);
+    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, smin, sinv, bits);
+    std::vector<uint32_t> idx(n);
+    std::iota(idx.begin(), idx.end(), 0u);
+    std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+    for (uint32_t i = 0; i < n; ++i) {
+        sorted_prim[i] = idx[i];
+        sorted_keys[i] = keys[idx[i]];
+    }
+    std::vector<uint32_t> other(n, UNVISITED);
+    for (uint32_t t = 0; t < n; ++t)
+        build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), leaf_entity, root);
+}
+
+void emu_trace_lbvh(const Node* nodes, uint32_t root, uint32_t n_leaves, const uint32_t* leaf_entity, const float* rays6, size_t n_rays,
+                    uint32_t* out9, float T)
+{
+    for (size_t i = 0; i < n_rays; ++i) {
+        const RayPre r = ray_prepare(rays6 + 6 * i, rays6 + 6 * i + 3);
+        if (n_leaves == 0) {
+            write_raycast(out9 + 9 * i, r, false, 0.0f, 0, 0u);
+            continue;
+        }
+        const Hit h = trace_lbvh<HostOps>(r, nodes, root, T);
+        write_raycast(out9 + 9 * i, r, h.leaf >= 0, h.t, h.side, h.leaf >= 0 ? leaf_entity[h.leaf] : 0u);
+    }
+}
+
+int emu_trace_reftopo(const uint32_t* words, uint32_t n_nodes, const float* rays6, size_t n_rays, uint32_t* out9, float T)
+{
+    int overflow = 0;
+    for (size_t i = 0; i < n_rays; ++i) {
+        const RayPre r = ray_prepare(rays6 + 6 * i, rays6 + 6 * i + 3);
+        const RefHit h = trace_reftopo(r, words, n_nodes, T);
+        overflow |= h.overflow ? 1 : 0;
+        write_raycast(out9 + 9 * i, r, h.hit, h.t, h.side, h.entity);
+    }
+    return overflow;
+}
+
+// returns number of nodes written to out (capacity 2n)
+size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const uint32_t* leaf_entity, const Aabb24* world_aabb, const uint32_t* sorted_prim,
+                  BiTreeNode60* out, size_t capacity)
+{
+    if (n == 0) return 0;
+    if (n == 1) {
+        std::memset(out, 0, sizeof *out);
+        for (int k = 0; k < 3; ++k) {
+            out[0].box1[k] = world_aabb[0].lo[k];
+            out[0].box1[3 + k] = world_aabb[0].hi[k];
+        }
+        out[0].index1 = leaf_entity[0];
+        out[0].type1 = 1;
+        out[0].type2 = 2;
+        return 1;
+    }
+    const size_t cand = 2 * (size_t)n - 1;
+    std::vector<BiTreeNode60> tmp(cand);
+    std::vector<uint8_t> used(cand, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+        export_wrapper(i, world_aabb, sorted_prim, leaf_entity, tmp.data());
+        if (i + 1 < n) export_internal(i, n, root, nodes, leaf_entity, tmp.data(), used.data());
+    }
+    return compact_export(tmp.data(), used.data(), cand, out, capacity);
+}
+
+}  // extern "C"

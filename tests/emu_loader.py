@@ -1,0 +1,88 @@
+"""TEST INFRASTRUCTURE: builds and loads tests/emu/libemu.so (host execution of the kernel bodies)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+SRC = os.path.join(HERE, "emu", "emu.cpp")
+LIB = os.path.join(HERE, "emu", "libemu.so")
+DEPS = [SRC] + [os.path.join(ROOT, "engine_b200", "csrc", f) for f in ("b2col_math.cuh", "b2col_bvh.cuh")]
+
+NODE64 = np.dtype([("lo0", "<f4", 3), ("hi0", "<f4", 3), ("ref0", "<u4"), ("aux0", "<u4"), ("lo1", "<f4", 3), ("hi1", "<f4", 3), ("ref1", "<u4"), ("aux1", "<u4")])
+assert NODE64.itemsize == 64
+LEAF_BIT = 0x80000000
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Emu:
+    def __init__(self):
+        if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in DEPS):
+            subprocess.check_call(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-std=c++17", "-Wno-unknown-pragmas", "-o", LIB, SRC])
+        self.lib = C.CDLL(LIB)
+        self.lib.emu_export.restype = C.c_size_t
+        self.lib.emu_trace_reftopo.restype = C.c_int
+
+    def propagate(self, parent, pos, rot, scl):
+        parent = np.ascontiguousarray(parent, np.uint32)
+        n = parent.shape[0] - 1
+        world = np.zeros((n + 1, 16), np.float32)
+        pos, rot, scl = (np.ascontiguousarray(a, np.float32) for a in (pos, rot, scl))
+        self.lib.emu_propagate(C.c_uint32(n), _p(parent), _p(pos), _p(rot), _p(scl), _p(world))
+        return world
+
+    def refit(self, entity, local, world):
+        entity = np.ascontiguousarray(entity, np.uint32)
+        local = np.ascontiguousarray(local, np.float32).reshape(-1, 6)
+        world = np.ascontiguousarray(world, np.float32)
+        out = np.zeros((entity.shape[0], 6), np.float32)
+        self.lib.emu_refit(C.c_uint32(entity.shape[0]), _p(entity), _p(local), _p(world), _p(out))
+        return out
+
+    def build(self, world_aabb, entity, bits=16, order=None):
+        world_aabb = np.ascontiguousarray(world_aabb, np.float32).reshape(-1, 6)
+        entity = np.ascontiguousarray(entity, np.uint32)
+        n = entity.shape[0]
+        nodes = np.zeros(max(n - 1, 1), NODE64)
+        leaf_entity = np.zeros(n, np.uint32)
+        sorted_prim = np.zeros(n, np.uint32)
+        sorted_keys = np.zeros(n, np.uint64)
+        root = C.c_uint32(0)
+        if order is not None:
+            order = np.ascontiguousarray(order, np.uint32)
+        self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), _p(nodes), _p(leaf_entity), _p(sorted_prim), _p(sorted_keys),
+                           C.byref(root), _p(order))
+        return dict(n=n, nodes=nodes, leaf_entity=leaf_entity, sorted_prim=sorted_prim, sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
+
+    def trace_lbvh(self, tree, rays, T=1000.0):
+        from oracle.oracle import RAYCAST_DTYPE
+
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        self.lib.emu_trace_lbvh(_p(tree["nodes"]), C.c_uint32(tree["root"]), C.c_uint32(tree["n"]), _p(tree["leaf_entity"]), _p(rays),
+                                C.c_size_t(rays.shape[0]), _p(out), C.c_float(T))
+        return out
+
+    def trace_reftopo(self, nodes60, rays, T=1000.0):
+        from oracle.oracle import NODE_DTYPE, RAYCAST_DTYPE
+
+        nodes60 = np.ascontiguousarray(nodes60, NODE_DTYPE)
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        ov = self.lib.emu_trace_reftopo(_p(nodes60), C.c_uint32(nodes60.shape[0]), _p(rays), C.c_size_t(rays.shape[0]), _p(out), C.c_float(T))
+        assert ov == 0, "stack overflow"
+        return out
+
+    def export(self, tree):
+        from oracle.oracle import NODE_DTYPE
+
+        n = tree["n"]
+        out = np.zeros(2 * max(n, 1), NODE_DTYPE)
+        k = self.lib.emu_export(C.c_uint32(n), _p(tree["nodes"]), C.c_uint32(tree["root"]), _p(tree["leaf_entity"]), _p(tree["world_aabb"]),
+                                _p(tree["sorted_prim"]), _p(out), C.c_size_t(out.shape[0]))
+        return out[:k].copy()

@@ -1,0 +1,289 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI (engine_b200.collision -> libb2col.so),
+against the oracle: golden vectors from the real reference, the oracle port, the live reference where
+oracle/_ref/libref_engine.so travelled with the snapshot, and size-independent properties at
+BASELINE.json's full sizes.  Parity bar: hit flag + hit_entity bit-exact; distance / location /
+normal held to exact float equality (stricter than the 1e-5 relative tolerance of north_star)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import SCENE_FIXTURES, assert_raycast_equal, load_golden
+from emu_loader import Emu
+from engine_b200 import capi, synth
+from oracle.oracle import RefEngine
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def CollisionSystem():
+    if not torch.cuda.is_available():
+        pytest.fail("no CUDA device: the gpu-marked tests must run on the B200 box")
+    from engine_b200.collision import CollisionSystem as CS
+
+    return CS
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return Emu()
+
+
+# ---------------------------------------------------------------------------------------------
+# golden fixtures (outputs of the real reference)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_golden_scene(CollisionSystem, port, emu, name):
+    g = load_golden(name)
+    s = g["scene"]
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    # a1: TransformSystem::onUpdate
+    assert (bits(cs.world_matrices()) == bits(g["world"])).all(), "world matrices must be bit-exact"
+    # a2: refit
+    boxes = cs.world_aabbs()
+    assert (bits(boxes) == bits(g["world_aabb"])).all(), "world AABBs must be bit-exact"
+    # a6/a7 reference-topology mode on the reference's own tree: everything incl. tie winners
+    cs.upload_ref_bvh(g["bvh"])
+    assert_raycast_equal(cs.get_raycasts(g["rays"], capi.MODE_REFTOPO), g["raycast"], name + " reftopo")
+    # a4: the LBVH equals the host execution of the same algorithm bit for bit (sort order, nodes, root)
+    order = cs.leaf_order()
+    tree = emu.build(boxes, s.collider_entity)
+    assert (order == tree["sorted_prim"]).all(), "radix sort / Morton keys disagree with the host restatement"
+    exported = cs.bvh
+    assert (exported.view(np.uint8) == emu.export(tree).view(np.uint8)).all(), "exported tree differs"
+    # a6/a7 production traversal
+    got = cs.get_raycasts(g["rays"])
+    brute, ties = port.raycast_brute(s.collider_entity[order], boxes[order], g["rays"], nthreads=4, want_ties=True)
+    assert_raycast_equal(got, brute, name + " lbvh vs brute force (last-in-Morton-order tie rule)")
+    assert_raycast_equal(got, port.raycast_tree(exported, g["rays"]), name + " lbvh vs reference traversal of the exported tree")
+    assert_raycast_equal(got, g["raycast"], name + " lbvh vs reference on its own tree", ignore_entity_on=ties > 0)
+    if RefEngine.available():
+        r = RefEngine()
+        r.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+        r.add_colliders(s.collider_entity, s.collider_aabb)
+        r.set_bvh(exported)
+        assert_raycast_equal(got, r.raycast(g["rays"]), name + " lbvh vs LIVE reference GetRaycast on the exported tree")
+    cs.close()
+
+
+def test_world_matrices_supplied_by_caller(CollisionSystem):
+    """The shim path that keeps the reference's CPU TransformSystem: upload world_matrix, skip propagation."""
+    g = load_golden("hier1500")
+    s = g["scene"]
+    cs = CollisionSystem()
+    world = np.zeros((s.n_entities + 1, 16), np.float32)
+    world[1:] = g["world"]
+    cs.set_world_matrices(world)
+    cs.set_colliders(s.collider_entity, s.collider_aabb)
+    cs.on_update()
+    assert (bits(cs.world_aabbs()) == bits(g["world_aabb"])).all()
+
+
+# ---------------------------------------------------------------------------------------------
+# edge cases
+# ---------------------------------------------------------------------------------------------
+def test_queries_before_first_update_miss(CollisionSystem):
+    cs = CollisionSystem()  # frame 0: bvh_ empty, every query misses (reference :164-167)
+    out = cs.get_raycasts(synth.random_rays(100, extent=5))
+    assert not out.view(np.uint8).any()
+    assert cs.get_raycasts(np.zeros((0, 6), np.float32)).shape == (0,)
+
+
+def test_zero_colliders(CollisionSystem):
+    cs = CollisionSystem()
+    s = synth.uniform_boxes(4)
+    cs.set_hierarchy(s.parent)
+    cs.set_trs(s.pos, s.rot, s.scl)
+    cs.set_colliders(np.zeros(0, np.uint32), np.zeros((0, 6), np.float32))
+    cs.on_update()  # the reference abort()s here (:136 -> :208); we build an empty tree
+    assert not cs.get_raycasts(synth.random_rays(64, extent=5)).view(np.uint8).any()
+    assert cs.bvh.shape == (0,)
+
+
+def test_error_statuses(CollisionSystem):
+    cs = CollisionSystem()
+    with pytest.raises(capi.B2ColError) as e:
+        cs.on_update()
+    assert e.value.status == capi.ERR_STATE
+    with pytest.raises(capi.B2ColError) as e:
+        cs.set_hierarchy(np.array([0, 2, 0], np.uint32))  # entity 1's parent is 2
+    assert e.value.status == capi.ERR_UNSUPPORTED
+    with pytest.raises(capi.B2ColError) as e:
+        cs.set_colliders(np.array([0], np.uint32), np.zeros((1, 6), np.float32))
+    assert e.value.status == capi.ERR_INVALID
+    bad = np.zeros(1, capi.NODE_DTYPE)
+    bad["index1"] = 7  # BoundingVolume child outside the array
+    with pytest.raises(capi.B2ColError):
+        cs.upload_ref_bvh(bad)
+
+
+def test_degenerate_inputs(CollisionSystem, port):
+    """inf / NaN components and zero-length directions must not hang or fault, and must agree with the
+    oracle on hit flags and IDs."""
+    s = synth.uniform_boxes(2000, seed=51, extent=30)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    rays = synth.random_rays(512, seed=52, extent=35)
+    rays[0, 3:] = 0.0                      # zero direction -> NaN after normalize
+    rays[1, 3:] = (np.inf, 0, 0)
+    rays[2, 0] = np.nan
+    rays[3, 3:] = (0.0, -0.0, 1.0)
+    rays[4, 3:] = (1e-30, 1e-30, 1e-30)    # denormal dot product
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    got = cs.get_raycasts(rays)
+    want = port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=4)
+    assert (got["hit"] == want["hit"]).all() and (got["hit_entity"] == want["hit_entity"]).all()
+
+
+# ---------------------------------------------------------------------------------------------
+# radix sort and hierarchy at scale, duplicates
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,bits_per_axis", [(4095, 16), (4096, 16), (4097, 16), (70001, 10), (300000, 16), (300000, 21), (1 << 20, 16)])
+def test_build_matches_host_restatement(CollisionSystem, emu, n, bits_per_axis):
+    s = synth.uniform_boxes(n, seed=60 + bits_per_axis, extent=200.0) if n < 200000 else synth.clustered_boxes(n, seed=61, n_clusters=50)
+    cs = CollisionSystem(morton_bits_per_axis=bits_per_axis)
+    cs.set_scene(s)
+    cs.on_update()
+    boxes = cs.world_aabbs()
+    tree = emu.build(boxes, s.collider_entity, bits=bits_per_axis)
+    order = cs.leaf_order()
+    assert sorted(order.tolist()) == list(range(n)) if n <= 70001 else np.array_equal(np.sort(order), np.arange(n, dtype=np.uint32))
+    assert np.array_equal(order, tree["sorted_prim"]), "sorted order differs from a stable sort of the same keys"
+    st = cs.stats()
+    assert st["root"] == tree["root"] and st["n_internal_nodes"] == n - 1
+    if n <= 300000:
+        assert (cs.bvh.view(np.uint8) == emu.export(tree).view(np.uint8)).all()
+
+
+def test_duplicate_boxes_and_ties(CollisionSystem, port):
+    s = synth.grid_boxes(12, 12, 12, spacing=3.0)
+    # append exact duplicates of the first 300 boxes (new entities at the same place)
+    E = s.n_entities
+    dup = 300
+    s2 = synth.Scene(
+        parent=np.concatenate([s.parent, np.zeros(dup, np.uint32)]), pos=np.concatenate([s.pos, s.pos[1 : dup + 1]]),
+        rot=np.concatenate([s.rot, s.rot[1 : dup + 1]]), scl=np.concatenate([s.scl, s.scl[1 : dup + 1]]),
+        collider_entity=np.arange(1, E + dup + 1, dtype=np.uint32), collider_aabb=np.concatenate([s.collider_aabb, s.collider_aabb[:dup]]),
+    )
+    cs = CollisionSystem()
+    cs.set_scene(s2)
+    cs.on_update()
+    rays = synth.axis_rays(20000, seed=71, extent=36)
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    got = cs.get_raycasts(rays)
+    brute, ties = port.raycast_brute(s2.collider_entity[order], boxes[order], rays, nthreads=8, want_ties=True)
+    assert (ties > 0).sum() > 200, "scene must produce exact ties"
+    assert_raycast_equal(got, brute, "ties: lbvh vs brute force")
+    assert_raycast_equal(got, port.raycast_tree(cs.bvh, rays), "ties: lbvh vs reference traversal of exported tree")
+
+
+# ---------------------------------------------------------------------------------------------
+# configs at (or near) BASELINE sizes: sampled oracle + size-independent properties
+# ---------------------------------------------------------------------------------------------
+def test_config2_100k_camera_rays(CollisionSystem, port):
+    s = synth.static_city(100_000)
+    rays = synth.camera_rays(1000, 1000)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    got = cs.get_raycasts(rays)
+    exported = cs.bvh
+    # reference traversal (restated) of the exported tree on every 8th ray
+    sel = np.arange(0, rays.shape[0], 8)
+    assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), "config 2 vs reference traversal")
+    # brute force on a sample
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    sel = np.arange(0, rays.shape[0], 997)
+    assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), "config 2 vs brute force")
+    assert got["hit"].sum() > 1000
+
+
+def test_config3_1m_incoherent(CollisionSystem, port):
+    n_rays = 1 << 21
+    s = synth.uniform_boxes(1_000_000)
+    rays = synth.random_rays(n_rays)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    got = cs.get_raycasts(rays)
+    frac = got["hit"].mean()
+    assert 0.2 < frac < 0.9, frac
+    # (1) idempotence + rebuild determinism
+    cs.on_update()
+    again = cs.get_raycasts(rays)
+    assert (got.view(np.uint8) == again.view(np.uint8)).all()
+    # (2) sharded == unsharded (what the multi-GPU path relies on)
+    parts = np.concatenate([cs.get_raycasts(rays[lo : lo + n_rays // 8]) for lo in range(0, n_rays, n_rays // 8)])
+    assert (parts.view(np.uint8) == got.view(np.uint8)).all()
+    # (3) reference traversal of the exported tree on a sample, (4) brute force on a smaller sample
+    exported = cs.bvh
+    sel = np.arange(0, n_rays, 64)
+    assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), "config 3 vs reference traversal")
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    sel = np.arange(0, n_rays, 8192)
+    assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), "config 3 vs brute force")
+    # (5) geometric self-consistency of every hit: location on the hit box's face named by the normal
+    h = got["hit"] > 0
+    inv = np.empty(s.n_entities + 1, np.int64)
+    inv[s.collider_entity] = np.arange(s.n_colliders)
+    b = boxes[inv[got["hit_entity"][h]]]
+    loc, nrm = got["location"][h], got["normal"][h]
+    axis = np.abs(nrm).argmax(1)
+    face = np.where(nrm[np.arange(len(axis)), axis] > 0, b[np.arange(len(axis)), 3 + axis], b[np.arange(len(axis)), axis])
+    outside = got["distance"][h] >= 0
+    assert np.allclose(loc[np.arange(len(axis)), axis][outside], face[outside], rtol=1e-4, atol=1e-2)
+
+
+def test_config4_dynamic_frames(CollisionSystem, port, emu):
+    """Per-frame TRS change -> propagate + refit + rebuild; checked against the oracle every frame."""
+    n, roots = 200_000, 200
+    s = synth.hierarchy_scene(n, roots, extent=500)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    rays = synth.random_rays(50_000, seed=81, extent=500)
+    for frame in range(3):
+        synth.perturb_roots(s, roots, frame)
+        cs.set_trs(s.pos, s.rot, s.scl)
+        cs.on_update()
+        world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+        assert (bits(cs.world_matrices()) == bits(world[1:])).all(), f"frame {frame}: world matrices"
+        want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+        boxes = cs.world_aabbs()
+        assert (bits(boxes) == bits(want_boxes)).all(), f"frame {frame}: world AABBs"
+        got = cs.get_raycasts(rays)
+        sel = np.arange(0, rays.shape[0], 10)
+        assert_raycast_equal(got[sel], port.raycast_tree(cs.bvh, rays[sel], nthreads=8), f"frame {frame}")
+
+
+def test_device_resident_and_replicated_tree(CollisionSystem):
+    """raycast_device on torch CUDA buffers == host path; a second context that imports the BVH blob
+    (what each rank does after the NCCL broadcast) answers identically."""
+    s = synth.uniform_boxes(50_000, seed=91, extent=300)
+    rays = synth.random_rays(200_000, seed=92, extent=300)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    want = cs.get_raycasts(rays)
+    d_rays = torch.from_numpy(rays).cuda()
+    d_out = torch.empty(rays.shape[0] * 36, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    cs.raycast_device(d_rays, rays.shape[0], d_out)
+    cs.sync()
+    assert (d_out.cpu().numpy() == want.view(np.uint8)).all()
+    p, nbytes = cs.bvh_blob()
+    replica = CollisionSystem()
+    blob = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    cs.bvh_export_blob(blob, nbytes)
+    cs.sync()
+    replica.bvh_import_blob(blob, nbytes)
+    assert (replica.get_raycasts(rays).view(np.uint8) == want.view(np.uint8)).all()
+    st0, st1 = cs.stats(), replica.stats()
+    assert st0["kernel_launches"] > 0 and st1["kernel_launches"] > 0
