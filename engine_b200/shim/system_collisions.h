@@ -1,0 +1,83 @@
+// Drop-in replacement for the reference's include/system_collisions.h (bailwillharr/engine).
+//
+// Same namespace, class name, base class, public method names and public `bvh_` member as the
+// reference class (reference include/system_collisions.h:28-74), so that scene.cpp (:29 registers
+// it), application.cpp (:61-62,153-154 read bvh_) and game code calling
+// scene->GetSystem<CollisionSystem>()->GetRaycast(ray) compile unchanged when this directory is put
+// in front of the reference's include path.  The bodies (system_collisions.cpp next to this file)
+// forward to the C ABI of libb2col.so (include/b2col.h): the BVH lives on the GPU.
+//
+// Additive API: GetRaycasts (batch), SyncDebugBvh / keep_debug_bvh (materialise bvh_ on demand).
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include <glm/vec3.hpp>
+
+#include "component_collider.h"
+#include "ecs.h"
+
+struct b2col_ctx;  // include/b2col.h
+
+namespace engine {
+
+// Layouts are part of the contract with libb2col.so: static_asserts in system_collisions.cpp.
+struct Ray {
+    glm::vec3 origin;
+    glm::vec3 direction;  // need not be normalised
+};
+
+struct Raycast {
+    glm::vec3 location;
+    glm::vec3 normal;
+    Entity hit_entity;
+    float distance;  // negative when the origin is inside the hit box, as in the reference
+    bool hit;
+};
+
+enum class AABBSide { Left, Right, Bottom, Top, Front, Back };
+
+class CollisionSystem : public System {
+   public:
+    explicit CollisionSystem(Scene* scene);
+    ~CollisionSystem() override;
+
+    void onComponentInsert(Entity entity) override;
+
+    // Gathers ColliderComponent::aabb + TransformComponent::world_matrix from the ECS, uploads them and
+    // enqueues refit + LBVH build on the GPU (the reference rebuilds every frame too).
+    void onUpdate(float ts) override;
+
+    // Nearest hit, reference semantics. One ray = a batch of one (latency-bound; prefer GetRaycasts).
+    Raycast GetRaycast(Ray ray);
+    void GetRaycasts(const Ray* rays, std::size_t count, Raycast* results);
+
+    // One node of the BVH in the reference's exchange format (60 bytes, align 4).
+    struct BiTreeNode {
+        enum class Type : uint8_t { BoundingVolume, Entity, Empty };
+        AABB box1;
+        AABB box2;
+        uint32_t index1;
+        uint32_t index2;
+        Type type1;
+        Type type2;
+    };
+
+    // The debug overlay reads this member directly. It is refreshed from the GPU tree by
+    // SyncDebugBvh(), or after every onUpdate when keep_debug_bvh is set (costs a device->host copy).
+    std::vector<BiTreeNode> bvh_{};
+    bool keep_debug_bvh = false;
+    void SyncDebugBvh();
+
+   private:
+    b2col_ctx* ctx_ = nullptr;
+    std::size_t colliders_inserted_ = 0;
+    std::vector<uint32_t> gather_entities_;
+    std::vector<AABB> gather_boxes_;
+    std::vector<float> gather_world_;
+    void Check(int status, const char* what) const;
+};
+
+}  // namespace engine

@@ -19,6 +19,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "liboracle_port.so")
 REF_SO = os.path.join(HERE, "_ref", "libref_engine.so")
+# reference Scene/ECS/TransformSystem + engine_b200/shim's replacement CollisionSystem (the drop-in test)
+DROPIN_SO = os.path.join(HERE, "_ref", "libdropin_engine.so")
 
 # Layouts of the reference's PODs (include/system_collisions.h:13-24,40-48; component_collider.h:7-10)
 RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3)])
@@ -159,20 +161,20 @@ class RefEngine:
             build()
         return os.path.exists(REF_SO)
 
+    SO = REF_SO
+
     def __init__(self):
-        if not self.available():
-            raise RuntimeError("oracle/_ref/libref_engine.so not built (needs /root/reference)")
-        self.lib = C.CDLL(REF_SO)
+        if not self.available() or not os.path.exists(self.SO):
+            raise RuntimeError(f"{self.SO} not built (needs /root/reference)")
+        self.lib = C.CDLL(self.SO)
         L = self.lib
-        L.refh_create.restype = C.c_void_p
-        L.refh_sizeof.restype = C.c_size_t
-        L.refh_create_entities.restype = C.c_uint32
-        L.refh_scene_update.restype = C.c_double
-        L.refh_transform_update.restype = C.c_double
-        L.refh_refit.restype = C.c_size_t
-        L.refh_bvh_size.restype = C.c_size_t
-        L.refh_raycast.restype = C.c_double
-        L.refh_ray_box.restype = C.c_int
+        for name, rt in (("refh_create", C.c_void_p), ("refh_sizeof", C.c_size_t), ("refh_create_entities", C.c_uint32),
+                         ("refh_scene_update", C.c_double), ("refh_transform_update", C.c_double), ("refh_refit", C.c_size_t),
+                         ("refh_bvh_size", C.c_size_t), ("refh_raycast", C.c_double), ("refh_ray_box", C.c_int)):
+            try:
+                getattr(L, name).restype = rt
+            except AttributeError:  # the drop-in build has no access to the reference's file-static helpers
+                pass
         self.h = C.c_void_p(L.refh_create())
         self.n_entities = 0
 
@@ -263,4 +265,21 @@ class RefEngine:
         v = _f32(v3, (3,))
         out = np.zeros(3, np.float32)
         self.lib.refh_normalize(_p(v), _p(out))
+        return out
+
+
+class DropinEngine(RefEngine):
+    """The reference's Scene / ECS / TransformSystem with engine_b200/shim's CollisionSystem compiled in
+    place of the reference's (oracle/_ref/libdropin_engine.so, needs a GPU at run time)."""
+
+    SO = DROPIN_SO
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(DROPIN_SO)
+
+    def raycast_batch(self, rays) -> np.ndarray:
+        rays = as_rays(rays)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        self.lib.refh_raycast_batch(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(out))
         return out

@@ -10,7 +10,16 @@
 // helpers (transformBox :14, RayBoxIntersection :62) can be called directly for
 // known-answer tests and for the O(N) refit at sizes where the reference's O(N^2)
 // BuildNode (:205-376) cannot run.  No reference source is copied into this repository.
+// Built a second time with -DB2COL_DROPIN (oracle/_ref/libdropin_engine.so): the same harness and the
+// same reference Scene / ECS / TransformSystem translation units, but with engine_b200/shim's
+// replacement CollisionSystem compiled in place of the reference's — the drop-in test.
+#ifdef B2COL_DROPIN
+#include "system_collisions.h"  // engine_b200/shim precedes the reference's include directory
+#include "component_transform.h"
+#include "scene.h"
+#else
 #include "system_collisions.cpp"  // -I/root/reference/src
+#endif
 
 #include "system_transform.h"
 
@@ -45,7 +54,9 @@ size_t refh_sizeof(int which)
         case 2: return sizeof(AABB);
         case 3: return sizeof(CollisionSystem::BiTreeNode);
         case 4: return sizeof(TransformComponent);
+#ifndef B2COL_DROPIN
         case 5: return sizeof(CollisionSystem::PrimitiveInfo);
+#endif
     }
     return 0;
 }
@@ -109,6 +120,7 @@ double refh_transform_update(void* h)
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+#ifndef B2COL_DROPIN
 // The reference's refit loop (src/system_collisions.cpp:123-132) without the O(N^2) build:
 // iterates CollisionSystem::m_entities (ascending entity ID) and calls the reference's own
 // transformBox on each collider. Returns the collider count; seconds in *secs.
@@ -130,6 +142,8 @@ size_t refh_refit(void* h, uint32_t* out_entity, float* out_aabb6, double* secs)
     return i;
 }
 
+#endif  // !B2COL_DROPIN
+
 // world_matrix as 16 floats, column-major (glm memory order)
 void refh_get_world_matrices(void* h, size_t n, const uint32_t* entity, float* out16)
 {
@@ -137,10 +151,19 @@ void refh_get_world_matrices(void* h, size_t n, const uint32_t* entity, float* o
     for (size_t i = 0; i < n; ++i) std::memcpy(out16 + 16 * i, &H->scene.GetTransform(entity[i])->world_matrix, 64);
 }
 
-size_t refh_bvh_size(void* h) { return static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->bvh_.size(); }
+size_t refh_bvh_size(void* h)
+{
+#ifdef B2COL_DROPIN
+    static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->SyncDebugBvh();
+#endif
+    return static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->bvh_.size();
+}
 
 void refh_bvh_get(void* h, void* out60)
 {
+#ifdef B2COL_DROPIN
+    static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->SyncDebugBvh();
+#endif
     auto& v = static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->bvh_;
     if (!v.empty()) std::memcpy(out60, v.data(), v.size() * sizeof(CollisionSystem::BiTreeNode));
 }
@@ -187,6 +210,7 @@ double refh_raycast(void* h, size_t n, const void* rays24, void* out36, int nthr
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+#ifndef B2COL_DROPIN
 // Direct known-answer access to the file-static helpers.
 // RayBoxIntersection (src/system_collisions.cpp:62-100); direction is used as given (NOT normalised).
 int refh_ray_box(const float* ray6, const float* aabb6, float T, float* t_out, int* side_out)
@@ -219,6 +243,16 @@ void refh_normalize(const float* v3, float* out3)
     const glm::vec3 v = glm::normalize(glm::vec3{v3[0], v3[1], v3[2]});
     std::memcpy(out3, &v, 12);
 }
+
+#endif  // !B2COL_DROPIN
+
+// batch entry of the drop-in class (additive API); the reference has none
+#ifdef B2COL_DROPIN
+void refh_raycast_batch(void* h, size_t n, const void* rays24, void* out36)
+{
+    static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->GetRaycasts(static_cast<const Ray*>(rays24), n, static_cast<Raycast*>(out36));
+}
+#endif
 
 int refh_hw_threads() { return static_cast<int>(std::thread::hardware_concurrency()); }
 

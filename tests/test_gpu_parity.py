@@ -10,7 +10,7 @@ import torch
 from conftest import SCENE_FIXTURES, assert_raycast_equal, load_golden
 from emu_loader import Emu
 from engine_b200 import capi, synth
-from oracle.oracle import RefEngine
+from oracle.oracle import DropinEngine, RefEngine
 
 pytestmark = pytest.mark.gpu
 
@@ -287,3 +287,40 @@ def test_device_resident_and_replicated_tree(CollisionSystem):
     assert (replica.get_raycasts(rays).view(np.uint8) == want.view(np.uint8)).all()
     st0, st1 = cs.stats(), replica.stats()
     assert st0["kernel_launches"] > 0 and st1["kernel_launches"] > 0
+
+
+@pytest.mark.skipif(not (DropinEngine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_dropin_shim_inside_reference_scene(port):
+    """The reference's own Scene::Update loop and GetSystem<CollisionSystem>()->GetRaycast(), once with the
+    reference's CollisionSystem and once with engine_b200/shim's replacement compiled in its place."""
+    s = synth.game_scene(800)
+    rays = np.concatenate([synth.game_rays(40), synth.random_rays(3000, seed=95, extent=120, normalised=False)])
+    engines = []
+    for cls in (RefEngine, DropinEngine):
+        e = cls()
+        e.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+        e.add_colliders(s.collider_entity, s.collider_aabb)
+        pre = e.raycast(rays[:64])  # frame 0: bvh_ empty, every query misses
+        assert not pre.view(np.uint8).any()
+        e.scene_update()
+        engines.append(e)
+    ref, drop = engines
+    want = ref.raycast(rays)
+    got_single = drop.raycast(rays)        # GetRaycast, one ray per call, as game code issues them
+    got_batch = drop.raycast_batch(rays)   # additive batch entry
+    assert (got_single.view(np.uint8) == got_batch.view(np.uint8)).all()
+    # the shim's public bvh_ (debug overlay) walked by the reference traversal gives the same answers incl. ties
+    exported = drop.bvh()
+    assert_raycast_equal(got_batch, port.raycast_tree(exported, rays), "shim vs reference traversal of shim.bvh_")
+    ent, box = port.tree_leaves_dfs(exported)
+    _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
+    assert_raycast_equal(got_batch, want, "shim vs reference CollisionSystem", ignore_entity_on=ties > 0)
+    # second frame after moving things
+    s.pos[1:20] += 1.5
+    for e in engines:
+        e.set_trs(np.arange(1, s.n_entities + 1, dtype=np.uint32), s.pos[1:], s.rot[1:], s.scl[1:])
+        e.scene_update()
+    exported = drop.bvh()
+    ent, box = port.tree_leaves_dfs(exported)
+    _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
+    assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), "frame 2", ignore_entity_on=ties > 0)
