@@ -241,20 +241,11 @@ def run_ours(args):
                    "achieved_gbs": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak,
                    "what": "propagate + refit + Morton + 6-pass radix sort + hierarchy/bounds, device-resident TRS, back-to-back on one stream"}
     if world > 1:
-        nbytes = torch.zeros(1, dtype=torch.int64, device="cuda")
-        if rank == 0:
-            nbytes[0] = cs.bvh_blob()[1]
-        dist.broadcast(nbytes, 0)
-        blob = torch.empty(int(nbytes.item()), dtype=torch.uint8, device="cuda")
+        from engine_b200 import dist as b2dist
+
         barrier()
         t0 = time.perf_counter()
-        if rank == 0:
-            cs.bvh_export_blob(blob, blob.numel())
-            cs.sync()
-        dist.broadcast(blob, 0)
-        if rank != 0:
-            cs.bvh_import_blob(blob, blob.numel())
-            cs.sync()
+        b2dist.replicate_bvh(cs, src=0)  # one NCCL broadcast of the BVH blob over NVLink
         barrier()
         bcast_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
 

@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb2col.so")
+LIB_PATH = os.environ.get("B2COL_LIB") or os.path.join(HERE, "libb2col.so")  # B2COL_LIB: dev override (kernel variants)
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_OVERFLOW = range(7)
 MODE_LBVH, MODE_REFTOPO = 0, 1

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -229,22 +230,116 @@ __device__ __forceinline__ RayPre load_ray(const b2col_ray* rays, size_t i)
     return ray_prepare(o, d);
 }
 
-// GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
-__global__ void __launch_bounds__(128)
-k_trace_lbvh(const b2col_ray* __restrict__ rays, size_t n_rays, b2col_raycast* __restrict__ out, const BlobHeader* __restrict__ hdr,
-             const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity, float T)
+// One traversal node = two 32-byte slots, fetched with two 256-bit read-only loads (sm_100a
+// LDG.E.ENL2.256): half the L1 wavefronts of four LDG.128 for the same bytes.
+__device__ __forceinline__ Slot load_slot256(const Slot* p)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_rays) return;
-    const RayPre r = load_ray(rays, i);
-    uint32_t* o9 = reinterpret_cast<uint32_t*>(out + i);
-    if (hdr->n_leaves == 0u) {  // empty tree: value-initialised Raycast (:164-167)
-        write_raycast(o9, r, false, 0.0f, 0, 0u);
-        return;
+    Slot s;
+    float f6, f7;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(s.lo[0]), "=f"(s.lo[1]), "=f"(s.lo[2]), "=f"(s.hi[0]), "=f"(s.hi[1]), "=f"(s.hi[2]), "=f"(f6), "=f"(f7)
+                 : "l"(p));
+    s.ref = __float_as_uint(f6);
+    s.aux = __float_as_uint(f7);
+    return s;
+}
+
+constexpr int TRACE_BLOCK = 128;
+#ifndef B2_SMEM_STACK
+#define B2_SMEM_STACK 12
+#endif
+constexpr int TRACE_SMEM_STACK = B2_SMEM_STACK;  // entries per thread held in shared memory
+
+// Deferred-children stack of one lane: the first TRACE_SMEM_STACK entries live in shared memory,
+// laid out [entry][thread] so that lane l always hits bank l whatever its depth (conflict-free: one
+// wavefront per warp access, where a local-memory stack costs one wavefront per distinct depth);
+// deeper entries (rare) overflow to local memory.
+struct DevStack {
+    uint32_t* s_node;  // this thread's column
+    float* s_t;
+    uint32_t l_node[LBVH_STACK - TRACE_SMEM_STACK];
+    float l_t[LBVH_STACK - TRACE_SMEM_STACK];
+    __device__ __forceinline__ void put(int i, uint32_t n, float t)
+    {
+        if (i < TRACE_SMEM_STACK) {
+            s_node[i * TRACE_BLOCK] = n;
+            s_t[i * TRACE_BLOCK] = t;
+        }
+        else {
+            l_node[i - TRACE_SMEM_STACK] = n;
+            l_t[i - TRACE_SMEM_STACK] = t;
+        }
     }
-    const Hit h = trace_lbvh<DevOps>(r, nodes, hdr->root, T);
-    const bool hit = h.leaf >= 0;
-    write_raycast(o9, r, hit, h.t, h.side, hit ? __ldg(leaf_entity + h.leaf) : 0u);
+    __device__ __forceinline__ float get_t(int i) const { return i < TRACE_SMEM_STACK ? s_t[i * TRACE_BLOCK] : l_t[i - TRACE_SMEM_STACK]; }
+    __device__ __forceinline__ uint32_t get_node(int i) const { return i < TRACE_SMEM_STACK ? s_node[i * TRACE_BLOCK] : l_node[i - TRACE_SMEM_STACK]; }
+};
+
+// GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
+// Persistent warps with dynamic ray fetch: incoherent rays finish after wildly different numbers of
+// node visits, so a lane whose ray is done does not idle until the slowest ray of its warp ends —
+// when fewer than `fetch_threshold` lanes are still busy the warp claims new rays for its idle lanes
+// from a global counter (one atomicAdd per warp) and carries on.  Per-lane traversal state lives in
+// registers + a local-memory stack across fetches.
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
+             const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity, float T,
+             unsigned long long* counter, int fetch_threshold)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t root = hdr->root;
+    __shared__ uint32_t sm_node[TRACE_SMEM_STACK * TRACE_BLOCK];
+    __shared__ float sm_t[TRACE_SMEM_STACK * TRACE_BLOCK];
+    TraceState st;
+    DevStack stk;
+    stk.s_node = sm_node + threadIdx.x;
+    stk.s_t = sm_t + threadIdx.x;
+    RayPre r;
+    unsigned long long my = 0ull;
+    bool active = false;
+    bool exhausted = false;  // warp-uniform: the pool has no rays left
+    for (;;) {
+        const unsigned need = __ballot_sync(0xffffffffu, !active);
+        if (need != 0u && !exhausted) {
+            const int leader = __ffs(need) - 1;
+            const unsigned long long cnt = (unsigned long long)__popc(need);
+            unsigned long long base = 0ull;
+            if (lane == leader) base = atomicAdd(counter, cnt);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active) {
+                my = base + (unsigned long long)__popc(need & lt_mask);
+                if (my < n_rays) {
+                    r = load_ray(rays, my);
+                    trace_begin(st, root);
+                    active = true;
+                }
+            }
+            exhausted = base + cnt >= n_rays;
+        }
+        const unsigned busy = __ballot_sync(0xffffffffu, active);
+        if (busy == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        const int keep_going = exhausted ? 1 : fetch_threshold;
+        for (;;) {
+            if (active) {
+#if defined(B2_NODE_LOAD_128)
+                const Slot a = DevOps::load_slot(&nodes[st.cur].s[0]);
+                const Slot b = DevOps::load_slot(&nodes[st.cur].s[1]);
+#else
+                const Slot a = load_slot256(&nodes[st.cur].s[0]);
+                const Slot b = load_slot256(&nodes[st.cur].s[1]);
+#endif
+                if (!trace_visit(st, stk, r, a, b, T)) {
+                    const bool hit = st.best.leaf >= 0;
+                    write_raycast(reinterpret_cast<uint32_t*>(out + my), r, hit, st.best.t, st.best.side, hit ? __ldg(leaf_entity + st.best.leaf) : 0u);
+                    active = false;
+                }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, active)) < keep_going) break;
+        }
+    }
 }
 
 // Same query, walking an uploaded reference-format tree with the reference's exact semantics.
@@ -317,7 +412,8 @@ struct b2col_ctx {
     DevBuf d_ref_nodes, d_flag;
     uint32_t n_ref_nodes = 0;
     // staging for host-buffer queries
-    DevBuf d_rays, d_hits;
+    DevBuf d_rays, d_hits, d_counter;
+    int trace_grid = 148 * 8, fetch_threshold = 20;
     cudaEvent_t events[16] = {};
 };
 
@@ -403,7 +499,15 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
             CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
             return B2COL_OK;
         }
-        LAUNCH(ctx, k_trace_lbvh, cdiv(n, 128), 128, d_rays, n, d_out, blob_hdr(ctx), blob_nodes(ctx), blob_leaf_entity(ctx, ctx->tree_leaves), ctx->T);
+        if (ctx->tree_leaves == 0) {  // empty tree: value-initialised Raycast (:164-167)
+            CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
+            return B2COL_OK;
+        }
+        GUARD(ensure(ctx, ctx->d_counter, 8));
+        CU(cudaMemsetAsync(ctx->d_counter.p, 0, 8, ctx->stream));
+        const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        LAUNCH(ctx, k_trace_lbvh, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_nodes(ctx),
+               blob_leaf_entity(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
     }
     else if (mode == B2COL_MODE_REFTOPO) {
         GUARD(ensure(ctx, ctx->d_flag, 4));
@@ -455,6 +559,14 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         return fail(nullptr, B2COL_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
     }
     for (auto& ev : c->events) cudaEventCreate(&ev);
+    {   // persistent trace kernel: one resident wave of blocks
+        int sms = 148, per_sm = 8;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
+        if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
+        if (const char* e = getenv("B2COL_TRACE_FETCH_THRESHOLD")) c->fetch_threshold = std::min(32, std::max(1, atoi(e)));
+        c->trace_grid = sms * per_sm;
+    }
     *out = c;
     return B2COL_OK;
 }
@@ -466,7 +578,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits})
+                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);

@@ -229,72 +229,99 @@ struct Hit {
     int side;
 };
 
+// Traversal state of one ray, advanced one node visit at a time so that a persistent warp can
+// retire finished rays and fetch new ones between steps (k_trace_lbvh in b2col.cu).  The stack of
+// deferred far children (node, entry tmin) is a policy: a plain array on the host, shared memory
+// with a local-memory overflow on the device.
+struct TraceState {
+    uint32_t cur;
+    int sp;
+    Hit best;
+};
+
+struct ArrayStack {
+    uint32_t node[LBVH_STACK];
+    float t[LBVH_STACK];
+    B2_HD void put(int i, uint32_t n, float tt)
+    {
+        node[i] = n;
+        t[i] = tt;
+    }
+    B2_HD float get_t(int i) const { return t[i]; }
+    B2_HD uint32_t get_node(int i) const { return node[i]; }
+};
+
+B2_HD void trace_begin(TraceState& st, uint32_t root)
+{
+    st.cur = root;
+    st.sp = 0;
+    st.best.t = B2_INF;
+    st.best.leaf = -1;
+    st.best.side = SIDE_LEFT;
+}
+
+B2_HD void leaf_candidate(Hit& best, const SlabT& s, uint32_t ref)
+{
+    const int32_t leaf = (int32_t)(ref & ~LEAF_BIT);
+    if (s.tmin < best.t || (s.tmin == best.t && leaf > best.leaf)) {
+        best.t = s.tmin;
+        best.leaf = leaf;
+        best.side = slab_side(s);
+    }
+}
+
+// Visit node st.cur (its two slots are passed in), then select the next node. Returns false when the
+// traversal of this ray is complete.
+template <class Stack>
+B2_HD bool trace_visit(TraceState& st, Stack& stk, const RayPre& r, const Slot& a, const Slot& b, float T)
+{
+    const SlabT sa = slab(r, a.lo, a.hi);
+    const SlabT sb = slab(r, b.lo, b.hi);
+    bool ha = slab_hit(sa, T);
+    bool hb = slab_hit(sb, T);
+    if (ha && (a.ref & LEAF_BIT)) {
+        leaf_candidate(st.best, sa, a.ref);
+        ha = false;
+    }
+    if (hb && (b.ref & LEAF_BIT)) {
+        leaf_candidate(st.best, sb, b.ref);
+        hb = false;
+    }
+    ha = ha && (sa.tmin <= st.best.t);
+    hb = hb && (sb.tmin <= st.best.t);
+    if (ha && hb) {
+        const bool a_first = !(sb.tmin < sa.tmin);
+        stk.put(st.sp, a_first ? b.ref : a.ref, a_first ? sb.tmin : sa.tmin);
+        ++st.sp;
+        st.cur = a_first ? a.ref : b.ref;
+        return true;
+    }
+    if (ha || hb) {
+        st.cur = ha ? a.ref : b.ref;
+        return true;
+    }
+    while (st.sp > 0) {
+        --st.sp;
+        if (stk.get_t(st.sp) <= st.best.t) {
+            st.cur = stk.get_node(st.sp);
+            return true;
+        }
+    }
+    return false;
+}
+
 template <class Ops>
 B2_HD Hit trace_lbvh(const RayPre& r, const Node* nodes, uint32_t root, float T)
 {
-    Hit best;
-    best.t = B2_INF;
-    best.leaf = -1;
-    best.side = SIDE_LEFT;
-    uint32_t stack_node[LBVH_STACK];
-    float stack_t[LBVH_STACK];
-    int sp = 0;
-    uint32_t cur = root;
+    TraceState st;
+    ArrayStack stk;
+    trace_begin(st, root);
     for (;;) {
-        const Slot a = Ops::load_slot(&nodes[cur].s[0]);
-        const Slot b = Ops::load_slot(&nodes[cur].s[1]);
-        const SlabT sa = slab(r, a.lo, a.hi);
-        const SlabT sb = slab(r, b.lo, b.hi);
-        bool ha = slab_hit(sa, T);
-        bool hb = slab_hit(sb, T);
-        if (ha && (a.ref & LEAF_BIT)) {
-            const int32_t leaf = (int32_t)(a.ref & ~LEAF_BIT);
-            if (sa.tmin < best.t || (sa.tmin == best.t && leaf > best.leaf)) {
-                best.t = sa.tmin;
-                best.leaf = leaf;
-                best.side = slab_side(sa);
-            }
-            ha = false;
-        }
-        if (hb && (b.ref & LEAF_BIT)) {
-            const int32_t leaf = (int32_t)(b.ref & ~LEAF_BIT);
-            if (sb.tmin < best.t || (sb.tmin == best.t && leaf > best.leaf)) {
-                best.t = sb.tmin;
-                best.leaf = leaf;
-                best.side = slab_side(sb);
-            }
-            hb = false;
-        }
-        ha = ha && (sa.tmin <= best.t);
-        hb = hb && (sb.tmin <= best.t);
-        if (ha && hb) {
-            const bool a_first = !(sb.tmin < sa.tmin);
-            stack_node[sp] = a_first ? b.ref : a.ref;
-            stack_t[sp] = a_first ? sb.tmin : sa.tmin;
-            ++sp;
-            cur = a_first ? a.ref : b.ref;
-            continue;
-        }
-        if (ha) {
-            cur = a.ref;
-            continue;
-        }
-        if (hb) {
-            cur = b.ref;
-            continue;
-        }
-        bool found = false;
-        while (sp > 0) {
-            --sp;
-            if (stack_t[sp] <= best.t) {
-                cur = stack_node[sp];
-                found = true;
-                break;
-            }
-        }
-        if (!found) break;
+        const Slot a = Ops::load_slot(&nodes[st.cur].s[0]);
+        const Slot b = Ops::load_slot(&nodes[st.cur].s[1]);
+        if (!trace_visit(st, stk, r, a, b, T)) break;
     }
-    return best;
+    return st.best;
 }
 
 // ---- reference-topology traversal ---------------------------------------------------------------

@@ -141,3 +141,41 @@ size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const uint32_t* 
 }
 
 }  // extern "C"
+
+// Instrumentation (dev): node visits per tree depth, and visits in total, for a ray sample.
+extern "C" void emu_visit_histogram(const Node* nodes, uint32_t root, const float* rays6, size_t n_rays, float T, uint64_t* hist, int max_depth,
+                                    uint64_t* total_visits, uint64_t* leaf_tests)
+{
+    std::vector<uint32_t> sn(256);
+    std::vector<float> stt(256);
+    std::vector<int> sd(256);
+    for (size_t i = 0; i < n_rays; ++i) {
+        const RayPre r = ray_prepare(rays6 + 6 * i, rays6 + 6 * i + 3);
+        Hit best;
+        best.t = INFINITY;
+        best.leaf = -1;
+        best.side = 0;
+        int sp = 0, depth = 0;
+        uint32_t cur = root;
+        for (;;) {
+            ++*total_visits;
+            ++hist[depth < max_depth ? depth : max_depth - 1];
+            const Slot a = nodes[cur].s[0], b = nodes[cur].s[1];
+            const SlabT sa = slab(r, a.lo, a.hi), sb = slab(r, b.lo, b.hi);
+            bool ha = slab_hit(sa, T), hb = slab_hit(sb, T);
+            if (ha && (a.ref & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, sa, a.ref); ha = false; }
+            if (hb && (b.ref & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, sb, b.ref); hb = false; }
+            ha = ha && sa.tmin <= best.t;
+            hb = hb && sb.tmin <= best.t;
+            if (ha && hb) {
+                const bool af = !(sb.tmin < sa.tmin);
+                sn[sp] = af ? b.ref : a.ref; stt[sp] = af ? sb.tmin : sa.tmin; sd[sp] = depth + 1; ++sp;
+                cur = af ? a.ref : b.ref; ++depth; continue;
+            }
+            if (ha || hb) { cur = ha ? a.ref : b.ref; ++depth; continue; }
+            bool found = false;
+            while (sp > 0) { --sp; if (stt[sp] <= best.t) { cur = sn[sp]; depth = sd[sp]; found = true; break; } }
+            if (!found) break;
+        }
+    }
+}
