@@ -53,6 +53,37 @@ struct DevOps {
     }
     static __device__ __forceinline__ void fence() { __threadfence(); }
     static __device__ __forceinline__ uint32_t exch(uint32_t* p, uint32_t v) { return atomicExch(p, v); }
+    // 32-byte records move as two 16-byte vectors on the store side and as ONE 256-bit read-only load
+    // (sm_100a LDG.E.ENL2.256) on the traversal side: one L1 wavefront per lane per record.
+    static __device__ __forceinline__ void store_qnode(QNode* p, const QNode& n)
+    {
+        uint4* q = reinterpret_cast<uint4*>(p);
+        q[0] = make_uint4(n.w[0], n.w[1], n.w[2], n.w[3]);
+        q[1] = make_uint4(n.w[4], n.w[5], n.w[6], n.w[7]);
+    }
+    static __device__ __forceinline__ void store_leaf(LeafRec* p, const LeafRec& r)
+    {
+        float4* q = reinterpret_cast<float4*>(p);
+        q[0] = make_float4(r.lo[0], r.lo[1], r.lo[2], r.hi[0]);
+        q[1] = make_float4(r.hi[1], r.hi[2], __uint_as_float(r.entity), __uint_as_float(r.prim));
+    }
+    static __device__ __forceinline__ QNode load_qnode(const QNode* p)
+    {
+        QNode n;
+        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(n.w[0]), "=r"(n.w[1]), "=r"(n.w[2]), "=r"(n.w[3]), "=r"(n.w[4]), "=r"(n.w[5]), "=r"(n.w[6]), "=r"(n.w[7])
+                     : "l"(p));
+        return n;
+    }
+    static __device__ __forceinline__ LeafRec load_leaf(const LeafRec* p)
+    {
+        LeafRec r;
+        asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(r.lo[0]), "=f"(r.lo[1]), "=f"(r.lo[2]), "=f"(r.hi[0]), "=f"(r.hi[1]), "=f"(r.hi[2]), "=f"(*reinterpret_cast<float*>(&r.entity)),
+                       "=f"(*reinterpret_cast<float*>(&r.prim))
+                     : "l"(p));
+        return r;
+    }
 };
 
 // Contents of the first 256 bytes of the BVH blob (device memory).
@@ -60,7 +91,10 @@ struct BlobHeader {
     uint32_t magic, n_leaves, n_nodes, root;
     uint32_t bounds_min_inv[3];  // ~ordered(min centroid): zero-initialised, raised with atomicMax
     uint32_t bounds_max[3];      //  ordered(max centroid)
-    uint32_t reserved[54];
+    uint32_t box_min_inv[3];     // ~ordered(min finite box coordinate)
+    uint32_t box_max[3];         //  ordered(max finite box coordinate)
+    Grid grid;                   // quantisation grid of the traversal nodes (written by k_morton)
+    uint32_t reserved[39];
 };
 static_assert(sizeof(BlobHeader) == 256, "blob header");
 constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
@@ -112,7 +146,8 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
         Aabb24* __restrict__ world_aabb, BlobHeader* hdr)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    float cmin[3] = {B2_INF, B2_INF, B2_INF}, cmax[3] = {-B2_INF, -B2_INF, -B2_INF};
+    // [0..2] centroid bounds (Morton grid), [3..5] bounds of all finite box coordinates (node quantisation grid)
+    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
     if (i < n) {
         const uint32_t e = __ldg(col_entity + i);
         float M[16];
@@ -137,37 +172,48 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
                 cmin[k] = c;
                 cmax[k] = c;
             }
+            if (isfinite(b.lo[k])) {
+                cmin[3 + k] = b.lo[k];
+                cmax[3 + k] = b.lo[k];
+            }
+            if (isfinite(b.hi[k])) {
+                cmin[3 + k] = fminf(cmin[3 + k], b.hi[k]);
+                cmax[3 + k] = fmaxf(cmax[3 + k], b.hi[k]);
+            }
         }
     }
     // block reduction: warp shuffles, then one atomic per warp and axis
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
+    for (int k = 0; k < 6; ++k) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             cmin[k] = fminf(cmin[k], __shfl_xor_sync(0xffffffffu, cmin[k], o));
             cmax[k] = fmaxf(cmax[k], __shfl_xor_sync(0xffffffffu, cmax[k], o));
         }
     }
-    __shared__ float smin[8][3], smax[8][3];
+    __shared__ float smin[8][6], smax[8][6];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
+        for (int k = 0; k < 6; ++k) {
             smin[warp][k] = cmin[k];
             smax[warp][k] = cmax[k];
         }
     }
     __syncthreads();
-    if (threadIdx.x < 3) {
+    if (threadIdx.x < 6) {
         const int k = threadIdx.x;
         float a = smin[0][k], b = smax[0][k];
         for (int w = 1; w < 8; ++w) {
             a = fminf(a, smin[w][k]);
             b = fmaxf(b, smax[w][k]);
         }
-        if (a <= b) {  // false when the block saw no finite centroid
-            atomicMax(&hdr->bounds_min_inv[k], ~float_to_ordered(a));
-            atomicMax(&hdr->bounds_max[k], float_to_ordered(b));
+        if (a <= b) {  // false when the block saw no finite value
+            // bounds_min_inv/bounds_max and box_min_inv/box_max are laid out as two consecutive groups of 3+3 words
+            uint32_t* mn = k < 3 ? &hdr->bounds_min_inv[k] : &hdr->box_min_inv[k - 3];
+            uint32_t* mx = k < 3 ? &hdr->bounds_max[k] : &hdr->box_max[k - 3];
+            atomicMax(mn, ~float_to_ordered(a));
+            atomicMax(mx, float_to_ordered(b));
         }
     }
 }
@@ -175,7 +221,7 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway), and reset of the per-node arrival words used by k_build.
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int passes, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* __restrict__ other_bound, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
@@ -210,38 +256,34 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
         hdr->magic = BLOB_MAGIC;
         hdr->n_leaves = n;
         hdr->n_nodes = n > 1u ? n - 1u : 1u;
+        float bmin[3], bmax[3];
+        for (int k = 0; k < 3; ++k) {
+            bmin[k] = ordered_to_float(~hdr->box_min_inv[k]);
+            bmax[k] = ordered_to_float(hdr->box_max[k]);
+        }
+        hdr->grid = make_grid(bmin, bmax, T);
     }
 }
 
 __global__ void __launch_bounds__(256)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
-        const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, uint32_t* leaf_entity, BlobHeader* hdr)
+        const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    build_from_leaf<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, nodes, other_bound, leaf_entity, &hdr->root);
+    const Grid grid = hdr->grid;  // written by k_morton
+    build_from_leaf<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, nodes, other_bound, grid, qnodes, leaves, &hdr->root);
 }
 
-__device__ __forceinline__ RayPre load_ray(const b2col_ray* rays, size_t i)
+// Ray prologue (GetRaycast :162 + the hoisted reciprocals of :65).  Deliberately NOT inlined: it runs
+// three times per ray against ~100 node visits, and keeping its IEEE division / square-root sequences
+// (the only FFMA-containing code on this path) out of the traversal loop saves registers there.
+__device__ __noinline__ RayPre load_ray(const b2col_ray* rays, size_t i)
 {
     const float2* rp = reinterpret_cast<const float2*>(rays + i);  // 24-byte records are 8-byte aligned
     const float2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
     const float o[3] = {a.x, a.y, b.x}, d[3] = {b.y, c.x, c.y};
     return ray_prepare(o, d);
-}
-
-// One traversal node = two 32-byte slots, fetched with two 256-bit read-only loads (sm_100a
-// LDG.E.ENL2.256): half the L1 wavefronts of four LDG.128 for the same bytes.
-__device__ __forceinline__ Slot load_slot256(const Slot* p)
-{
-    Slot s;
-    float f6, f7;
-    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(s.lo[0]), "=f"(s.lo[1]), "=f"(s.lo[2]), "=f"(s.hi[0]), "=f"(s.hi[1]), "=f"(s.hi[2]), "=f"(f6), "=f"(f7)
-                 : "l"(p));
-    s.ref = __float_as_uint(f6);
-    s.aux = __float_as_uint(f7);
-    return s;
 }
 
 constexpr int TRACE_BLOCK = 128;
@@ -275,30 +317,47 @@ struct DevStack {
 };
 
 // GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
+//
 // Persistent warps with dynamic ray fetch: incoherent rays finish after wildly different numbers of
 // node visits, so a lane whose ray is done does not idle until the slowest ray of its warp ends —
 // when fewer than `fetch_threshold` lanes are still busy the warp claims new rays for its idle lanes
-// from a global counter (one atomicAdd per warp) and carries on.  Per-lane traversal state lives in
-// registers + a local-memory stack across fetches.
-__global__ void __launch_bounds__(TRACE_BLOCK)
+// from a global counter (one atomicAdd per warp) and carries on.
+//
+// Per-lane state is kept small so that many warps fit: the grid-space ray (6 floats), node, stack
+// pointer, best (t, leaf).  The exact ray (origin, normalised direction, reciprocals) is NOT kept in
+// registers: it is re-derived from the ray record (an L1/L2 hit) on the rare occasions it is needed
+// — when a leaf slot passes the grid test (about once per ray) and in the epilogue — which is
+// bit-identical because it is a pure function of the record.
+#ifndef B2_TRACE_MIN_BLOCKS
+#define B2_TRACE_MIN_BLOCKS 10
+#endif
+__global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
 k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
-             const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity, float T,
+             const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
              unsigned long long* counter, int fetch_threshold)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t root = hdr->root;
+    const Grid grid = hdr->grid;
     __shared__ uint32_t sm_node[TRACE_SMEM_STACK * TRACE_BLOCK];
     __shared__ float sm_t[TRACE_SMEM_STACK * TRACE_BLOCK];
     TraceState st;
     DevStack stk;
     stk.s_node = sm_node + threadIdx.x;
     stk.s_t = sm_t + threadIdx.x;
-    RayPre r;
+    RayQ q;
     unsigned long long my = 0ull;
     bool active = false;
+    bool pending = false;    // this lane's ray is finished but its Raycast is not written yet
     bool exhausted = false;  // warp-uniform: the pool has no rays left
     for (;;) {
+        // Epilogues are deferred to this point so that the lanes that finished since the last fetch
+        // run them together instead of one at a time inside the traversal loop.
+        if (pending) {
+            finish_raycast<DevOps>(reinterpret_cast<uint32_t*>(out + my), load_ray(rays, my), st.best, leaves);
+            pending = false;
+        }
         const unsigned need = __ballot_sync(0xffffffffu, !active);
         if (need != 0u && !exhausted) {
             const int leader = __ffs(need) - 1;
@@ -309,9 +368,10 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
             if (!active) {
                 my = base + (unsigned long long)__popc(need & lt_mask);
                 if (my < n_rays) {
-                    r = load_ray(rays, my);
+                    const RayPre r = load_ray(rays, my);
                     trace_begin(st, root);
-                    active = true;
+                    if (rayq_prepare(r, grid, q)) active = true;
+                    else write_raycast(reinterpret_cast<uint32_t*>(out + my), r, false, 0.0f, 0, 0u);  // provable miss
                 }
             }
             exhausted = base + cnt >= n_rays;
@@ -324,17 +384,10 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
         const int keep_going = exhausted ? 1 : fetch_threshold;
         for (;;) {
             if (active) {
-#if defined(B2_NODE_LOAD_128)
-                const Slot a = DevOps::load_slot(&nodes[st.cur].s[0]);
-                const Slot b = DevOps::load_slot(&nodes[st.cur].s[1]);
-#else
-                const Slot a = load_slot256(&nodes[st.cur].s[0]);
-                const Slot b = load_slot256(&nodes[st.cur].s[1]);
-#endif
-                if (!trace_visit(st, stk, r, a, b, T)) {
-                    const bool hit = st.best.leaf >= 0;
-                    write_raycast(reinterpret_cast<uint32_t*>(out + my), r, hit, st.best.t, st.best.side, hit ? __ldg(leaf_entity + st.best.leaf) : 0u);
+                const QNode nd = DevOps::load_qnode(&qnodes[st.cur]);
+                if (!trace_visit<DevOps>(st, stk, q, nd, leaves, T, [&]() { return load_ray(rays, my); })) {
                     active = false;
+                    pending = true;
                 }
             }
             if (__popc(__ballot_sync(0xffffffffu, active)) < keep_going) break;
@@ -356,12 +409,12 @@ k_trace_reftopo(const b2col_ray* __restrict__ rays, size_t n_rays, b2col_raycast
 }
 
 __global__ void __launch_bounds__(256)
-k_export(uint32_t n, const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const uint32_t* __restrict__ leaf_entity,
-         const Aabb24* __restrict__ world_aabb, const uint32_t* __restrict__ sorted_prim, BiTreeNode60* out, uint8_t* used)
+k_export(uint32_t n, const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const LeafRec* __restrict__ leaves, BiTreeNode60* out,
+         uint8_t* used)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) export_wrapper(i, world_aabb, sorted_prim, leaf_entity, out);
-    if (i + 1u < n) export_internal(i, n, hdr->root, nodes, leaf_entity, out, used);
+    if (i < n) export_wrapper(i, leaves, out);
+    if (i + 1u < n) export_internal(i, n, hdr->root, nodes, leaves, out, used);
 }
 
 // =================================================================================================
@@ -401,9 +454,10 @@ struct b2col_ctx {
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
     DevBuf d_keys[2], d_vals[2], d_other_bound, d_zero;  // d_zero: histograms, tickets, look-back words
+    DevBuf d_nodes_full;  // full-precision two-slot nodes: sibling exchange during the build, source of the BiTreeNode export
     size_t zero_bytes = 0;
     int sorted_side = 0;
-    // traversal structure: one allocation [BlobHeader | nodes | leaf_entity]
+    // traversal structure: one allocation [BlobHeader | QNode x (N-1) | LeafRec x N]
     DevBuf d_blob;
     size_t blob_bytes = 0;
     uint32_t tree_leaves = 0;  // leaves of the tree currently in the blob
@@ -413,7 +467,7 @@ struct b2col_ctx {
     uint32_t n_ref_nodes = 0;
     // staging for host-buffer queries
     DevBuf d_rays, d_hits, d_counter;
-    int trace_grid = 148 * 8, fetch_threshold = 20;
+    int trace_grid = 148 * 8, fetch_threshold = 24;
     cudaEvent_t events[16] = {};
 };
 
@@ -473,15 +527,14 @@ inline uint32_t cdiv(size_t a, size_t b) { return (uint32_t)((a + b - 1) / b); }
 size_t blob_size_for(uint32_t n_leaves)
 {
     const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
-    size_t leaf_bytes = ((size_t)n_leaves * 4 + 63) & ~(size_t)63;
-    return sizeof(BlobHeader) + n_nodes * sizeof(Node) + leaf_bytes;
+    return sizeof(BlobHeader) + n_nodes * sizeof(QNode) + (size_t)n_leaves * sizeof(LeafRec);
 }
 inline BlobHeader* blob_hdr(const b2col_ctx* c) { return c->d_blob.as<BlobHeader>(); }
-inline Node* blob_nodes(const b2col_ctx* c) { return reinterpret_cast<Node*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader)); }
-inline uint32_t* blob_leaf_entity(const b2col_ctx* c, uint32_t n_leaves)
+inline QNode* blob_qnodes(const b2col_ctx* c) { return reinterpret_cast<QNode*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader)); }
+inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
 {
     const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
-    return reinterpret_cast<uint32_t*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader) + n_nodes * sizeof(Node));
+    return reinterpret_cast<LeafRec*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader) + n_nodes * sizeof(QNode));
 }
 
 #define GUARD(st_expr)                      \
@@ -506,8 +559,8 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
         GUARD(ensure(ctx, ctx->d_counter, 8));
         CU(cudaMemsetAsync(ctx->d_counter.p, 0, 8, ctx->stream));
         const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-        LAUNCH(ctx, k_trace_lbvh, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_nodes(ctx),
-               blob_leaf_entity(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+        LAUNCH(ctx, k_trace_lbvh, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+               blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
     }
     else if (mode == B2COL_MODE_REFTOPO) {
         GUARD(ensure(ctx, ctx->d_flag, 4));
@@ -578,7 +631,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
+                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
@@ -739,6 +792,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_other_bound, (size_t)n * 4));
+    GUARD(ensure(ctx, ctx->d_nodes_full, (size_t)(n > 1 ? n - 1 : 1) * sizeof(Node)));
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t hist_bytes = (size_t)RS_MAX_PASSES * RS_RADIX * 4;
     const size_t ticket_bytes = 64;
@@ -757,7 +811,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     // ---- a4: LBVH build -------------------------------------------------------------------------
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->passes, ctx->d_keys[0].as<uint64_t>(),
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->passes, ctx->T, ctx->d_keys[0].as<uint64_t>(),
                ctx->d_vals[0].as<uint32_t>(), ctx->d_other_bound.as<uint32_t>(), ghist);
     }
     int side = 0;
@@ -769,7 +823,8 @@ b2col_status b2col_update(b2col_ctx* ctx)
     }
     ctx->sorted_side = side;
     LAUNCH(ctx, k_build, cdiv(n, 256), 256, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
-           ctx->d_col_entity.as<uint32_t>(), blob_nodes(ctx), ctx->d_other_bound.as<uint32_t>(), blob_leaf_entity(ctx, n), blob_hdr(ctx));
+           ctx->d_col_entity.as<uint32_t>(), ctx->d_nodes_full.as<Node>(), ctx->d_other_bound.as<uint32_t>(), blob_qnodes(ctx), blob_leaves(ctx, n),
+           blob_hdr(ctx));
     ctx->have_tree = true;
     return B2COL_OK;
 }
@@ -832,14 +887,12 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
     const uint32_t n = ctx->tree_leaves;
     if (n == 1) {
         if (capacity < 1 || !h_out) return fail(ctx, B2COL_ERR_INVALID, "capacity too small");
-        b2col_aabb box;
-        uint32_t ent;
+        LeafRec rec;
         CU(cudaStreamSynchronize(ctx->stream));
-        CU(cudaMemcpy(&box, ctx->d_world_aabb.p, 24, cudaMemcpyDeviceToHost));
-        CU(cudaMemcpy(&ent, blob_leaf_entity(ctx, 1), 4, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(&rec, blob_leaves(ctx, 1), sizeof rec, cudaMemcpyDeviceToHost));
         memset(h_out, 0, sizeof *h_out);
-        h_out[0].box1 = box;
-        h_out[0].index1 = ent;
+        memcpy(&h_out[0].box1, &rec, 24);
+        h_out[0].index1 = rec.entity;
         h_out[0].type1 = B2COL_NODE_ENTITY;
         h_out[0].type2 = B2COL_NODE_EMPTY;
         *n_out = 1;
@@ -857,8 +910,8 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
     std::vector<uint8_t> used(cand);
     cudaError_t e = cudaMemsetAsync(d_used.p, 0, cand, ctx->stream);
     if (e == cudaSuccess) {
-        k_export<<<cdiv(n, 256), 256, 0, ctx->stream>>>(n, blob_hdr(ctx), blob_nodes(ctx), blob_leaf_entity(ctx, n), ctx->d_world_aabb.as<Aabb24>(),
-                                                        ctx->d_vals[ctx->sorted_side].as<uint32_t>(), d_nodes.as<BiTreeNode60>(), d_used.as<uint8_t>());
+        k_export<<<cdiv(n, 256), 256, 0, ctx->stream>>>(n, blob_hdr(ctx), ctx->d_nodes_full.as<Node>(), blob_leaves(ctx, n), d_nodes.as<BiTreeNode60>(),
+                                                        d_used.as<uint8_t>());
         ++ctx->launches;
         e = cudaGetLastError();
     }

@@ -15,6 +15,92 @@ struct Aabb24 {  // engine::AABB, 24 bytes (reference include/component_collider
 
 constexpr uint32_t UNVISITED = 0xFFFFFFFFu;
 
+// ---- traversal structure: 32-byte quantised nodes + 32-byte exact leaf records -------------------
+// The production traversal is bound first by L1 wavefronts (one per lane per 32-byte sector: incoherent
+// rays never share a line) and then by instruction issue, so a node visit must cost ONE sector and as
+// few instructions as possible.  Child boxes are therefore stored on a 15-bit grid spanning the scene's
+// box bounds — conservatively: lo rounded down, hi rounded up, plus a 2-cell margin that absorbs every
+// float rounding of the grid-space slab test — and only PRUNE.  Exactness lives in the leaf records: a
+// leaf slot that passes the grid test is re-tested against the exact world AABB (bit copy of the refit
+// output) with the reference's arithmetic.
+//
+// A cell index q (15 bits) is stored as the 16-bit value 0x8000|q so that ONE byte-permute turns it into
+// the float 1 + q*2^-15 in [1,2): bytes (0x00, s.lo, s.hi, 0x3F) = 0x3F800000 | q<<8.  The lo and hi
+// planes of one axis share a 32-bit word; the ray picks its near / far plane with a per-ray permute
+// selector, so the slab test needs no per-axis min/max.
+struct alignas(32) QNode {
+    // w[0..2]: slot 0, axis x,y,z: (lo | hi<<16);  w[3..5]: slot 1 likewise;
+    // w[6], w[7]: child refs (LEAF_BIT | Morton position, or internal node index)
+    uint32_t w[8];
+};
+struct alignas(32) LeafRec {  // indexed by Morton position
+    float lo[3], hi[3];
+    uint32_t entity;
+    uint32_t prim;  // index into the b2col_set_colliders order
+};
+static_assert(sizeof(QNode) == 32 && sizeof(LeafRec) == 32, "traversal records are one sector each");
+
+constexpr float GRID_CELLS = 32768.0f;  // 15 bits
+
+struct Grid {
+    float gmin[3], cell[3], inv_cell[3];
+};
+
+// Grid over [bmin,bmax] (bounds of all finite world-box coordinates).  The cell size is bounded below
+// so that (a) a cell is >= 8 ulp of the largest coordinate (quantisation arithmetic stays monotone),
+// (b) a cell is >= T*2^-18: the grid-space t of any |t| <= T then carries an error far below one
+// cell, and a ray origin more than 2^22 cells away from the grid is more than 16 T away from every
+// box, i.e. provably misses (rayq_prepare).
+B2_HD Grid make_grid(const float* bmin, const float* bmax, float T)
+{
+    Grid g;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float lo = bmin[k], hi = bmax[k];
+        if (!(lo <= hi)) {  // no finite coordinate on this axis
+            lo = 0.0f;
+            hi = 0.0f;
+        }
+        const float ext = hi - lo;
+        const float maxabs = fmaxf(fabsf(lo), fabsf(hi));
+        float cell = ext / (GRID_CELLS - 9.0f);
+        cell = fmaxf(cell, T * 3.814697265625e-06f);       // T * 2^-18
+        cell = fmaxf(cell, maxabs * 9.5367431640625e-07f);  // maxabs * 2^-20
+        if (!(cell < B2_INF)) cell = 1.0f;
+        g.cell[k] = cell;
+        g.inv_cell[k] = 1.0f / cell;
+        g.gmin[k] = lo - 4.0f * cell;
+    }
+    return g;
+}
+
+B2_HD uint32_t quant_lo(float x, const Grid& g, int k)
+{
+    float f = floorf((x - g.gmin[k]) * g.inv_cell[k]) - 2.0f;
+    f = fminf(fmaxf(f, 0.0f), GRID_CELLS - 1.0f);  // NaN -> 0 (widest)
+    return 0x8000u | (uint32_t)f;
+}
+B2_HD uint32_t quant_hi(float x, const Grid& g, int k)
+{
+    float f = ceilf((x - g.gmin[k]) * g.inv_cell[k]) + 2.0f;
+    f = fmaxf(fminf(f, GRID_CELLS - 1.0f), 0.0f);
+    if (!(f == f)) f = GRID_CELLS - 1.0f;
+    return 0x8000u | (uint32_t)f;
+}
+
+B2_HD QNode quantise_node(const Slot& a, const Slot& b, const Grid& g)
+{
+    QNode n;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        n.w[k] = quant_lo(a.lo[k], g, k) | (quant_hi(a.hi[k], g, k) << 16);
+        n.w[3 + k] = quant_lo(b.lo[k], g, k) | (quant_hi(b.hi[k], g, k) << 16);
+    }
+    n.w[6] = a.ref;
+    n.w[7] = b.ref;
+    return n;
+}
+
 // ---- LBVH hierarchy + bounds in ONE bottom-up pass ---------------------------------------------
 // Replaces BuildNode (reference src/system_collisions.cpp:205-376) by a different algorithm: the
 // tree of Karras 2012 (radix tree over sorted Morton keys, ties broken by position), emitted
@@ -41,16 +127,22 @@ B2_HD bool delta_less(const Delta& a, const Delta& b) { return a.hi < b.hi || (a
 
 template <class Ops>
 B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
-                           const uint32_t* col_entity, Node* nodes, uint32_t* other_bound, uint32_t* leaf_entity, uint32_t* root_out)
+                           const uint32_t* col_entity, Node* nodes, uint32_t* other_bound, const Grid& grid, QNode* qnodes, LeafRec* leaves,
+                           uint32_t* root_out)
 {
     const uint32_t prim = sorted_prim[i];
-    leaf_entity[i] = col_entity[prim];
     Box box;
+    LeafRec rec;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         box.lo[k] = world_aabb[prim].lo[k];
         box.hi[k] = world_aabb[prim].hi[k];
+        rec.lo[k] = box.lo[k];
+        rec.hi[k] = box.hi[k];
     }
+    rec.entity = col_entity[prim];
+    rec.prim = prim;
+    Ops::store_leaf(&leaves[i], rec);
     if (n == 1) {  // a lone leaf still gets a node: {leaf, nothing} (cf. the reference's {Entity,Empty}, :363-369)
         Slot a, b;
 #pragma unroll
@@ -66,6 +158,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
         b.aux = 0u;
         Ops::store_slot(&nodes[0].s[0], a);
         Ops::store_slot(&nodes[0].s[1], b);
+        Ops::store_qnode(&qnodes[0], quantise_node(a, a, grid));  // both slots = the leaf: an empty slot has no grid encoding
         *root_out = 0u;
         return;
     }
@@ -91,6 +184,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
         if (other == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
         Ops::fence();
         const Slot sib = Ops::load_slot_coherent(&nodes[p].s[is_left ? 1 : 0]);
+        Ops::store_qnode(&qnodes[p], is_left ? quantise_node(mine, sib, grid) : quantise_node(sib, mine, grid));
         if (is_left) r = other;
         else l = other;
 #pragma unroll
@@ -123,7 +217,7 @@ static_assert(sizeof(BiTreeNode60) == 60, "BiTreeNode layout");
 
 B2_HD uint32_t export_perm(uint32_t p, uint32_t root, uint32_t last) { return p == root ? last : (p == last ? root : p); }
 
-B2_HD void export_internal(uint32_t p, uint32_t n, uint32_t root, const Node* nodes, const uint32_t* leaf_entity, BiTreeNode60* out,
+B2_HD void export_internal(uint32_t p, uint32_t n, uint32_t root, const Node* nodes, const LeafRec* leaves, BiTreeNode60* out,
                            uint8_t* used)
 {
     const Node nd = nodes[p];
@@ -142,8 +236,8 @@ B2_HD void export_internal(uint32_t p, uint32_t n, uint32_t root, const Node* no
     if (leaf0 && leaf1) {  // {Entity, Entity}, reference :355-362
         o.type1 = 1;
         o.type2 = 1;
-        o.index1 = leaf_entity[nd.s[0].ref & ~LEAF_BIT];
-        o.index2 = leaf_entity[nd.s[1].ref & ~LEAF_BIT];
+        o.index1 = leaves[nd.s[0].ref & ~LEAF_BIT].entity;
+        o.index2 = leaves[nd.s[1].ref & ~LEAF_BIT].entity;
     }
     else {  // {BoundingVolume, BoundingVolume}, reference :349-352; leaf children go through a wrapper
         o.type1 = 0;
@@ -168,10 +262,10 @@ B2_HD void export_internal(uint32_t p, uint32_t n, uint32_t root, const Node* no
     used[at] = 1;
 }
 
-B2_HD void export_wrapper(uint32_t i, const Aabb24* world_aabb, const uint32_t* sorted_prim, const uint32_t* leaf_entity, BiTreeNode60* out)
+B2_HD void export_wrapper(uint32_t i, const LeafRec* leaves, BiTreeNode60* out)
 {
     BiTreeNode60 o;
-    const Aabb24 b = world_aabb[sorted_prim[i]];
+    const LeafRec b = leaves[i];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         o.box1[k] = b.lo[k];
@@ -179,7 +273,7 @@ B2_HD void export_wrapper(uint32_t i, const Aabb24* world_aabb, const uint32_t* 
         o.box2[k] = 0.0f;  // value-initialised, as BiTreeNode node{} at reference :223
         o.box2[3 + k] = 0.0f;
     }
-    o.index1 = leaf_entity[i];
+    o.index1 = b.entity;
     o.index2 = 0u;
     o.type1 = 1;  // Entity
     o.type2 = 2;  // Empty
@@ -218,16 +312,80 @@ inline size_t compact_export(const BiTreeNode60* cand, const uint8_t* used, size
 // that pass the reference's slab test; on equal tmin the leaf that comes LAST in depth-first order
 // wins, which for this tree is the larger Morton position — exactly what the reference's own
 // RaycastTreeNode (strict '<' at :447 and :488, else second child) returns when it walks the
-// exported tree.  Internal boxes only prune: a child is skipped when its box misses (same slab test,
-// monotone in the box, so a hit leaf implies hit ancestors) or when its entry tmin is already
-// greater than the best tmin (strictly: an equal tmin may still hide a later-position tie winner).
+// exported tree.  Internal (and quantised leaf) boxes only prune: a child is skipped when its grid box
+// misses (superset of the exact box, monotone slab test => a hit leaf implies hit ancestors) or when its
+// grid-space entry tmin is greater than the best exact tmin (strictly: an equal tmin may still hide a
+// later-position tie winner).
 constexpr int LBVH_STACK = 96;  // depth <= key bits (63) + position bits (<= 31): cannot overflow
 
 struct Hit {
     float t;
     int32_t leaf;  // Morton position of the winning leaf, -1 = none
-    int side;
 };
+
+// The ray in normalised grid space (a cell plane q sits at x_n = 1 + q*2^-15):
+//     t = (x_n - o_n) * n,   n = 2^15*cell / d,   evaluated as fma(x_n, n, c) with c = -(o_n*n).
+// |n| is clamped to 2^40: an (almost) axis-parallel ray then keeps a finite, correctly signed slab
+// interval instead of inf - inf; 1.5 cells * 2^40 * 2^-15 dwarfs any T, so the clamp can only ever turn
+// a provable miss into a (harmless) false positive.  sel_near / sel_far pick the lo or hi plane of each
+// axis' word according to the sign of the direction.
+constexpr uint32_t SEL_LO16 = 0x7104u, SEL_HI16 = 0x7324u;  // bytes (const.0, w.0|w.2, w.1|w.3, const.3)
+struct RayQ {
+    float n[3];
+    float c[3];
+    uint32_t sel_near[3], sel_far[3];
+};
+
+// false => the origin is non-finite or more than 2^22 cells from the grid: every box is then more
+// than 16 T away (make_grid), so the reference's slab test (tmin < T) rejects them all: a miss.
+B2_HD bool rayq_prepare(const RayPre& r, const Grid& g, RayQ& q)
+{
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float og = (r.o[k] - g.gmin[k]) * g.inv_cell[k];
+        ok = ok && (fabsf(og) < 4194304.0f);
+        const float on = 1.0f + og * (1.0f / GRID_CELLS);
+        float n = r.ninv[k] * (g.cell[k] * GRID_CELLS);
+        n = fminf(fmaxf(n, -1.099511627776e12f), 1.099511627776e12f);  // +-2^40 (NaN -> -2^40: harmless, exact tests decide)
+        q.n[k] = n;
+        q.c[k] = -(on * n);
+        const bool neg = n < 0.0f;
+        q.sel_near[k] = neg ? SEL_HI16 : SEL_LO16;
+        q.sel_far[k] = neg ? SEL_LO16 : SEL_HI16;
+    }
+    return ok;
+}
+
+B2_HD float cell_plane(uint32_t w, uint32_t sel)
+{
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x3F000000u, sel));
+#else
+    union { uint32_t u; float f; } cv;
+    const uint32_t s16 = (sel == SEL_LO16) ? (w & 0xFFFFu) : (w >> 16);
+    cv.u = 0x3F000000u | (s16 << 8);
+    return cv.f;
+#endif
+}
+
+B2_HD float max3f(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+B2_HD float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
+
+// Grid-space slab test of one slot (wx, wy, wz = the slot's three axis words).
+B2_HD bool qslab(const RayQ& q, uint32_t wx, uint32_t wy, uint32_t wz, float T, float& tmin_out)
+{
+    const float tnx = fmaf(cell_plane(wx, q.sel_near[0]), q.n[0], q.c[0]);
+    const float tny = fmaf(cell_plane(wy, q.sel_near[1]), q.n[1], q.c[1]);
+    const float tnz = fmaf(cell_plane(wz, q.sel_near[2]), q.n[2], q.c[2]);
+    const float tfx = fmaf(cell_plane(wx, q.sel_far[0]), q.n[0], q.c[0]);
+    const float tfy = fmaf(cell_plane(wy, q.sel_far[1]), q.n[1], q.c[1]);
+    const float tfz = fmaf(cell_plane(wz, q.sel_far[2]), q.n[2], q.c[2]);
+    const float tmin = max3f(tnx, tny, tnz);
+    const float tmax = min3f(tfx, tfy, tfz);
+    tmin_out = tmin;
+    return (tmax >= fmaxf(0.0f, tmin)) && (tmin < T);
+}
 
 // Traversal state of one ray, advanced one node visit at a time so that a persistent warp can
 // retire finished rays and fetch new ones between steps (k_trace_lbvh in b2col.cu).  The stack of
@@ -257,47 +415,54 @@ B2_HD void trace_begin(TraceState& st, uint32_t root)
     st.sp = 0;
     st.best.t = B2_INF;
     st.best.leaf = -1;
-    st.best.side = SIDE_LEFT;
 }
 
-B2_HD void leaf_candidate(Hit& best, const SlabT& s, uint32_t ref)
+// Exact test of a candidate leaf (the reference's RayBoxIntersection on the exact world AABB).
+B2_HD void leaf_candidate(Hit& best, const RayPre& r, const LeafRec& rec, uint32_t ref, float T)
 {
+    const SlabT s = slab(r, rec.lo, rec.hi);
+    if (!slab_hit(s, T)) return;
     const int32_t leaf = (int32_t)(ref & ~LEAF_BIT);
     if (s.tmin < best.t || (s.tmin == best.t && leaf > best.leaf)) {
         best.t = s.tmin;
         best.leaf = leaf;
-        best.side = slab_side(s);
     }
 }
 
-// Visit node st.cur (its two slots are passed in), then select the next node. Returns false when the
-// traversal of this ray is complete.
-template <class Stack>
-B2_HD bool trace_visit(TraceState& st, Stack& stk, const RayPre& r, const Slot& a, const Slot& b, float T)
+// Visit node st.cur (already loaded into nd), then select the next node.  RayFn() yields the exact
+// ray (only evaluated when a leaf slot passes the grid test — about once per ray).  Returns false when
+// the traversal of this ray is complete.
+template <class Ops, class Stack, class RayFn>
+B2_HD bool trace_visit(TraceState& st, Stack& stk, const RayQ& q, const QNode& nd, const LeafRec* leaves, float T, RayFn exact_ray)
 {
-    const SlabT sa = slab(r, a.lo, a.hi);
-    const SlabT sb = slab(r, b.lo, b.hi);
-    bool ha = slab_hit(sa, T);
-    bool hb = slab_hit(sb, T);
-    if (ha && (a.ref & LEAF_BIT)) {
-        leaf_candidate(st.best, sa, a.ref);
-        ha = false;
+    float ta, tb;
+    bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], T, ta);
+    bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], T, tb);
+    ha = ha && (ta <= st.best.t);
+    hb = hb && (tb <= st.best.t);
+    const uint32_t ra = nd.w[6], rb = nd.w[7];
+    if ((ha && (ra & LEAF_BIT)) || (hb && (rb & LEAF_BIT))) {
+        const RayPre r = exact_ray();
+        if (ha && (ra & LEAF_BIT)) {
+            leaf_candidate(st.best, r, Ops::load_leaf(&leaves[ra & ~LEAF_BIT]), ra, T);
+            ha = false;
+        }
+        if (hb && (rb & LEAF_BIT)) {
+            leaf_candidate(st.best, r, Ops::load_leaf(&leaves[rb & ~LEAF_BIT]), rb, T);
+            hb = false;
+        }
+        ha = ha && (ta <= st.best.t);
+        hb = hb && (tb <= st.best.t);
     }
-    if (hb && (b.ref & LEAF_BIT)) {
-        leaf_candidate(st.best, sb, b.ref);
-        hb = false;
-    }
-    ha = ha && (sa.tmin <= st.best.t);
-    hb = hb && (sb.tmin <= st.best.t);
     if (ha && hb) {
-        const bool a_first = !(sb.tmin < sa.tmin);
-        stk.put(st.sp, a_first ? b.ref : a.ref, a_first ? sb.tmin : sa.tmin);
+        const bool a_first = !(tb < ta);
+        stk.put(st.sp, a_first ? rb : ra, a_first ? tb : ta);
         ++st.sp;
-        st.cur = a_first ? a.ref : b.ref;
+        st.cur = a_first ? ra : rb;
         return true;
     }
     if (ha || hb) {
-        st.cur = ha ? a.ref : b.ref;
+        st.cur = ha ? ra : rb;
         return true;
     }
     while (st.sp > 0) {
@@ -310,16 +475,32 @@ B2_HD bool trace_visit(TraceState& st, Stack& stk, const RayPre& r, const Slot& 
     return false;
 }
 
+// Raycast epilogue for the winner: the exact slab test is repeated on the winning leaf record to obtain
+// the entry side (bit-identical inputs, bit-identical result), src/system_collisions.cpp:85-97,170-194.
 template <class Ops>
-B2_HD Hit trace_lbvh(const RayPre& r, const Node* nodes, uint32_t root, float T)
+B2_HD void finish_raycast(uint32_t* out9, const RayPre& r, const Hit& best, const LeafRec* leaves)
+{
+    if (best.leaf < 0) {
+        write_raycast(out9, r, false, 0.0f, 0, 0u);
+        return;
+    }
+    const LeafRec rec = Ops::load_leaf(&leaves[best.leaf]);
+    const SlabT s = slab(r, rec.lo, rec.hi);
+    write_raycast(out9, r, true, s.tmin, slab_side(s), rec.entity);
+}
+
+// Whole-ray form (host emulation; the device kernel interleaves trace_visit with ray fetching).
+template <class Ops>
+B2_HD Hit trace_lbvh(const RayPre& r, const Grid& grid, const QNode* qnodes, const LeafRec* leaves, uint32_t root, float T)
 {
     TraceState st;
     ArrayStack stk;
     trace_begin(st, root);
+    RayQ q;
+    if (!rayq_prepare(r, grid, q)) return st.best;
     for (;;) {
-        const Slot a = Ops::load_slot(&nodes[st.cur].s[0]);
-        const Slot b = Ops::load_slot(&nodes[st.cur].s[1]);
-        if (!trace_visit(st, stk, r, a, b, T)) break;
+        const QNode nd = Ops::load_qnode(&qnodes[st.cur]);
+        if (!trace_visit<Ops>(st, stk, q, nd, leaves, T, [&]() { return r; })) break;
     }
     return st.best;
 }

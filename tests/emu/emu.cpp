@@ -26,6 +26,10 @@ struct HostOps {
         *p = v;
         return o;
     }
+    static void store_qnode(QNode* p, const QNode& n) { *p = n; }
+    static void store_leaf(LeafRec* p, const LeafRec& r) { *p = r; }
+    static QNode load_qnode(const QNode* p) { return *p; }
+    static LeafRec load_leaf(const LeafRec* p) { return *p; }
 };
 
 extern "C" {
@@ -51,29 +55,33 @@ void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, 
     }
 }
 
-// bounds -> Morton keys -> stable sort -> bottom-up hierarchy.  nodes: max(n-1,1) entries.
+// bounds -> Morton keys -> stable sort -> bottom-up hierarchy.  nodes/qnodes: max(n-1,1) entries, leaves: n.
 // `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
 // that the result does not depend on thread scheduling.
-void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, Node* nodes, uint32_t* leaf_entity,
-               uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order)
+void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
+               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order)
 {
     if (n == 0) return;
     float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (uint32_t i = 0; i < n; ++i)
         for (int k = 0; k < 3; ++k) {
-            const float c = (world_aabb[i].lo[k] + world_aabb[i].hi[k]) * 0.5f;
+            const float lo = world_aabb[i].lo[k], hi = world_aabb[i].hi[k];
+            const float c = (lo + hi) * 0.5f;
             if (std::isfinite(c)) {
                 smin[k] = fminf(smin[k], c);
                 smax[k] = fmaxf(smax[k], c);
             }
+            if (std::isfinite(lo)) { bmin[k] = fminf(bmin[k], lo); bmax[k] = fmaxf(bmax[k], lo); }
+            if (std::isfinite(hi)) { bmin[k] = fminf(bmin[k], hi); bmax[k] = fmaxf(bmax[k], hi); }
         }
     float sinv[3];
     for (int k = 0; k < 3; ++k) {
-        // same round trip through the order-preserving encoding as the device
-        smin[k] = ordered_to_float(~(~float_to_ordered(smin[k])));
         const float ext = smax[k] - smin[k];
         sinv[k] = (ext > 0.0f && std::isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
     }
+    const Grid grid = make_grid(bmin, bmax, T);
+    *grid_out = grid;
     std::vector<uint64_t> keys(n);
     for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, smin, sinv, bits);
     std::vector<uint32_t> idx(n);
@@ -85,10 +93,10 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
     }
     std::vector<uint32_t> other(n, UNVISITED);
     for (uint32_t t = 0; t < n; ++t)
-        build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), leaf_entity, root);
+        build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), grid, qnodes, leaves, root);
 }
 
-void emu_trace_lbvh(const Node* nodes, uint32_t root, uint32_t n_leaves, const uint32_t* leaf_entity, const float* rays6, size_t n_rays,
+void emu_trace_lbvh(const QNode* qnodes, const LeafRec* leaves, const Grid* grid, uint32_t root, uint32_t n_leaves, const float* rays6, size_t n_rays,
                     uint32_t* out9, float T)
 {
     for (size_t i = 0; i < n_rays; ++i) {
@@ -97,8 +105,8 @@ void emu_trace_lbvh(const Node* nodes, uint32_t root, uint32_t n_leaves, const u
             write_raycast(out9 + 9 * i, r, false, 0.0f, 0, 0u);
             continue;
         }
-        const Hit h = trace_lbvh<HostOps>(r, nodes, root, T);
-        write_raycast(out9 + 9 * i, r, h.leaf >= 0, h.t, h.side, h.leaf >= 0 ? leaf_entity[h.leaf] : 0u);
+        const Hit h = trace_lbvh<HostOps>(r, *grid, qnodes, leaves, root, T);
+        finish_raycast<HostOps>(out9 + 9 * i, r, h, leaves);
     }
 }
 
@@ -115,17 +123,13 @@ int emu_trace_reftopo(const uint32_t* words, uint32_t n_nodes, const float* rays
 }
 
 // returns number of nodes written to out (capacity 2n)
-size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const uint32_t* leaf_entity, const Aabb24* world_aabb, const uint32_t* sorted_prim,
-                  BiTreeNode60* out, size_t capacity)
+size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const LeafRec* leaves, BiTreeNode60* out, size_t capacity)
 {
     if (n == 0) return 0;
     if (n == 1) {
         std::memset(out, 0, sizeof *out);
-        for (int k = 0; k < 3; ++k) {
-            out[0].box1[k] = world_aabb[0].lo[k];
-            out[0].box1[3 + k] = world_aabb[0].hi[k];
-        }
-        out[0].index1 = leaf_entity[0];
+        std::memcpy(out[0].box1, &leaves[0], 24);
+        out[0].index1 = leaves[0].entity;
         out[0].type1 = 1;
         out[0].type2 = 2;
         return 1;
@@ -134,45 +138,47 @@ size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const uint32_t* 
     std::vector<BiTreeNode60> tmp(cand);
     std::vector<uint8_t> used(cand, 0);
     for (uint32_t i = 0; i < n; ++i) {
-        export_wrapper(i, world_aabb, sorted_prim, leaf_entity, tmp.data());
-        if (i + 1 < n) export_internal(i, n, root, nodes, leaf_entity, tmp.data(), used.data());
+        export_wrapper(i, leaves, tmp.data());
+        if (i + 1 < n) export_internal(i, n, root, nodes, leaves, tmp.data(), used.data());
     }
     return compact_export(tmp.data(), used.data(), cand, out, capacity);
 }
 
 }  // extern "C"
 
-// Instrumentation (dev): node visits per tree depth, and visits in total, for a ray sample.
-extern "C" void emu_visit_histogram(const Node* nodes, uint32_t root, const float* rays6, size_t n_rays, float T, uint64_t* hist, int max_depth,
-                                    uint64_t* total_visits, uint64_t* leaf_tests)
+// Instrumentation (dev): node visits per tree depth, visits in total and exact leaf tests, for a ray sample.
+extern "C" void emu_visit_histogram(const QNode* qnodes, const LeafRec* leaves, const Grid* grid, uint32_t root, const float* rays6, size_t n_rays,
+                                    float T, uint64_t* hist, int max_depth, uint64_t* total_visits, uint64_t* leaf_tests)
 {
     std::vector<uint32_t> sn(256);
     std::vector<float> stt(256);
     std::vector<int> sd(256);
     for (size_t i = 0; i < n_rays; ++i) {
         const RayPre r = ray_prepare(rays6 + 6 * i, rays6 + 6 * i + 3);
+        RayQ q;
+        if (!rayq_prepare(r, *grid, q)) continue;
         Hit best;
         best.t = INFINITY;
         best.leaf = -1;
-        best.side = 0;
         int sp = 0, depth = 0;
         uint32_t cur = root;
         for (;;) {
             ++*total_visits;
             ++hist[depth < max_depth ? depth : max_depth - 1];
-            const Slot a = nodes[cur].s[0], b = nodes[cur].s[1];
-            const SlabT sa = slab(r, a.lo, a.hi), sb = slab(r, b.lo, b.hi);
-            bool ha = slab_hit(sa, T), hb = slab_hit(sb, T);
-            if (ha && (a.ref & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, sa, a.ref); ha = false; }
-            if (hb && (b.ref & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, sb, b.ref); hb = false; }
-            ha = ha && sa.tmin <= best.t;
-            hb = hb && sb.tmin <= best.t;
+            const QNode nd = qnodes[cur];
+            float ta, tb;
+            bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], T, ta) && ta <= best.t;
+            bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], T, tb) && tb <= best.t;
+            if (ha && (nd.w[6] & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, r, leaves[nd.w[6] & ~LEAF_BIT], nd.w[6], T); ha = false; }
+            if (hb && (nd.w[7] & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, r, leaves[nd.w[7] & ~LEAF_BIT], nd.w[7], T); hb = false; }
+            ha = ha && ta <= best.t;
+            hb = hb && tb <= best.t;
             if (ha && hb) {
-                const bool af = !(sb.tmin < sa.tmin);
-                sn[sp] = af ? b.ref : a.ref; stt[sp] = af ? sb.tmin : sa.tmin; sd[sp] = depth + 1; ++sp;
-                cur = af ? a.ref : b.ref; ++depth; continue;
+                const bool af = !(tb < ta);
+                sn[sp] = af ? nd.w[7] : nd.w[6]; stt[sp] = af ? tb : ta; sd[sp] = depth + 1; ++sp;
+                cur = af ? nd.w[6] : nd.w[7]; ++depth; continue;
             }
-            if (ha || hb) { cur = ha ? a.ref : b.ref; ++depth; continue; }
+            if (ha || hb) { cur = ha ? nd.w[6] : nd.w[7]; ++depth; continue; }
             bool found = false;
             while (sp > 0) { --sp; if (stt[sp] <= best.t) { cur = sn[sp]; depth = sd[sp]; found = true; break; } }
             if (!found) break;

@@ -13,6 +13,10 @@ DEPS = [SRC] + [os.path.join(ROOT, "engine_b200", "csrc", f) for f in ("b2col_ma
 
 NODE64 = np.dtype([("lo0", "<f4", 3), ("hi0", "<f4", 3), ("ref0", "<u4"), ("aux0", "<u4"), ("lo1", "<f4", 3), ("hi1", "<f4", 3), ("ref1", "<u4"), ("aux1", "<u4")])
 assert NODE64.itemsize == 64
+QNODE = np.dtype([("w", "<u4", 8)])
+LEAFREC = np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("entity", "<u4"), ("prim", "<u4")])
+GRID = np.dtype([("gmin", "<f4", 3), ("cell", "<f4", 3), ("inv_cell", "<f4", 3)])
+assert QNODE.itemsize == 32 and LEAFREC.itemsize == 32 and GRID.itemsize == 36
 LEAF_BIT = 0x80000000
 
 
@@ -44,27 +48,30 @@ class Emu:
         self.lib.emu_refit(C.c_uint32(entity.shape[0]), _p(entity), _p(local), _p(world), _p(out))
         return out
 
-    def build(self, world_aabb, entity, bits=16, order=None):
+    def build(self, world_aabb, entity, bits=16, order=None, T=1000.0):
         world_aabb = np.ascontiguousarray(world_aabb, np.float32).reshape(-1, 6)
         entity = np.ascontiguousarray(entity, np.uint32)
         n = entity.shape[0]
         nodes = np.zeros(max(n - 1, 1), NODE64)
-        leaf_entity = np.zeros(n, np.uint32)
+        qnodes = np.zeros(max(n - 1, 1), QNODE)
+        leaves = np.zeros(n, LEAFREC)
+        grid = np.zeros(1, GRID)
         sorted_prim = np.zeros(n, np.uint32)
         sorted_keys = np.zeros(n, np.uint64)
         root = C.c_uint32(0)
         if order is not None:
             order = np.ascontiguousarray(order, np.uint32)
-        self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), _p(nodes), _p(leaf_entity), _p(sorted_prim), _p(sorted_keys),
-                           C.byref(root), _p(order))
-        return dict(n=n, nodes=nodes, leaf_entity=leaf_entity, sorted_prim=sorted_prim, sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
+        self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
+                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order))
+        return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
+                    sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
 
     def trace_lbvh(self, tree, rays, T=1000.0):
         from oracle.oracle import RAYCAST_DTYPE
 
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
         out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
-        self.lib.emu_trace_lbvh(_p(tree["nodes"]), C.c_uint32(tree["root"]), C.c_uint32(tree["n"]), _p(tree["leaf_entity"]), _p(rays),
+        self.lib.emu_trace_lbvh(_p(tree["qnodes"]), _p(tree["leaves"]), _p(tree["grid"]), C.c_uint32(tree["root"]), C.c_uint32(tree["n"]), _p(rays),
                                 C.c_size_t(rays.shape[0]), _p(out), C.c_float(T))
         return out
 
@@ -83,6 +90,5 @@ class Emu:
 
         n = tree["n"]
         out = np.zeros(2 * max(n, 1), NODE_DTYPE)
-        k = self.lib.emu_export(C.c_uint32(n), _p(tree["nodes"]), C.c_uint32(tree["root"]), _p(tree["leaf_entity"]), _p(tree["world_aabb"]),
-                                _p(tree["sorted_prim"]), _p(out), C.c_size_t(out.shape[0]))
+        k = self.lib.emu_export(C.c_uint32(n), _p(tree["nodes"]), C.c_uint32(tree["root"]), _p(tree["leaves"]), _p(out), C.c_size_t(out.shape[0]))
         return out[:k].copy()

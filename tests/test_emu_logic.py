@@ -144,3 +144,46 @@ def test_emu_export_walked_by_live_reference(emu):
     r.transform_update()
     r.set_bvh(emu.export(tree))  # the reference's public bvh_ member
     assert_raycast_equal(emu.trace_lbvh(tree, rays), r.raycast(rays), "reference GetRaycast on exported tree")
+
+
+def dequant(tree):
+    """World-space boxes of both slots of every quantised node (15-bit cells, flag bit 0x8000)."""
+    g = tree["grid"][0]
+    w = tree["qnodes"]["w"].astype(np.uint64)
+    assert ((w[:, :6] & 0x8000) != 0).all() and (((w[:, :6] >> 16) & 0x8000) != 0).all()
+    lo = (w[:, :6] & 0x7FFF).astype(np.float64)          # (n, 6): slot0 xyz, slot1 xyz
+    hi = ((w[:, :6] >> 16) & 0x7FFF).astype(np.float64)
+    gm, cell = g["gmin"].astype(np.float64), g["cell"].astype(np.float64)
+    return {s: np.concatenate([gm + lo[:, 3 * s : 3 * s + 3] * cell, gm + hi[:, 3 * s : 3 * s + 3] * cell], 1) for s in (0, 1)}
+
+
+@pytest.mark.parametrize("extent,offset,box", [(1000.0, 0.0, 2.0), (1.0, 0.0, 0.01), (1e-3, 0.0, 1e-5), (50.0, 1.0e6, 1.0), (1.0e5, -3.0e5, 30.0), (20.0, 0.0, 15.0)])
+def test_emu_quantised_nodes_are_conservative(emu, port, extent, offset, box):
+    """The 16-bit grid boxes must contain the exact boxes (they only prune), for scenes of any scale and
+    position, and the quantised traversal must still equal brute force — including rays that start far
+    outside the grid (provable-miss shortcut) and rays lying exactly on box planes."""
+    rng = np.random.default_rng(int(extent * 7) % 1000 + 3)
+    n = 3000
+    c = (rng.uniform(-extent, extent, (n, 3)) + offset).astype(np.float32)
+    h = rng.uniform(0.1 * box, box, (n, 3)).astype(np.float32)
+    boxes = np.concatenate([c - h, c + h], 1).astype(np.float32)
+    ent = np.arange(1, n + 1, dtype=np.uint32)
+    tree = emu.build(boxes, ent)
+    dq = dequant(tree)
+    nodes = tree["nodes"]
+    for s in (0, 1):
+        lo, hi = nodes[f"lo{s}"].astype(np.float64), nodes[f"hi{s}"].astype(np.float64)
+        assert (dq[s][:, :3] <= lo).all() and (dq[s][:, 3:] >= hi).all(), "grid box does not contain the exact box"
+    g = tree["grid"][0]
+    assert (g["cell"] >= 1000.0 * 2.0**-18 * 0.999).all()
+    o = (rng.uniform(-1.2 * extent, 1.2 * extent, (6000, 3)) + offset).astype(np.float32)
+    d = rng.standard_normal((6000, 3)).astype(np.float32)
+    d[:1500] = np.sign(d[:1500]) * (np.abs(d[:1500]) > 1.0)          # axis-parallel / diagonal / zero
+    o[1500:2500] = boxes[rng.integers(0, n, 1000), :3]               # origins exactly on box min planes
+    o[2500:3000] += np.float32(40000.0) * np.sign(d[2500:3000])      # far outside: out of the grid's range
+    o[3000:3200] = np.nan
+    rays = np.concatenate([o, d], 1).astype(np.float32)
+    got = emu.trace_lbvh(tree, rays)
+    brute = port.raycast_brute(tree["leaf_entity"], boxes[tree["sorted_prim"]], rays, nthreads=4)
+    assert_raycast_equal(got, brute, f"quantised traversal, extent {extent} offset {offset}")
+    assert got["hit"].sum() > 0
