@@ -467,6 +467,9 @@ struct b2col_ctx {
     uint32_t n_ref_nodes = 0;
     // staging for host-buffer queries
     DevBuf d_rays, d_hits, d_counter;
+    cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
+    std::vector<cudaEvent_t> pipe_events;
+    size_t e2e_chunk = 2u << 20;
     int trace_grid = 148 * 8, fetch_threshold = 24;
     cudaEvent_t events[16] = {};
 };
@@ -617,6 +620,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
+        if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_TRACE_FETCH_THRESHOLD")) c->fetch_threshold = std::min(32, std::max(1, atoi(e)));
         c->trace_grid = sms * per_sm;
     }
@@ -635,6 +639,9 @@ void b2col_destroy(b2col_ctx* ctx)
         release(*b);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->pipe_events) cudaEventDestroy(ev);
+    if (ctx->stream_in) cudaStreamDestroy(ctx->stream_in);
+    if (ctx->stream_out) cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -843,6 +850,38 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
     CU(cudaSetDevice(ctx->device));
     GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
     GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
+    const size_t chunk = ctx->e2e_chunk;
+    if (mode == B2COL_MODE_LBVH && n >= 2 * chunk) {
+        // Large batch: pipeline in chunks over three streams so that the upload of chunk c+1, the trace of
+        // chunk c and the download of chunk c-1 overlap (PCIe is full duplex).  Needs page-locked host
+        // buffers to actually overlap; with pageable memory the copies serialise but stay correct.
+        if (!ctx->stream_in) {
+            CU(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
+            CU(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
+        }
+        const size_t n_chunks = (n + chunk - 1) / chunk;
+        while (ctx->pipe_events.size() < 2 * n_chunks) {
+            cudaEvent_t ev;
+            CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            ctx->pipe_events.push_back(ev);
+        }
+        b2col_ray* d_r = ctx->d_rays.as<b2col_ray>();
+        b2col_raycast* d_h = ctx->d_hits.as<b2col_raycast>();
+        for (size_t c = 0; c < n_chunks; ++c) {
+            const size_t off = c * chunk, m = std::min(chunk, n - off);
+            cudaEvent_t ev_in = ctx->pipe_events[2 * c], ev_k = ctx->pipe_events[2 * c + 1];
+            CU(cudaMemcpyAsync(d_r + off, h_rays + off, m * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream_in));
+            CU(cudaEventRecord(ev_in, ctx->stream_in));
+            CU(cudaStreamWaitEvent(ctx->stream, ev_in, 0));
+            GUARD(enqueue_trace(ctx, d_r + off, m, d_h + off, mode));
+            CU(cudaEventRecord(ev_k, ctx->stream));
+            CU(cudaStreamWaitEvent(ctx->stream_out, ev_k, 0));
+            CU(cudaMemcpyAsync(h_out + off, d_h + off, m * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream_out));
+        }
+        CU(cudaStreamSynchronize(ctx->stream_out));
+        CU(cudaStreamSynchronize(ctx->stream));
+        return B2COL_OK;
+    }
     CU(cudaMemcpyAsync(ctx->d_rays.p, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));
     GUARD(enqueue_trace(ctx, ctx->d_rays.as<b2col_ray>(), n, ctx->d_hits.as<b2col_raycast>(), mode));
     CU(cudaMemcpyAsync(h_out, ctx->d_hits.p, n * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream));
