@@ -24,7 +24,7 @@ def _rays(rays) -> np.ndarray:
 
 
 class CollisionSystem:
-    def __init__(self, device: int = 0, max_distance: float = 1000.0, morton_bits_per_axis: int = 16):
+    def __init__(self, device: int = 0, max_distance: float = 1000.0, morton_bits_per_axis: int = 0):
         self.lib = capi.load()
         cfg = capi.Config(device=device, max_distance=max_distance, morton_bits_per_axis=morton_bits_per_axis, use_cuda_graph=0)
         h = C.c_void_p()

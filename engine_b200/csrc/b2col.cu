@@ -51,8 +51,15 @@ struct DevOps {
         const float4* q = reinterpret_cast<const float4*>(p);
         return unpack(__ldcg(q), __ldcg(q + 1));
     }
-    static __device__ __forceinline__ void fence() { __threadfence(); }
-    static __device__ __forceinline__ uint32_t exch(uint32_t* p, uint32_t v) { return atomicExch(p, v); }
+    // Arrival at a node: one exchange with acquire-release semantics at GPU scope.  The release half
+    // publishes this thread's child slot (stored just before) to whoever reads the exchanged word; the
+    // acquire half makes the sibling's slot, published the same way, visible to the loads that follow.
+    static __device__ __forceinline__ uint32_t arrive(uint32_t* p, uint32_t v)
+    {
+        uint32_t old;
+        asm volatile("atom.acq_rel.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+        return old;
+    }
     // 32-byte records move as two 16-byte vectors on the store side and as ONE 256-bit read-only load
     // (sm_100a LDG.E.ENL2.256) on the traversal side: one L1 wavefront per lane per record.
     static __device__ __forceinline__ void store_qnode(QNode* p, const QNode& n)
@@ -221,7 +228,7 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway), and reset of the per-node arrival words used by k_build.
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int passes, float T, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* __restrict__ other_bound, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
@@ -241,7 +248,7 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
         const float2* bp = reinterpret_cast<const float2*>(world_aabb + i);
         const float2 b0 = bp[0], b1 = bp[1], b2 = bp[2];
         const float lo[3] = {b0.x, b0.y, b1.x}, hi[3] = {b1.y, b2.x, b2.y};
-        const uint64_t key = morton_key(lo, hi, smin, sinv, bits);
+        const uint64_t key = morton_key(lo, hi, smin, sinv, bits, drop);
         keys[i] = key;
         vals[i] = i;
         other_bound[i] = UNVISITED;
@@ -438,8 +445,8 @@ struct b2col_ctx {
     cudaStream_t stream = nullptr;
     b2col_config cfg{};
     float T = 1000.0f;
-    int bits = 16;
-    int passes = 6;
+    int cfg_bits = 0;  // 0 = choose the key width from the collider count
+    int bits = 11, drop = 1, passes = 4;
     std::string err;
     uint64_t launches = 0;
 
@@ -603,12 +610,11 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
     c->device = dev;
     if (cfg) c->cfg = *cfg;
     c->T = (cfg && cfg->max_distance > 0.0f) ? cfg->max_distance : 1000.0f;
-    c->bits = (cfg && cfg->morton_bits_per_axis > 0) ? cfg->morton_bits_per_axis : 16;
-    if (c->bits < 4 || c->bits > 21) {
+    c->cfg_bits = (cfg && cfg->morton_bits_per_axis > 0) ? cfg->morton_bits_per_axis : 0;
+    if (c->cfg_bits != 0 && (c->cfg_bits < 4 || c->cfg_bits > 21)) {
         delete c;
-        return fail(nullptr, B2COL_ERR_INVALID, "morton_bits_per_axis must be in [4,21]");
+        return fail(nullptr, B2COL_ERR_INVALID, "morton_bits_per_axis must be 0 (auto) or in [4,21]");
     }
-    c->passes = (3 * c->bits + RS_BITS - 1) / RS_BITS;
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete c;
@@ -800,6 +806,20 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_other_bound, (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_nodes_full, (size_t)(n > 1 ? n - 1 : 1) * sizeof(Node)));
+    // Morton key width: the radix sort costs one pass per 8 key bits, and at ~1M colliders each pass is
+    // latency-bound (~20 us), so the key is only as wide as the collider count needs: 32 bits (11,11,10 per
+    // axis, 4.3e9 cells) up to 2M colliders, 40 bits up to 32M, 48 beyond; an explicit
+    // morton_bits_per_axis overrides (3*bits key bits).
+    if (ctx->cfg_bits > 0) {
+        ctx->bits = ctx->cfg_bits;
+        ctx->drop = 0;
+    }
+    else {
+        const int key_bits = n <= (1u << 21) ? 32 : (n <= (1u << 25) ? 40 : 48);
+        ctx->bits = (key_bits + 2) / 3;
+        ctx->drop = 3 * ctx->bits - key_bits;
+    }
+    ctx->passes = (3 * ctx->bits - ctx->drop + RS_BITS - 1) / RS_BITS;
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t hist_bytes = (size_t)RS_MAX_PASSES * RS_RADIX * 4;
     const size_t ticket_bytes = 64;
@@ -818,7 +838,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     // ---- a4: LBVH build -------------------------------------------------------------------------
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->passes, ctx->T, ctx->d_keys[0].as<uint64_t>(),
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T, ctx->d_keys[0].as<uint64_t>(),
                ctx->d_vals[0].as<uint32_t>(), ctx->d_other_bound.as<uint32_t>(), ghist);
     }
     int side = 0;

@@ -179,10 +179,8 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
         mine.ref = ref;
         mine.aux = is_left ? l : r;
         Ops::store_slot(&nodes[p].s[is_left ? 0 : 1], mine);
-        Ops::fence();
-        const uint32_t other = Ops::exch(&other_bound[p], is_left ? l : r);
+        const uint32_t other = Ops::arrive(&other_bound[p], is_left ? l : r);  // release my slot / acquire the sibling's
         if (other == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
-        Ops::fence();
         const Slot sib = Ops::load_slot_coherent(&nodes[p].s[is_left ? 1 : 0]);
         Ops::store_qnode(&qnodes[p], is_left ? quantise_node(mine, sib, grid) : quantise_node(sib, mine, grid));
         if (is_left) r = other;

@@ -252,9 +252,10 @@ B2_HD uint64_t spread3(uint32_t v)
 }
 
 // Centroid (GetBoxCentroid, src/system_collisions.cpp:43-50: (min+max)*0.5f) quantised to `bits`
-// bits per axis inside the scene's centroid bounds, interleaved x (most significant), y, z.
-// Only steers tree topology; never affects which box a ray hits.
-B2_HD uint64_t morton_key(const float* lo, const float* hi, const float* smin, const float* sinv, int bits)
+// bits per axis inside the scene's centroid bounds, interleaved x (most significant), y, z; the lowest
+// `drop` bits of the interleaved code are discarded (e.g. bits = 11, drop = 1: a 32-bit key with 11,11,10
+// bits for x,y,z — four 8-bit radix passes).  Only steers tree topology; never affects which box a ray hits.
+B2_HD uint64_t morton_key(const float* lo, const float* hi, const float* smin, const float* sinv, int bits, int drop = 0)
 {
     const float maxq = (float)((1u << bits) - 1u);
     uint32_t q[3];
@@ -265,7 +266,7 @@ B2_HD uint64_t morton_key(const float* lo, const float* hi, const float* smin, c
         f = fminf(fmaxf(f, 0.0f), maxq);                // NaN -> 0 (fmaxf drops NaN)
         q[k] = (uint32_t)f;
     }
-    return (spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2]);
+    return ((spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2])) >> drop;
 }
 
 // Order-preserving float <-> uint map for atomicMin/atomicMax on floats.

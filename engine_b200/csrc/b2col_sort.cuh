@@ -15,13 +15,20 @@ constexpr int RS_BITS = 8;
 constexpr int RS_RADIX = 1 << RS_BITS;
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
+#ifndef B2_RS_ITEMS
+#define B2_RS_ITEMS 16
+#endif
+constexpr int RS_ITEMS = B2_RS_ITEMS;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 pairs per tile
 constexpr int RS_MAX_PASSES = 8;
 
 constexpr uint32_t LB_FLAG_AGG = 1u << 30;     // tile's own digit count is posted
 constexpr uint32_t LB_FLAG_PREFIX = 2u << 30;  // inclusive count over tiles 0..this is posted
 constexpr uint32_t LB_VALUE_MASK = (1u << 30) - 1u;
+#ifndef B2_LB_BATCH
+#define B2_LB_BATCH 8
+#endif
+constexpr int LB_BATCH = B2_LB_BATCH;
 
 static_assert(RS_THREADS == RS_RADIX, "one thread per digit in the scan phases");
 
@@ -119,14 +126,24 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
         }
         else {
             lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_AGG | tile_count;
+            // Walk back over the predecessors' status words LB_BATCH at a time: the loads of a batch are
+            // independent (one L2 round trip for the batch instead of one per tile); tiles start almost
+            // simultaneously here, so a serial walk would be a chain of up to `tile` dependent L2 reads.
             int t = (int)tile - 1;
-            for (;;) {
-                const uint32_t v = lb[(size_t)t * RS_RADIX + tid];
-                const uint32_t f = v >> 30;
-                if (f == 0u) continue;  // not posted yet: that tile is running (ticket order)
-                excl += v & LB_VALUE_MASK;
-                if (f == 2u) break;
-                --t;
+            bool done = false;
+            while (!done) {
+                uint32_t v[LB_BATCH];
+#pragma unroll
+                for (int j = 0; j < LB_BATCH; ++j) v[j] = (t - j >= 0) ? lb[(size_t)(t - j) * RS_RADIX + tid] : (2u << 30);  // LB_FLAG_PREFIX with value 0: ends the walk
+#pragma unroll
+                for (int j = 0; j < LB_BATCH; ++j) {
+                    if (done) break;
+                    uint32_t w = v[j];
+                    while ((w >> 30) == 0u) w = lb[(size_t)(t - j) * RS_RADIX + tid];  // not posted yet: that tile is running (ticket order)
+                    excl += w & LB_VALUE_MASK;
+                    done = (w >> 30) == 2u;
+                }
+                t -= LB_BATCH;
             }
             lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_PREFIX | (excl + tile_count);
         }

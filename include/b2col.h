@@ -85,7 +85,7 @@ typedef struct b2col_bitreenode {
 typedef struct b2col_config {
     int device;              /* CUDA device ordinal */
     float max_distance;      /* reference hard-codes T = 1000.0f (src/system_collisions.cpp:384); 0 => 1000 */
-    int morton_bits_per_axis; /* 10..21; 0 => 16 (48-bit keys, 6 radix passes) */
+    int morton_bits_per_axis; /* 4..21 (key = 3*bits); 0 => automatic: 32-bit keys up to 2M colliders, 40 up to 32M, else 48 */
     int use_cuda_graph;      /* 1: b2col_update replays a captured CUDA graph when shapes are unchanged */
 } b2col_config;
 

@@ -19,8 +19,7 @@ struct HostOps {
     static void store_slot(Slot* p, const Slot& s) { *p = s; }
     static Slot load_slot(const Slot* p) { return *p; }
     static Slot load_slot_coherent(const Slot* p) { return *p; }
-    static void fence() {}
-    static uint32_t exch(uint32_t* p, uint32_t v)
+    static uint32_t arrive(uint32_t* p, uint32_t v)
     {
         const uint32_t o = *p;
         *p = v;
@@ -58,7 +57,7 @@ void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, 
 // bounds -> Morton keys -> stable sort -> bottom-up hierarchy.  nodes/qnodes: max(n-1,1) entries, leaves: n.
 // `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
 // that the result does not depend on thread scheduling.
-void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
+void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, int drop, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
                Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order)
 {
     if (n == 0) return;
@@ -83,7 +82,7 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
     const Grid grid = make_grid(bmin, bmax, T);
     *grid_out = grid;
     std::vector<uint64_t> keys(n);
-    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, smin, sinv, bits);
+    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, smin, sinv, bits, drop);
     std::vector<uint32_t> idx(n);
     std::iota(idx.begin(), idx.end(), 0u);
     std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });

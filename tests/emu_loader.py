@@ -48,10 +48,18 @@ class Emu:
         self.lib.emu_refit(C.c_uint32(entity.shape[0]), _p(entity), _p(local), _p(world), _p(out))
         return out
 
-    def build(self, world_aabb, entity, bits=16, order=None, T=1000.0):
+    @staticmethod
+    def auto_bits(n):
+        """the library's automatic key width (b2col_update): (bits per axis, dropped low bits)"""
+        key_bits = 32 if n <= (1 << 21) else (40 if n <= (1 << 25) else 48)
+        bits = (key_bits + 2) // 3
+        return bits, 3 * bits - key_bits
+
+    def build(self, world_aabb, entity, bits=0, order=None, T=1000.0):
         world_aabb = np.ascontiguousarray(world_aabb, np.float32).reshape(-1, 6)
         entity = np.ascontiguousarray(entity, np.uint32)
         n = entity.shape[0]
+        bits, drop = (bits, 0) if bits else self.auto_bits(n)
         nodes = np.zeros(max(n - 1, 1), NODE64)
         qnodes = np.zeros(max(n - 1, 1), QNODE)
         leaves = np.zeros(n, LEAFREC)
@@ -61,7 +69,7 @@ class Emu:
         root = C.c_uint32(0)
         if order is not None:
             order = np.ascontiguousarray(order, np.uint32)
-        self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
+        self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_int(drop), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
                            _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order))
         return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
                     sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)

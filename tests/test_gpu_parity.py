@@ -145,8 +145,8 @@ def test_degenerate_inputs(CollisionSystem, port):
 # ---------------------------------------------------------------------------------------------
 # radix sort and hierarchy at scale, duplicates
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("n,bits_per_axis", [(4095, 16), (4096, 16), (4097, 16), (70001, 10), (300000, 16), (300000, 21), (1 << 20, 16)])
-def test_build_matches_host_restatement(CollisionSystem, emu, n, bits_per_axis):
+@pytest.mark.parametrize("n,bits_per_axis", [(4095, 16), (4096, 0), (4097, 16), (70001, 10), (300000, 0), (300000, 21), (1 << 20, 0), (3_000_000, 0)])
+def test_build_matches_host_restatement(CollisionSystem, emu, n, bits_per_axis):  # 0 = automatic key width
     s = synth.uniform_boxes(n, seed=60 + bits_per_axis, extent=200.0) if n < 200000 else synth.clustered_boxes(n, seed=61, n_clusters=50)
     cs = CollisionSystem(morton_bits_per_axis=bits_per_axis)
     cs.set_scene(s)

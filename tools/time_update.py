@@ -1,0 +1,27 @@
+"""Time b2col_update (propagate + refit + sort + build) on device-resident inputs (dev tool)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from engine_b200 import synth  # noqa: E402
+from engine_b200.collision import CollisionSystem  # noqa: E402
+
+
+def main():
+    for name, scene in (("flat 1M", synth.uniform_boxes(1_000_000)), ("hier 1M (1000 roots, depth 3)", synth.hierarchy_scene(1_000_000, 1000))):
+        cs = CollisionSystem()
+        cs.set_scene(scene)
+        for _ in range(5):
+            cs.on_update(wait=False)
+        cs.sync()
+        K = 50
+        cs.event_record(0)
+        for _ in range(K):
+            cs.on_update(wait=False)
+        cs.event_record(1)
+        print(f"{name:32s} update {cs.event_elapsed_ms(0, 1) / K * 1e3:8.1f} us", flush=True)
+        cs.close()
+
+
+if __name__ == "__main__":
+    main()
