@@ -297,31 +297,47 @@ constexpr int TRACE_BLOCK = 128;
 #ifndef B2_SMEM_STACK
 #define B2_SMEM_STACK 12
 #endif
-constexpr int TRACE_SMEM_STACK = B2_SMEM_STACK;  // entries per thread held in shared memory
+constexpr int TRACE_SMEM_STACK = B2_SMEM_STACK;  // deferred children per lane held in shared memory (even)
+constexpr int TRACE_SPILL = TRACE_SMEM_STACK / 2;
+static_assert(TRACE_SMEM_STACK % 2 == 0 && TRACE_SMEM_STACK >= 4, "spill granularity is half the shared-memory stack");
+#ifndef B2_TRACE_MIN_BLOCKS
+#define B2_TRACE_MIN_BLOCKS 10
+#endif
+#ifndef B2_TRACE_STEPS
+#define B2_TRACE_STEPS 4  // node visits between two warp votes
+#endif
 
-// Deferred-children stack of one lane: the first TRACE_SMEM_STACK entries live in shared memory,
-// laid out [entry][thread] so that lane l always hits bank l whatever its depth (conflict-free: one
-// wavefront per warp access, where a local-memory stack costs one wavefront per distinct depth);
-// deeper entries (rare) overflow to local memory.
-struct DevStack {
-    uint32_t* s_node;  // this thread's column
-    float* s_t;
-    uint32_t l_node[LBVH_STACK - TRACE_SMEM_STACK];
-    float l_t[LBVH_STACK - TRACE_SMEM_STACK];
-    __device__ __forceinline__ void put(int i, uint32_t n, float t)
-    {
-        if (i < TRACE_SMEM_STACK) {
-            s_node[i * TRACE_BLOCK] = n;
-            s_t[i * TRACE_BLOCK] = t;
-        }
-        else {
-            l_node[i - TRACE_SMEM_STACK] = n;
-            l_t[i - TRACE_SMEM_STACK] = t;
-        }
-    }
-    __device__ __forceinline__ float get_t(int i) const { return i < TRACE_SMEM_STACK ? s_t[i * TRACE_BLOCK] : l_t[i - TRACE_SMEM_STACK]; }
-    __device__ __forceinline__ uint32_t get_node(int i) const { return i < TRACE_SMEM_STACK ? s_node[i * TRACE_BLOCK] : l_node[i - TRACE_SMEM_STACK]; }
+// Shared memory of one trace block.  Everything is laid out [row][thread], so lane l always hits bank
+// l whatever row it addresses: every access is one conflict-free wavefront.
+struct TraceSmem {
+    uint32_t node[TRACE_SMEM_STACK][TRACE_BLOCK];  // deferred far children ...
+    float t[TRACE_SMEM_STACK][TRACE_BLOCK];        // ... and their entry tmin
+    float ray[9][TRACE_BLOCK];                     // the lane's exact ray: origin, normalised direction, reciprocals
 };
+
+// Overflow of the shared-memory stack (a lane more than TRACE_SMEM_STACK deferred children deep — rare):
+// the older half moves to a local-memory array and comes back when the shared part runs empty.  Total depth
+// is bounded by LBVH_STACK (tree depth <= key bits + position bits), so `l_node/l_t` cannot overflow.
+// (sp and lsp are passed and returned by value so that they stay in registers in the caller.)
+__device__ __noinline__ int trace_spill(TraceSmem& sm, int tid, uint32_t* l_node, float* l_t, int lsp)
+{
+    for (int k = 0; k < TRACE_SPILL; ++k) {
+        l_node[lsp + k] = sm.node[k][tid];
+        l_t[lsp + k] = sm.t[k][tid];
+        sm.node[k][tid] = sm.node[k + TRACE_SPILL][tid];
+        sm.t[k][tid] = sm.t[k + TRACE_SPILL][tid];
+    }
+    return lsp + TRACE_SPILL;  // sp -= TRACE_SPILL in the caller
+}
+__device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t* l_node, const float* l_t, int lsp)
+{
+    lsp -= TRACE_SPILL;
+    for (int k = 0; k < TRACE_SPILL; ++k) {
+        sm.node[k][tid] = l_node[lsp + k];
+        sm.t[k][tid] = l_t[lsp + k];
+    }
+    return lsp;  // sp = TRACE_SPILL in the caller
+}
 
 // GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
 //
@@ -330,39 +346,56 @@ struct DevStack {
 // when fewer than `fetch_threshold` lanes are still busy the warp claims new rays for its idle lanes
 // from a global counter (one atomicAdd per warp) and carries on.
 //
-// Per-lane state is kept small so that many warps fit: the grid-space ray (6 floats), node, stack
-// pointer, best (t, leaf).  The exact ray (origin, normalised direction, reciprocals) is NOT kept in
-// registers: it is re-derived from the ray record (an L1/L2 hit) on the rare occasions it is needed
-// — when a leaf slot passes the grid test (about once per ray) and in the epilogue — which is
-// bit-identical because it is a pure function of the record.
-#ifndef B2_TRACE_MIN_BLOCKS
-#define B2_TRACE_MIN_BLOCKS 10
-#endif
+// The kernel is bound by instruction issue (ncu: 79 % issue slots busy, profiles/r1_b), so the step is
+// written branch-free where lanes disagree: the pop of a deferred child, the visit and the push are ONE
+// straight instruction stream per step (a lane that has nothing to pop / push just predicates the two
+// shared-memory accesses off); only the rare events — a leaf slot passing the grid test (about once per
+// ray), stack spill / refill — branch.  A popped child that has fallen behind the best hit costs its
+// lane one idle step instead of an inner loop.
+//
+// Per-lane registers: the grid-space ray (6 floats + 6 byte-permute selectors), node, stack pointers, best
+// (t, leaf), pruning limit, ray index.  The exact ray lives in shared memory (written once at fetch) for
+// the exact leaf tests and the epilogue.
 __global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
 k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
              const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
              unsigned long long* counter, int fetch_threshold)
 {
-    const int lane = threadIdx.x & 31;
+    __shared__ TraceSmem sm;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t root = hdr->root;
     const Grid grid = hdr->grid;
-    __shared__ uint32_t sm_node[TRACE_SMEM_STACK * TRACE_BLOCK];
-    __shared__ float sm_t[TRACE_SMEM_STACK * TRACE_BLOCK];
-    TraceState st;
-    DevStack stk;
-    stk.s_node = sm_node + threadIdx.x;
-    stk.s_t = sm_t + threadIdx.x;
+    const float lim0 = float_pred(T);
+    uint32_t l_node[LBVH_STACK];
+    float l_t[LBVH_STACK];
     RayQ q;
+    Hit best;
+    best.t = B2_INF;
+    best.leaf = -1;
+    float lim = lim0;
+    uint32_t cur = REF_EMPTY;
+    int sp = 0, lsp = 0;
     unsigned long long my = 0ull;
     bool active = false;
     bool pending = false;    // this lane's ray is finished but its Raycast is not written yet
     bool exhausted = false;  // warp-uniform: the pool has no rays left
+    auto exact_ray = [&]() {
+        RayPre r;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            r.o[k] = sm.ray[k][tid];
+            r.d[k] = sm.ray[3 + k][tid];
+            r.ninv[k] = sm.ray[6 + k][tid];
+        }
+        return r;
+    };
     for (;;) {
         // Epilogues are deferred to this point so that the lanes that finished since the last fetch
         // run them together instead of one at a time inside the traversal loop.
         if (pending) {
-            finish_raycast<DevOps>(reinterpret_cast<uint32_t*>(out + my), load_ray(rays, my), st.best, leaves);
+            finish_raycast<DevOps>(reinterpret_cast<uint32_t*>(out + my), exact_ray(), best, leaves);
             pending = false;
         }
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -376,9 +409,22 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
                 my = base + (unsigned long long)__popc(need & lt_mask);
                 if (my < n_rays) {
                     const RayPre r = load_ray(rays, my);
-                    trace_begin(st, root);
-                    if (rayq_prepare(r, grid, q)) active = true;
-                    else write_raycast(reinterpret_cast<uint32_t*>(out + my), r, false, 0.0f, 0, 0u);  // provable miss
+                    if (rayq_prepare(r, grid, q)) {
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) {
+                            sm.ray[k][tid] = r.o[k];
+                            sm.ray[3 + k][tid] = r.d[k];
+                            sm.ray[6 + k][tid] = r.ninv[k];
+                        }
+                        best.t = B2_INF;
+                        best.leaf = -1;
+                        lim = lim0;
+                        cur = root;
+                        active = true;
+                    }
+                    else {
+                        write_raycast(reinterpret_cast<uint32_t*>(out + my), r, false, 0.0f, 0, 0u);  // provable miss
+                    }
                 }
             }
             exhausted = base + cnt >= n_rays;
@@ -390,9 +436,34 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
         }
         const int keep_going = exhausted ? 1 : fetch_threshold;
         for (;;) {
-            if (active) {
-                const QNode nd = DevOps::load_qnode(&qnodes[st.cur]);
-                if (!trace_visit<DevOps>(st, stk, q, nd, leaves, T, [&]() { return load_ray(rays, my); })) {
+#pragma unroll
+            for (int step = 0; step < B2_TRACE_STEPS; ++step) {
+                // ---- pop (predicated): a lane without a current node takes its most recent deferred child
+                if (active && cur == REF_EMPTY && sp == 0) {  // rare; lsp > 0 here
+                    lsp = trace_refill(sm, tid, l_node, l_t, lsp);
+                    sp = TRACE_SPILL;
+                }
+                const bool pop = active && cur == REF_EMPTY;
+                sp -= pop ? 1 : 0;
+                const uint32_t pn = sm.node[sp][tid];  // sp < TRACE_SMEM_STACK always: harmless when not popping
+                const float pt = sm.t[sp][tid];
+                if (pop) cur = (pt <= lim) ? pn : REF_EMPTY;
+                // ---- visit
+                if (cur != REF_EMPTY) {
+                    const QNode nd = DevOps::load_qnode(&qnodes[cur]);
+                    const VisitOut v = visit_node<DevOps>(best, lim, q, nd, leaves, T, exact_ray);
+                    if (v.push) {
+                        sm.node[sp][tid] = v.far;
+                        sm.t[sp][tid] = v.tfar;
+                    }
+                    sp += v.push ? 1 : 0;
+                    cur = v.next;
+                }
+                if (sp == TRACE_SMEM_STACK) {  // rare
+                    lsp = trace_spill(sm, tid, l_node, l_t, lsp);
+                    sp = TRACE_SMEM_STACK - TRACE_SPILL;
+                }
+                if (active && cur == REF_EMPTY && sp == 0 && lsp == 0) {
                     active = false;
                     pending = true;
                 }
@@ -477,7 +548,7 @@ struct b2col_ctx {
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
     std::vector<cudaEvent_t> pipe_events;
     size_t e2e_chunk = 2u << 20;
-    int trace_grid = 148 * 8, fetch_threshold = 24;
+    int trace_grid = 148 * 8, fetch_threshold = 25;
     cudaEvent_t events[16] = {};
 };
 

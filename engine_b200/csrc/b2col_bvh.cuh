@@ -358,7 +358,11 @@ B2_HD bool rayq_prepare(const RayPre& r, const Grid& g, RayQ& q)
 B2_HD float cell_plane(uint32_t w, uint32_t sel)
 {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(w, 0x3F000000u, sel));
+    // prmt directly (not __byte_perm, which masks the selector first): the selectors only ever hold
+    // nibbles < 8, so the generic mode picks plain bytes
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0x3F000000u), "r"(sel));
+    return __uint_as_float(r);
 #else
     union { uint32_t u; float f; } cv;
     const uint32_t s16 = (sel == SEL_LO16) ? (w & 0xFFFFu) : (w >> 16);
@@ -370,8 +374,20 @@ B2_HD float cell_plane(uint32_t w, uint32_t sel)
 B2_HD float max3f(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 B2_HD float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
 
-// Grid-space slab test of one slot (wx, wy, wz = the slot's three axis words).
-B2_HD bool qslab(const RayQ& q, uint32_t wx, uint32_t wy, uint32_t wz, float T, float& tmin_out)
+// Largest float below a positive finite T.
+B2_HD float float_pred(float T)
+{
+    union { uint32_t u; float f; } cv;
+    cv.f = T;
+    cv.u -= 1u;
+    return cv.f;
+}
+
+// Grid-space slab test of one slot (wx, wy, wz = the slot's three axis words) against the pruning limit
+//     lim = best.t  once a hit exists (every hit has tmin < T),  else the largest float below T,
+// so that  tmin <= lim  <=>  tmin <= best.t && tmin < T  (the reference's cut-off, :99, and the
+// nearest-hit pruning in one comparison; equality must pass: an equal tmin may hide a later tie winner).
+B2_HD bool qslab(const RayQ& q, uint32_t wx, uint32_t wy, uint32_t wz, float lim, float& tmin_out)
 {
     const float tnx = fmaf(cell_plane(wx, q.sel_near[0]), q.n[0], q.c[0]);
     const float tny = fmaf(cell_plane(wy, q.sel_near[1]), q.n[1], q.c[1]);
@@ -382,95 +398,59 @@ B2_HD bool qslab(const RayQ& q, uint32_t wx, uint32_t wy, uint32_t wz, float T, 
     const float tmin = max3f(tnx, tny, tnz);
     const float tmax = min3f(tfx, tfy, tfz);
     tmin_out = tmin;
-    return (tmax >= fmaxf(0.0f, tmin)) && (tmin < T);
-}
-
-// Traversal state of one ray, advanced one node visit at a time so that a persistent warp can
-// retire finished rays and fetch new ones between steps (k_trace_lbvh in b2col.cu).  The stack of
-// deferred far children (node, entry tmin) is a policy: a plain array on the host, shared memory
-// with a local-memory overflow on the device.
-struct TraceState {
-    uint32_t cur;
-    int sp;
-    Hit best;
-};
-
-struct ArrayStack {
-    uint32_t node[LBVH_STACK];
-    float t[LBVH_STACK];
-    B2_HD void put(int i, uint32_t n, float tt)
-    {
-        node[i] = n;
-        t[i] = tt;
-    }
-    B2_HD float get_t(int i) const { return t[i]; }
-    B2_HD uint32_t get_node(int i) const { return node[i]; }
-};
-
-B2_HD void trace_begin(TraceState& st, uint32_t root)
-{
-    st.cur = root;
-    st.sp = 0;
-    st.best.t = B2_INF;
-    st.best.leaf = -1;
+    return (tmax >= tmin) && (tmax >= 0.0f) && (tmin <= lim);
 }
 
 // Exact test of a candidate leaf (the reference's RayBoxIntersection on the exact world AABB).
-B2_HD void leaf_candidate(Hit& best, const RayPre& r, const LeafRec& rec, uint32_t ref, float T)
+// Returns true when the leaf became the best hit.
+B2_HD bool leaf_candidate(Hit& best, const RayPre& r, const LeafRec& rec, uint32_t ref, float T)
 {
     const SlabT s = slab(r, rec.lo, rec.hi);
-    if (!slab_hit(s, T)) return;
+    if (!slab_hit(s, T)) return false;
     const int32_t leaf = (int32_t)(ref & ~LEAF_BIT);
     if (s.tmin < best.t || (s.tmin == best.t && leaf > best.leaf)) {
         best.t = s.tmin;
         best.leaf = leaf;
-    }
-}
-
-// Visit node st.cur (already loaded into nd), then select the next node.  RayFn() yields the exact
-// ray (only evaluated when a leaf slot passes the grid test — about once per ray).  Returns false when
-// the traversal of this ray is complete.
-template <class Ops, class Stack, class RayFn>
-B2_HD bool trace_visit(TraceState& st, Stack& stk, const RayQ& q, const QNode& nd, const LeafRec* leaves, float T, RayFn exact_ray)
-{
-    float ta, tb;
-    bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], T, ta);
-    bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], T, tb);
-    ha = ha && (ta <= st.best.t);
-    hb = hb && (tb <= st.best.t);
-    const uint32_t ra = nd.w[6], rb = nd.w[7];
-    if ((ha && (ra & LEAF_BIT)) || (hb && (rb & LEAF_BIT))) {
-        const RayPre r = exact_ray();
-        if (ha && (ra & LEAF_BIT)) {
-            leaf_candidate(st.best, r, Ops::load_leaf(&leaves[ra & ~LEAF_BIT]), ra, T);
-            ha = false;
-        }
-        if (hb && (rb & LEAF_BIT)) {
-            leaf_candidate(st.best, r, Ops::load_leaf(&leaves[rb & ~LEAF_BIT]), rb, T);
-            hb = false;
-        }
-        ha = ha && (ta <= st.best.t);
-        hb = hb && (tb <= st.best.t);
-    }
-    if (ha && hb) {
-        const bool a_first = !(tb < ta);
-        stk.put(st.sp, a_first ? rb : ra, a_first ? tb : ta);
-        ++st.sp;
-        st.cur = a_first ? ra : rb;
         return true;
-    }
-    if (ha || hb) {
-        st.cur = ha ? ra : rb;
-        return true;
-    }
-    while (st.sp > 0) {
-        --st.sp;
-        if (stk.get_t(st.sp) <= st.best.t) {
-            st.cur = stk.get_node(st.sp);
-            return true;
-        }
     }
     return false;
+}
+
+// One node visit, stack-free: tests both slots, resolves leaf slots exactly (updating best / lim) and
+// tells the caller where to go.  RayFn() yields the exact ray; it is only evaluated when a leaf slot
+// passes the grid test — about once per ray.
+//   next == REF_EMPTY : nothing to descend into, the caller pops
+//   push              : `far` (entry tmin `tfar`) is to be deferred, `next` is the nearer child
+struct VisitOut {
+    uint32_t next, far;
+    float tfar;
+    bool push;
+};
+
+template <class Ops, class RayFn>
+B2_HD VisitOut visit_node(Hit& best, float& lim, const RayQ& q, const QNode& nd, const LeafRec* leaves, float T, RayFn exact_ray)
+{
+    float ta, tb;
+    bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], lim, ta);
+    bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], lim, tb);
+    const uint32_t ra = nd.w[6], rb = nd.w[7];
+    const bool la = ha && (ra & LEAF_BIT), lb = hb && (rb & LEAF_BIT);
+    if (la || lb) {
+        const RayPre r = exact_ray();
+        bool better = false;
+        if (la) better = leaf_candidate(best, r, Ops::load_leaf(&leaves[ra & ~LEAF_BIT]), ra, T);
+        if (lb) better = leaf_candidate(best, r, Ops::load_leaf(&leaves[rb & ~LEAF_BIT]), rb, T) || better;
+        if (better) lim = best.t;
+        ha = ha && !la && (ta <= lim);
+        hb = hb && !lb && (tb <= lim);
+    }
+    VisitOut o;
+    const bool a_first = !(tb < ta);
+    o.push = ha && hb;
+    o.far = a_first ? rb : ra;
+    o.tfar = a_first ? tb : ta;
+    o.next = o.push ? (a_first ? ra : rb) : (ha ? ra : (hb ? rb : REF_EMPTY));
+    return o;
 }
 
 // Raycast epilogue for the winner: the exact slab test is repeated on the winning leaf record to obtain
@@ -487,20 +467,39 @@ B2_HD void finish_raycast(uint32_t* out9, const RayPre& r, const Hit& best, cons
     write_raycast(out9, r, true, s.tmin, slab_side(s), rec.entity);
 }
 
-// Whole-ray form (host emulation; the device kernel interleaves trace_visit with ray fetching).
+// Whole-ray form with a plain array stack (host emulation; the device kernel, k_trace_lbvh in b2col.cu,
+// runs the same visit_node per step with a shared-memory stack and interleaves ray fetching).  A
+// deferred child whose entry tmin has meanwhile fallen behind the best hit is dropped when popped.
 template <class Ops>
 B2_HD Hit trace_lbvh(const RayPre& r, const Grid& grid, const QNode* qnodes, const LeafRec* leaves, uint32_t root, float T)
 {
-    TraceState st;
-    ArrayStack stk;
-    trace_begin(st, root);
+    Hit best;
+    best.t = B2_INF;
+    best.leaf = -1;
     RayQ q;
-    if (!rayq_prepare(r, grid, q)) return st.best;
+    if (!rayq_prepare(r, grid, q)) return best;
+    float lim = float_pred(T);
+    uint32_t s_node[LBVH_STACK];
+    float s_t[LBVH_STACK];
+    int sp = 0;
+    uint32_t cur = root;
     for (;;) {
-        const QNode nd = Ops::load_qnode(&qnodes[st.cur]);
-        if (!trace_visit<Ops>(st, stk, q, nd, leaves, T, [&]() { return r; })) break;
+        if (cur == REF_EMPTY) {
+            if (sp == 0) break;
+            --sp;
+            if (!(s_t[sp] <= lim)) continue;
+            cur = s_node[sp];
+        }
+        const QNode nd = Ops::load_qnode(&qnodes[cur]);
+        const VisitOut v = visit_node<Ops>(best, lim, q, nd, leaves, T, [&]() { return r; });
+        if (v.push) {
+            s_node[sp] = v.far;
+            s_t[sp] = v.tfar;
+            ++sp;
+        }
+        cur = v.next;
     }
-    return st.best;
+    return best;
 }
 
 // ---- reference-topology traversal ---------------------------------------------------------------

@@ -166,8 +166,9 @@ extern "C" void emu_visit_histogram(const QNode* qnodes, const LeafRec* leaves, 
             ++hist[depth < max_depth ? depth : max_depth - 1];
             const QNode nd = qnodes[cur];
             float ta, tb;
-            bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], T, ta) && ta <= best.t;
-            bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], T, tb) && tb <= best.t;
+            const float lim = best.leaf >= 0 ? best.t : float_pred(T);
+            bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], lim, ta);
+            bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], lim, tb);
             if (ha && (nd.w[6] & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, r, leaves[nd.w[6] & ~LEAF_BIT], nd.w[6], T); ha = false; }
             if (hb && (nd.w[7] & LEAF_BIT)) { ++*leaf_tests; leaf_candidate(best, r, leaves[nd.w[7] & ~LEAF_BIT], nd.w[7], T); hb = false; }
             ha = ha && ta <= best.t;
