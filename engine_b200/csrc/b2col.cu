@@ -68,6 +68,30 @@ struct DevOps {
         q[0] = make_uint4(n.w[0], n.w[1], n.w[2], n.w[3]);
         q[1] = make_uint4(n.w[4], n.w[5], n.w[6], n.w[7]);
     }
+    static __device__ __forceinline__ void store_ref(QNode* p, int side, uint32_t ref) { p->w[6 + side] = ref; }
+    static __device__ __forceinline__ void store_qboxes(QNode* p, const uint32_t* left, const uint32_t* right)
+    {
+        *reinterpret_cast<uint4*>(p) = make_uint4(left[0], left[1], left[2], right[0]);
+        *reinterpret_cast<uint2*>(&p->w[4]) = make_uint2(right[1], right[2]);
+    }
+    // The arrival exchange of build_from_leaf_q: one relaxed 128-bit atomic at GPU scope (ATOMG.E.EXCH.128).
+    // Relaxed is enough: everything the sibling needs is the exchanged value itself.
+    static __device__ __forceinline__ Xch exchange(Xch* p, const Xch& v)
+    {
+        const unsigned long long lo = (unsigned long long)v.w[0] | ((unsigned long long)v.w[1] << 32);
+        const unsigned long long hi = (unsigned long long)v.w[2] | ((unsigned long long)v.w[3] << 32);
+        unsigned long long olo, ohi;
+        asm volatile("{\n\t.reg .b128 v, o;\n\tmov.b128 v, {%2, %3};\n\tatom.relaxed.gpu.global.exch.b128 o, [%4], v;\n\tmov.b128 {%0, %1}, o;\n\t}"
+                     : "=l"(olo), "=l"(ohi)
+                     : "l"(lo), "l"(hi), "l"(p)
+                     : "memory");
+        Xch o;
+        o.w[0] = (uint32_t)olo;
+        o.w[1] = (uint32_t)(olo >> 32);
+        o.w[2] = (uint32_t)ohi;
+        o.w[3] = (uint32_t)(ohi >> 32);
+        return o;
+    }
     static __device__ __forceinline__ void store_leaf(LeafRec* p, const LeafRec& r)
     {
         float4* q = reinterpret_cast<float4*>(p);
@@ -226,10 +250,10 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
 }
 
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
-// registers here anyway), and reset of the per-node arrival words used by k_build.
+// registers here anyway), and reset of the per-node arrival/exchange words used by k_build.
 __global__ void __launch_bounds__(256)
 k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
-         uint32_t* __restrict__ vals, uint32_t* __restrict__ other_bound, uint32_t* ghist)
+         uint32_t* __restrict__ vals, uint4* __restrict__ xch, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
     for (int p = 0; p < passes; ++p) shist[p][threadIdx.x] = 0u;
@@ -251,7 +275,7 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
         const uint64_t key = morton_key(lo, hi, smin, sinv, bits, drop);
         keys[i] = key;
         vals[i] = i;
-        other_bound[i] = UNVISITED;
+        xch[i] = make_uint4(0u, 0u, 0u, UNVISITED);  // arrival word of node i: nobody has arrived
         for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
     }
     __syncthreads();
@@ -272,14 +296,27 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
     }
 }
 
+// LBVH hierarchy + bounds, production form: traversal structure only, merged in grid space (b2col_bvh.cuh).
 __global__ void __launch_bounds__(256)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
-        const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr)
+        const uint32_t* __restrict__ col_entity, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const Grid grid = hdr->grid;  // written by k_morton
-    build_from_leaf<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, nodes, other_bound, grid, qnodes, leaves, &hdr->root);
+    build_from_leaf_q<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, xch, grid, qnodes, leaves, &hdr->root);
+}
+
+// Same hierarchy with exact (full-precision) two-slot nodes: only run on demand, as the source of the
+// BiTreeNode export (b2col_export_bitreenode).  Writes nothing into the traversal structure.
+__global__ void __launch_bounds__(256)
+k_build_exact(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
+              const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, const BlobHeader* hdr, uint32_t* root_out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Grid grid = hdr->grid;
+    build_from_leaf<DevOps>(i, n, keys, sorted_prim, world_aabb, col_entity, nodes, other_bound, grid, (QNode*)nullptr, (LeafRec*)nullptr, root_out);
 }
 
 // Ray prologue (GetRaycast :162 + the hoisted reciprocals of :65).  Deliberately NOT inlined: it runs
@@ -531,8 +568,9 @@ struct b2col_ctx {
     bool have_colliders = false;
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
-    DevBuf d_keys[2], d_vals[2], d_other_bound, d_zero;  // d_zero: histograms, tickets, look-back words
-    DevBuf d_nodes_full;  // full-precision two-slot nodes: sibling exchange during the build, source of the BiTreeNode export
+    DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
+    DevBuf d_nodes_full, d_other_bound;  // export only: full-precision two-slot nodes + their arrival words (k_build_exact)
+    bool exact_nodes_valid = false;      // d_nodes_full matches the tree in the blob
     size_t zero_bytes = 0;
     int sorted_side = 0;
     // traversal structure: one allocation [BlobHeader | QNode x (N-1) | LeafRec x N]
@@ -712,7 +750,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
+                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
@@ -875,8 +913,8 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(ensure(ctx, ctx->d_keys[1], (size_t)n * 8));
     GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
-    GUARD(ensure(ctx, ctx->d_other_bound, (size_t)n * 4));
-    GUARD(ensure(ctx, ctx->d_nodes_full, (size_t)(n > 1 ? n - 1 : 1) * sizeof(Node)));
+    GUARD(ensure(ctx, ctx->d_xch, (size_t)n * sizeof(Xch)));
+    ctx->exact_nodes_valid = false;
     // Morton key width: the radix sort costs one pass per 8 key bits, and at ~1M colliders each pass is
     // latency-bound (~20 us), so the key is only as wide as the collider count needs: 32 bits (11,11,10 per
     // axis, 4.3e9 cells) up to 2M colliders, 40 bits up to 32M, 48 beyond; an explicit
@@ -910,7 +948,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
         LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T, ctx->d_keys[0].as<uint64_t>(),
-               ctx->d_vals[0].as<uint32_t>(), ctx->d_other_bound.as<uint32_t>(), ghist);
+               ctx->d_vals[0].as<uint32_t>(), ctx->d_xch.as<uint4>(), ghist);
     }
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
@@ -921,8 +959,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     }
     ctx->sorted_side = side;
     LAUNCH(ctx, k_build, cdiv(n, 256), 256, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
-           ctx->d_col_entity.as<uint32_t>(), ctx->d_nodes_full.as<Node>(), ctx->d_other_bound.as<uint32_t>(), blob_qnodes(ctx), blob_leaves(ctx, n),
-           blob_hdr(ctx));
+           ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx));
     ctx->have_tree = true;
     return B2COL_OK;
 }
@@ -1027,6 +1064,15 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
         h_out[0].type2 = B2COL_NODE_EMPTY;
         *n_out = 1;
         return B2COL_OK;
+    }
+    if (!ctx->exact_nodes_valid) {  // full-precision nodes are only built when somebody asks for the reference-format tree
+        GUARD(ensure(ctx, ctx->d_other_bound, (size_t)n * 4 + 4));
+        GUARD(ensure(ctx, ctx->d_nodes_full, (size_t)(n - 1) * sizeof(Node)));
+        CU(cudaMemsetAsync(ctx->d_other_bound.p, 0xFF, (size_t)n * 4 + 4, ctx->stream));
+        LAUNCH(ctx, k_build_exact, cdiv(n, 256), 256, n, ctx->d_keys[ctx->sorted_side].as<uint64_t>(), ctx->d_vals[ctx->sorted_side].as<uint32_t>(),
+               ctx->d_world_aabb.as<Aabb24>(), ctx->d_col_entity.as<uint32_t>(), ctx->d_nodes_full.as<Node>(), ctx->d_other_bound.as<uint32_t>(), blob_hdr(ctx),
+               ctx->d_other_bound.as<uint32_t>() + n);
+        ctx->exact_nodes_valid = true;
     }
     const size_t cand = 2 * (size_t)n - 1;
     DevBuf d_nodes, d_used;

@@ -101,6 +101,30 @@ B2_HD QNode quantise_node(const Slot& a, const Slot& b, const Grid& g)
     return n;
 }
 
+// One box on the grid: per axis (lo | hi << 16), the layout of a QNode slot.  Quantisation is monotone,
+// so min/max commute with it: the grid box of a union of boxes is the per-plane min/max of their grid
+// boxes — the hierarchy can therefore be merged entirely in grid space (build_from_leaf_q).
+struct QBox {
+    uint32_t w[3];
+};
+B2_HD QBox quantise_box(const float* lo, const float* hi, const Grid& g)
+{
+    QBox q;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) q.w[k] = quant_lo(lo[k], g, k) | (quant_hi(hi[k], g, k) << 16);
+    return q;
+}
+B2_HD uint32_t qplane_merge(uint32_t a, uint32_t b)  // min of the low halves, max of the high halves
+{
+#if defined(__CUDA_ARCH__)
+    return (__vminu2(a, b) & 0xFFFFu) | (__vmaxu2(a, b) & 0xFFFF0000u);  // VIMNMX.U16x2
+#else
+    const uint32_t lo = (a & 0xFFFFu) < (b & 0xFFFFu) ? (a & 0xFFFFu) : (b & 0xFFFFu);
+    const uint32_t hi = (a >> 16) > (b >> 16) ? (a >> 16) : (b >> 16);
+    return lo | (hi << 16);
+#endif
+}
+
 // ---- LBVH hierarchy + bounds in ONE bottom-up pass ---------------------------------------------
 // Replaces BuildNode (reference src/system_collisions.cpp:205-376) by a different algorithm: the
 // tree of Karras 2012 (radix tree over sorted Morton keys, ties broken by position), emitted
@@ -116,17 +140,18 @@ struct Delta {
     uint64_t hi;
     uint32_t lo;
 };
-B2_HD Delta key_delta(const uint64_t* keys, uint32_t i)
+template <class Key>
+B2_HD Delta key_delta(const Key* keys, uint32_t i)
 {
     Delta d;
-    d.hi = keys[i] ^ keys[i + 1];
+    d.hi = (uint64_t)(keys[i] ^ keys[i + 1]);
     d.lo = d.hi ? 0u : (i ^ (i + 1u));  // duplicate keys: fall back to the position bits
     return d;
 }
 B2_HD bool delta_less(const Delta& a, const Delta& b) { return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo); }
 
-template <class Ops>
-B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
+template <class Ops, class Key>
+B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
                            const uint32_t* col_entity, Node* nodes, uint32_t* other_bound, const Grid& grid, QNode* qnodes, LeafRec* leaves,
                            uint32_t* root_out)
 {
@@ -142,7 +167,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
     }
     rec.entity = col_entity[prim];
     rec.prim = prim;
-    Ops::store_leaf(&leaves[i], rec);
+    if (leaves) Ops::store_leaf(&leaves[i], rec);
     if (n == 1) {  // a lone leaf still gets a node: {leaf, nothing} (cf. the reference's {Entity,Empty}, :363-369)
         Slot a, b;
 #pragma unroll
@@ -158,7 +183,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
         b.aux = 0u;
         Ops::store_slot(&nodes[0].s[0], a);
         Ops::store_slot(&nodes[0].s[1], b);
-        Ops::store_qnode(&qnodes[0], quantise_node(a, a, grid));  // both slots = the leaf: an empty slot has no grid encoding
+        if (qnodes) Ops::store_qnode(&qnodes[0], quantise_node(a, a, grid));  // both slots = the leaf: an empty slot has no grid encoding
         *root_out = 0u;
         return;
     }
@@ -182,7 +207,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
         const uint32_t other = Ops::arrive(&other_bound[p], is_left ? l : r);  // release my slot / acquire the sibling's
         if (other == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
         const Slot sib = Ops::load_slot_coherent(&nodes[p].s[is_left ? 1 : 0]);
-        Ops::store_qnode(&qnodes[p], is_left ? quantise_node(mine, sib, grid) : quantise_node(sib, mine, grid));
+        if (qnodes) Ops::store_qnode(&qnodes[p], is_left ? quantise_node(mine, sib, grid) : quantise_node(sib, mine, grid));
         if (is_left) r = other;
         else l = other;
 #pragma unroll
@@ -190,6 +215,73 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const uint64_t* keys, const u
             box.lo[k] = fminf(box.lo[k], sib.lo[k]);
             box.hi[k] = fmaxf(box.hi[k], sib.hi[k]);
         }
+        ref = p;
+        if (l == 0u && r == n - 1u) {
+            *root_out = p;
+            return;
+        }
+    }
+}
+
+// Production form of the same pass: builds ONLY the traversal structure (QNodes + leaf records), merging
+// boxes in grid space.  A child's whole message to its sibling — its grid box (3 words) and the far bound of
+// its range (1 word) — is 128 bits, so it travels INSIDE the arrival atomic (one 128-bit exchange per child per
+// node): the first arriver deposits its message and retires, the second receives it as the exchange's return
+// value.  No data is published through ordinary memory, hence no fences; and per climbed level a thread
+// issues one exchange, two key-delta comparisons and three packed min/max.  Each arriver stores its own child
+// ref into the node (nobody reads refs during the build), the second arriver stores both boxes.
+// Produces bit-identical QNodes to build_from_leaf (quantisation commutes with min/max) for NaN-free boxes;
+// with NaN coordinates both are conservative but may differ (fminf drops a NaN that quant_lo widens).
+struct Xch {
+    uint32_t w[4];  // grid box (3 words), range bound; w[3] == UNVISITED: nobody has arrived yet
+};
+
+template <class Ops, class Key>
+B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
+                             const uint32_t* col_entity, Xch* xch, const Grid& grid, QNode* qnodes, LeafRec* leaves, uint32_t* root_out)
+{
+    const uint32_t prim = sorted_prim[i];
+    LeafRec rec;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        rec.lo[k] = world_aabb[prim].lo[k];
+        rec.hi[k] = world_aabb[prim].hi[k];
+    }
+    rec.entity = col_entity[prim];
+    rec.prim = prim;
+    Ops::store_leaf(&leaves[i], rec);
+    QBox box = quantise_box(rec.lo, rec.hi, grid);
+    if (n == 1) {  // a lone leaf still gets a node; both slots = the leaf (an empty slot has no grid encoding)
+        QNode nd;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) nd.w[k] = nd.w[3 + k] = box.w[k];
+        nd.w[6] = LEAF_BIT | 0u;
+        nd.w[7] = LEAF_BIT | 0u;
+        Ops::store_qnode(&qnodes[0], nd);
+        *root_out = 0u;
+        return;
+    }
+    uint32_t l = i, r = i;
+    uint32_t ref = LEAF_BIT | i;
+    for (;;) {
+        bool is_left;
+        if (l == 0u) is_left = true;
+        else if (r == n - 1u) is_left = false;
+        else is_left = delta_less(key_delta(keys, r), key_delta(keys, l - 1u));
+        const uint32_t p = is_left ? r : l - 1u;
+        Ops::store_ref(&qnodes[p], is_left ? 0 : 1, ref);
+        Xch mine;
+        mine.w[0] = box.w[0];
+        mine.w[1] = box.w[1];
+        mine.w[2] = box.w[2];
+        mine.w[3] = is_left ? l : r;
+        const Xch sib = Ops::exchange(&xch[p], mine);
+        if (sib.w[3] == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
+        Ops::store_qboxes(&qnodes[p], is_left ? mine.w : sib.w, is_left ? sib.w : mine.w);
+        if (is_left) r = sib.w[3];
+        else l = sib.w[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) box.w[k] = qplane_merge(box.w[k], sib.w[k]);
         ref = p;
         if (l == 0u && r == n - 1u) {
             *root_out = p;

@@ -26,6 +26,20 @@ struct HostOps {
         return o;
     }
     static void store_qnode(QNode* p, const QNode& n) { *p = n; }
+    static void store_ref(QNode* p, int side, uint32_t ref) { p->w[6 + side] = ref; }
+    static void store_qboxes(QNode* p, const uint32_t* left, const uint32_t* right)
+    {
+        for (int k = 0; k < 3; ++k) {
+            p->w[k] = left[k];
+            p->w[3 + k] = right[k];
+        }
+    }
+    static Xch exchange(Xch* p, const Xch& v)
+    {
+        const Xch o = *p;
+        *p = v;
+        return o;
+    }
     static void store_leaf(LeafRec* p, const LeafRec& r) { *p = r; }
     static QNode load_qnode(const QNode* p) { return *p; }
     static LeafRec load_leaf(const LeafRec* p) { return *p; }
@@ -58,7 +72,7 @@ void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, 
 // `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
 // that the result does not depend on thread scheduling.
 void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, int drop, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
-               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order)
+               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order, int* mismatch)
 {
     if (n == 0) return;
     float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -90,9 +104,26 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
         sorted_prim[i] = idx[i];
         sorted_keys[i] = keys[idx[i]];
     }
+    // exact two-slot nodes (export path) ...
     std::vector<uint32_t> other(n, UNVISITED);
+    std::vector<QNode> q_exact(n > 1 ? n - 1 : 1);
     for (uint32_t t = 0; t < n; ++t)
-        build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), grid, qnodes, leaves, root);
+        build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), grid, q_exact.data(),
+                                 (LeafRec*)nullptr, root);
+    // ... and the traversal structure by the production builder (grid-space merge, visited in reverse order to
+    // vary which child arrives first); the two must agree on NaN-free input
+    Xch none;
+    none.w[0] = none.w[1] = none.w[2] = 0u;
+    none.w[3] = UNVISITED;
+    std::vector<Xch> xch(n, none);
+    uint32_t root_q = 0;
+    for (uint32_t t = 0; t < n; ++t)
+        build_from_leaf_q<HostOps>(order ? order[n - 1 - t] : n - 1 - t, n, sorted_keys, sorted_prim, world_aabb, col_entity, xch.data(), grid, qnodes, leaves, &root_q);
+    *mismatch = (root_q != *root) ? 1 : 0;
+    bool nan_free = true;
+    for (uint32_t i = 0; i < n && nan_free; ++i)
+        for (int k = 0; k < 3; ++k) nan_free = nan_free && world_aabb[i].lo[k] == world_aabb[i].lo[k] && world_aabb[i].hi[k] == world_aabb[i].hi[k];
+    if (nan_free && std::memcmp(q_exact.data(), qnodes, q_exact.size() * sizeof(QNode)) != 0) *mismatch |= 2;
 }
 
 void emu_trace_lbvh(const QNode* qnodes, const LeafRec* leaves, const Grid* grid, uint32_t root, uint32_t n_leaves, const float* rays6, size_t n_rays,

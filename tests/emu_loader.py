@@ -67,10 +67,12 @@ class Emu:
         sorted_prim = np.zeros(n, np.uint32)
         sorted_keys = np.zeros(n, np.uint64)
         root = C.c_uint32(0)
+        mismatch = C.c_int(0)
         if order is not None:
             order = np.ascontiguousarray(order, np.uint32)
         self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_int(drop), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
-                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order))
+                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order), C.byref(mismatch))
+        assert mismatch.value == 0, f"grid-space builder disagrees with the exact builder (flags {mismatch.value})"
         return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
                     sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
 

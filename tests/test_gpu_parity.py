@@ -33,6 +33,20 @@ def emu():
     return Emu()
 
 
+def read_blob(cs, n):
+    """(qnodes [n-1, 8] u32, leaf records [n, 8] u32) of the tree currently in the context's BVH blob"""
+    _, nbytes = cs.bvh_blob()
+    t = torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{cs.device}")
+    cs.bvh_export_blob(t, nbytes)
+    cs.sync()
+    words = t.cpu().numpy().view(np.uint32)
+    assert words[1] == n
+    n_nodes = max(n - 1, 1)
+    q = words[64 : 64 + 8 * n_nodes].reshape(n_nodes, 8)
+    lf = words[64 + 8 * n_nodes : 64 + 8 * n_nodes + 8 * n].reshape(n, 8)
+    return q, lf
+
+
 # ---------------------------------------------------------------------------------------------
 # golden fixtures (outputs of the real reference)
 # ---------------------------------------------------------------------------------------------
@@ -158,7 +172,11 @@ def test_build_matches_host_restatement(CollisionSystem, emu, n, bits_per_axis):
     assert np.array_equal(order, tree["sorted_prim"]), "sorted order differs from a stable sort of the same keys"
     st = cs.stats()
     assert st["root"] == tree["root"] and st["n_internal_nodes"] == n - 1
-    if n <= 300000:
+    # the traversal structure itself (built in grid space with 128-bit exchanges on the device), bit for bit
+    qnodes, leaves = read_blob(cs, n)
+    assert np.array_equal(qnodes, tree["qnodes"]["w"]), "quantised nodes differ from the host restatement"
+    assert np.array_equal(leaves.view(np.uint32), tree["leaves"].view(np.uint32).reshape(-1, 8)), "leaf records differ"
+    if n <= 300000:  # the reference-format export (exact boxes, built on demand by k_build_exact)
         assert (cs.bvh.view(np.uint8) == emu.export(tree).view(np.uint8)).all()
 
 

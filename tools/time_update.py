@@ -8,7 +8,8 @@ from engine_b200.collision import CollisionSystem  # noqa: E402
 
 
 def main():
-    for name, scene in (("flat 1M", synth.uniform_boxes(1_000_000)), ("hier 1M (1000 roots, depth 3)", synth.hierarchy_scene(1_000_000, 1000))):
+    n = int(os.environ.get("N_COL", 1_000_000))
+    for name, scene in ((f"flat {n}", synth.uniform_boxes(n)), (f"hier {n} (1000 roots, depth 3)", synth.hierarchy_scene(n, 1000))):
         cs = CollisionSystem()
         cs.set_scene(scene)
         for _ in range(5):
