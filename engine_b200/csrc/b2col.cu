@@ -932,7 +932,8 @@ b2col_status b2col_update(b2col_ctx* ctx)
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t hist_bytes = (size_t)RS_MAX_PASSES * RS_RADIX * 4;
     const size_t ticket_bytes = 64;
-    const size_t lb_bytes = (size_t)ctx->passes * tiles * RS_RADIX * 4;
+    const size_t lb_words_per_pass = ((size_t)tiles + (tiles + LB_GROUP - 1) / LB_GROUP) * RS_RADIX;  // tile counts + group status
+    const size_t lb_bytes = (size_t)ctx->passes * lb_words_per_pass * 4;
     ctx->zero_bytes = hist_bytes + ticket_bytes + lb_bytes;
     GUARD(ensure(ctx, ctx->d_zero, ctx->zero_bytes));
     CU(cudaMemsetAsync(ctx->d_zero.p, 0, ctx->zero_bytes, ctx->stream));
@@ -953,8 +954,8 @@ b2col_status b2col_update(b2col_ctx* ctx)
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
         LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
-               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, p * RS_BITS, ghist + p * RS_RADIX,
-               lookback + (size_t)p * tiles * RS_RADIX, tickets + p);
+               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
+               lookback + (size_t)p * lb_words_per_pass, tickets + p);
         side ^= 1;
     }
     ctx->sorted_side = side;

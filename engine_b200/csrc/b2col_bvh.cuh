@@ -224,17 +224,66 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32
 }
 
 // Production form of the same pass: builds ONLY the traversal structure (QNodes + leaf records), merging
-// boxes in grid space.  A child's whole message to its sibling — its grid box (3 words) and the far bound of
-// its range (1 word) — is 128 bits, so it travels INSIDE the arrival atomic (one 128-bit exchange per child per
-// node): the first arriver deposits its message and retires, the second receives it as the exchange's return
-// value.  No data is published through ordinary memory, hence no fences; and per climbed level a thread
-// issues one exchange, two key-delta comparisons and three packed min/max.  Each arriver stores its own child
-// ref into the node (nobody reads refs during the build), the second arriver stores both boxes.
-// Produces bit-identical QNodes to build_from_leaf (quantisation commutes with min/max) for NaN-free boxes;
-// with NaN coordinates both are conservative but may differ (fminf drops a NaN that quant_lo widens).
+// boxes in grid space.  A child's whole message to its sibling fits in 128 bits, so it travels INSIDE the
+// arrival atomic (one 128-bit exchange per child per node): the first arriver deposits its message and
+// retires, the second receives it as the exchange's return value.  No data is published through ordinary
+// memory, hence no fences.  The message holds
+//     the child's grid box            6 x 15 bits   (the always-set bit 15 of each plane is reused as payload)
+//     the far bound of its range      31 bits
+//     the split LEVEL beyond that bound  7 bits
+// where level(i) = 64 + msb(key[i] ^ key[i+1]), or msb(i ^ (i+1)) for duplicate keys, 127 = array end, is the
+// delta of Karras' tree reduced to what the climb compares: in any state the climb reaches, all splits
+// inside [l,r] are lower than both outer splits, and two outer splits with the same top bit would force
+// key[l] and key[r] to differ in that bit — so the outer deltas always differ in their top bit and the level
+// decides exactly as the full delta does (same tree as build_from_leaf; the tests compare them).  With the
+// levels in the message a thread reads keys only once (its own leaf's two neighbours, coalesced); per climbed
+// level it issues one exchange, one 4-byte and one 24-byte store, and three packed min/max.
 struct Xch {
-    uint32_t w[4];  // grid box (3 words), range bound; w[3] == UNVISITED: nobody has arrived yet
+    uint32_t w[4];  // w[3] == UNVISITED: nobody has arrived yet
 };
+constexpr uint32_t LEVEL_END = 127u;
+
+B2_HD uint32_t msb32(uint32_t x)
+{
+#if defined(__CUDA_ARCH__)
+    return 31u - (uint32_t)__clz((int)x);
+#else
+    return 31u - (uint32_t)__builtin_clz(x);
+#endif
+}
+B2_HD uint32_t msb64(uint64_t x)
+{
+#if defined(__CUDA_ARCH__)
+    return 63u - (uint32_t)__clzll((long long)x);
+#else
+    return 63u - (uint32_t)__builtin_clzll(x);
+#endif
+}
+// level of the split between sorted positions i and i+1 (ka, kb = their keys)
+B2_HD uint32_t split_level(uint64_t ka, uint64_t kb, uint32_t i)
+{
+    const uint64_t x = ka ^ kb;
+    return x ? 64u + msb64(x) : msb32(i ^ (i + 1u));
+}
+
+B2_HD Xch xch_pack(const QBox& box, uint32_t bound, uint32_t level)
+{
+    Xch m;
+    m.w[0] = (box.w[0] & 0x7FFF7FFFu) | ((level & 1u) << 15) | ((level & 2u) << 30);
+    m.w[1] = (box.w[1] & 0x7FFF7FFFu) | ((level & 4u) << 13) | ((level & 8u) << 28);
+    m.w[2] = (box.w[2] & 0x7FFF7FFFu) | ((level & 16u) << 11) | ((level & 32u) << 26);
+    m.w[3] = bound | ((level & 64u) << 25);
+    return m;
+}
+B2_HD void xch_unpack(const Xch& m, QBox& box, uint32_t& bound, uint32_t& level)
+{
+    level = ((m.w[0] >> 15) & 1u) | ((m.w[0] >> 30) & 2u) | ((m.w[1] >> 13) & 4u) | ((m.w[1] >> 28) & 8u) | ((m.w[2] >> 11) & 16u) |
+            ((m.w[2] >> 26) & 32u) | ((m.w[3] >> 25) & 64u);
+    box.w[0] = m.w[0] | 0x80008000u;
+    box.w[1] = m.w[1] | 0x80008000u;
+    box.w[2] = m.w[2] | 0x80008000u;
+    bound = m.w[3] & 0x7FFFFFFFu;
+}
 
 template <class Ops, class Key>
 B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
@@ -261,29 +310,34 @@ B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint
         *root_out = 0u;
         return;
     }
+    const uint64_t key = (uint64_t)keys[i];
     uint32_t l = i, r = i;
+    uint32_t lev_l = i > 0u ? split_level((uint64_t)keys[i - 1u], key, i - 1u) : LEVEL_END;  // split between l-1 and l
+    uint32_t lev_r = i + 1u < n ? split_level(key, (uint64_t)keys[i + 1u], i) : LEVEL_END;    // split between r and r+1
     uint32_t ref = LEAF_BIT | i;
     for (;;) {
-        bool is_left;
-        if (l == 0u) is_left = true;
-        else if (r == n - 1u) is_left = false;
-        else is_left = delta_less(key_delta(keys, r), key_delta(keys, l - 1u));
+        const bool is_left = lev_r < lev_l;  // join the neighbour beyond the LOWER split; array ends never win
         const uint32_t p = is_left ? r : l - 1u;
         Ops::store_ref(&qnodes[p], is_left ? 0 : 1, ref);
-        Xch mine;
-        mine.w[0] = box.w[0];
-        mine.w[1] = box.w[1];
-        mine.w[2] = box.w[2];
-        mine.w[3] = is_left ? l : r;
-        const Xch sib = Ops::exchange(&xch[p], mine);
-        if (sib.w[3] == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
-        Ops::store_qboxes(&qnodes[p], is_left ? mine.w : sib.w, is_left ? sib.w : mine.w);
-        if (is_left) r = sib.w[3];
-        else l = sib.w[3];
+        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r);
+        const Xch got = Ops::exchange(&xch[p], mine);
+        if (got.w[3] == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
+        QBox sib;
+        uint32_t bound, level;
+        xch_unpack(got, sib, bound, level);
+        Ops::store_qboxes(&qnodes[p], is_left ? box.w : sib.w, is_left ? sib.w : box.w);
+        if (is_left) {
+            r = bound;
+            lev_r = level;
+        }
+        else {
+            l = bound;
+            lev_l = level;
+        }
 #pragma unroll
         for (int k = 0; k < 3; ++k) box.w[k] = qplane_merge(box.w[k], sib.w[k]);
         ref = p;
-        if (l == 0u && r == n - 1u) {
+        if (lev_l == LEVEL_END && lev_r == LEVEL_END) {  // the range is the whole array
             *root_out = p;
             return;
         }

@@ -22,13 +22,19 @@ constexpr int RS_ITEMS = B2_RS_ITEMS;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 pairs per tile
 constexpr int RS_MAX_PASSES = 8;
 
-constexpr uint32_t LB_FLAG_AGG = 1u << 30;     // tile's own digit count is posted
-constexpr uint32_t LB_FLAG_PREFIX = 2u << 30;  // inclusive count over tiles 0..this is posted
-constexpr uint32_t LB_VALUE_MASK = (1u << 30) - 1u;
+enum : uint32_t {
+    LB_FLAG_AGG = 1u << 30,     // own digit count is posted
+    LB_FLAG_PREFIX = 2u << 30,  // inclusive count over everything up to and including this one is posted
+    LB_VALUE_MASK = (1u << 30) - 1u
+};
 #ifndef B2_LB_BATCH
 #define B2_LB_BATCH 8
 #endif
 constexpr int LB_BATCH = B2_LB_BATCH;
+#ifndef B2_LB_GROUP
+#define B2_LB_GROUP 16
+#endif
+constexpr uint32_t LB_GROUP = B2_LB_GROUP;  // tiles per look-back group
 
 static_assert(RS_THREADS == RS_RADIX, "one thread per digit in the scan phases");
 
@@ -55,10 +61,10 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* wa
 // One digit pass. Grid = number of tiles; tiles are claimed through `ticket` so that a tile can only
 // ever wait on tiles that already started (forward progress of the look-back).
 //   ghist    [256]  total count of each digit value in this pass (over all n keys)
-//   lookback [tiles][256] zero-initialised status words for this pass
+//   lookback [tiles + ceil(tiles / LB_GROUP)][256] zero-initialised status words for this pass
 __global__ void __launch_bounds__(RS_THREADS)
 k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
-           uint32_t n, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
+           uint32_t n, uint32_t n_tiles, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
 {
     __shared__ uint64_t skeys[RS_TILE];  // reused for the values after the keys are written out
     __shared__ uint32_t whist[RS_WARPS][RS_RADIX];
@@ -117,36 +123,61 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
         whist[w][tid] = tile_count;
         tile_count += c;
     }
-    // ---- publish the tile's count, then sum the counts of all earlier tiles (decoupled look-back)
+    // ---- publish the tile's count, then sum the counts of all earlier tiles.  Two levels, because at ~1M
+    // pairs every tile of the pass is resident and starts at the same moment: a plain decoupled look-back
+    // then degenerates into a serial walk over up to `tile` status words (dozens of dependent L2 round trips).
+    //   level 1: tiles form groups of LB_GROUP; a tile sums the counts of the earlier tiles of its own group
+    //            directly (<= LB_GROUP-1 independent loads, one round trip once they are posted);
+    //   level 2: the last tile of a group posts the group's count, then — by decoupled look-back over GROUP
+    //            status words, batched — the inclusive count over all groups up to its own; every tile
+    //            obtains the count of the groups before its own the same way.
+    // A tile only ever waits on tiles with a smaller ticket, which have started: forward progress holds for any
+    // grid size.
     uint32_t excl = 0u;
     {
-        volatile uint32_t* lb = lookback;
-        if (tile == 0u) {
-            lb[tid] = LB_FLAG_PREFIX | tile_count;
+        volatile uint32_t* ta = lookback;                                   // [tiles][256] tile counts
+        volatile uint32_t* gs = lookback + (size_t)n_tiles * RS_RADIX;      // [groups][256] group status
+        const uint32_t grp = tile / LB_GROUP, first = grp * LB_GROUP;
+        ta[(size_t)tile * RS_RADIX + tid] = LB_FLAG_AGG | tile_count;
+        uint32_t in_group = 0u;
+        {
+            uint32_t v[LB_GROUP - 1];
+#pragma unroll
+            for (int j = 0; j < LB_GROUP - 1; ++j) {
+                const uint32_t t = first + (uint32_t)j;
+                v[j] = t < tile ? ta[(size_t)t * RS_RADIX + tid] : LB_FLAG_AGG;
+            }
+#pragma unroll
+            for (int j = 0; j < LB_GROUP - 1; ++j) {
+                const uint32_t t = first + (uint32_t)j;
+                uint32_t w = v[j];
+                while ((w >> 30) == 0u) w = ta[(size_t)t * RS_RADIX + tid];  // not posted yet: that tile is running (ticket order)
+                in_group += w & LB_VALUE_MASK;
+            }
         }
-        else {
-            lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_AGG | tile_count;
-            // Walk back over the predecessors' status words LB_BATCH at a time: the loads of a batch are
-            // independent (one L2 round trip for the batch instead of one per tile); tiles start almost
-            // simultaneously here, so a serial walk would be a chain of up to `tile` dependent L2 reads.
-            int t = (int)tile - 1;
+        const bool closes_group = (tile % LB_GROUP) == LB_GROUP - 1u;
+        if (closes_group) gs[(size_t)grp * RS_RADIX + tid] = (grp == 0u ? LB_FLAG_PREFIX : LB_FLAG_AGG) | (in_group + tile_count);
+        uint32_t before = 0u;  // count over all groups before mine
+        if (grp > 0u) {
+            int g = (int)grp - 1;
             bool done = false;
             while (!done) {
                 uint32_t v[LB_BATCH];
 #pragma unroll
-                for (int j = 0; j < LB_BATCH; ++j) v[j] = (t - j >= 0) ? lb[(size_t)(t - j) * RS_RADIX + tid] : (2u << 30);  // LB_FLAG_PREFIX with value 0: ends the walk
+                for (int j = 0; j < LB_BATCH; ++j) v[j] = (g - j >= 0) ? gs[(size_t)(g - j) * RS_RADIX + tid] : LB_FLAG_PREFIX;  // PREFIX with value 0 ends the walk
 #pragma unroll
                 for (int j = 0; j < LB_BATCH; ++j) {
                     if (done) break;
                     uint32_t w = v[j];
-                    while ((w >> 30) == 0u) w = lb[(size_t)(t - j) * RS_RADIX + tid];  // not posted yet: that tile is running (ticket order)
-                    excl += w & LB_VALUE_MASK;
+                    while ((w >> 30) == 0u) w = gs[(size_t)(g - j) * RS_RADIX + tid];
+                    before += w & LB_VALUE_MASK;
                     done = (w >> 30) == 2u;
                 }
-                t -= LB_BATCH;
+                g -= LB_BATCH;
             }
-            lb[(size_t)tile * RS_RADIX + tid] = LB_FLAG_PREFIX | (excl + tile_count);
+            if (closes_group) gs[(size_t)grp * RS_RADIX + tid] = LB_FLAG_PREFIX | (before + in_group + tile_count);
         }
+        excl = before + in_group;
     }
     const uint32_t g_excl = block_excl_scan_256(ghist[tid], warp_tot);    // keys with a smaller digit, globally
     const uint32_t t_excl = block_excl_scan_256(tile_count, warp_tot);    // ... within this tile
