@@ -1198,6 +1198,13 @@ b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t byt
     return B2COL_OK;
 }
 
+#ifdef B2_SORT_TIMING
+int b2col_debug_sort_timing(unsigned long long* out, int n_tiles)  // dev builds only
+{
+    return (int)cudaMemcpyFromSymbol(out, b2::g_sort_timing, sizeof(unsigned long long) * 8 * (size_t)n_tiles);
+}
+#endif
+
 b2col_status b2col_event_record(b2col_ctx* ctx, int slot)
 {
     if (!ctx || slot < 0 || slot >= 16) return fail(ctx, B2COL_ERR_INVALID, "bad event slot");
