@@ -238,7 +238,7 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32
 // decides exactly as the full delta does (same tree as build_from_leaf; the tests compare them).  With the
 // levels in the message a thread reads keys only once (its own leaf's two neighbours, coalesced); per climbed
 // level it issues one exchange, one 4-byte and one 24-byte store, and three packed min/max.
-struct Xch {
+struct alignas(16) Xch {
     uint32_t w[4];  // w[3] == UNVISITED: nobody has arrived yet
 };
 constexpr uint32_t LEVEL_END = 127u;
