@@ -92,16 +92,18 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def make_scene(n_colliders: int):
+def make_scene(n_colliders: int, workload: str = "config3"):
     from engine_b200 import synth
 
+    if workload == "config5":  # clustered / skewed: Gaussian clusters + 5 % uniform background
+        return synth.clustered_boxes(n_colliders, seed=5)
     return synth.uniform_boxes(n_colliders, seed=3, extent=1000.0, hmin=0.5, hmax=2.0)
 
 
-def make_rays(n: int, rank: int):
+def make_rays(n: int, rank: int, workload: str = "config3"):
     from engine_b200 import synth
 
-    return synth.random_rays(n, seed=4 + 1000 * rank, extent=1000.0)
+    return synth.random_rays(n, seed=4 + 1000 * rank, extent=2000.0 if workload == "config5" else 1000.0)
 
 
 # -------------------------------------------------------------------------------------------------
@@ -154,9 +156,9 @@ def run_reference(args):
     rank = env_int("RANK", 0)
     if rank != 0:
         return
-    scene = make_scene(args.colliders)
+    scene = make_scene(args.colliders, args.workload)
     arm = CpuArm(scene)
-    pool = make_rays(min(args.rays, 4_000_000), 0)
+    pool = make_rays(min(args.rays, 4_000_000), 0, args.workload)
     n = arm.calibrate(pool, target_s=3.0)
     rays = pool[:n]
     for _ in range(args.warmup):
@@ -176,6 +178,12 @@ def run_reference(args):
 
 
 def workload_config(args):
+    if args.workload == "config5":
+        return {
+            "workload": "configs[4]: synthetic clustered AABBs (1000 Gaussian clusters, Zipf populations, 5 % uniform background, seed 5), incoherent random rays (seed 4), T=1000",
+            "colliders": args.colliders, "rays_per_gpu": args.rays, "sharding": "rays sharded across ranks, BVH replicated (NCCL broadcast)",
+            "l2": "ray + hit streams exceed the 126 MB L2 every step; at 10M colliders the 640 MB BVH does too",
+        }
     return {
         "workload": "configs[2]: synthetic 1M AABBs (uniform in [-1000,1000]^3, half-extents U[0.5,2], seed 3), incoherent random rays (seed 4), T=1000",
         "colliders": args.colliders, "rays_per_gpu": args.rays, "sharding": "rays sharded across ranks, BVH replicated (NCCL broadcast)",
@@ -215,7 +223,7 @@ def run_ours(args):
         return float(t.item())
 
     cs = CollisionSystem(device=local)
-    scene = make_scene(args.colliders)
+    scene = make_scene(args.colliders, args.workload)
     N = scene.n_colliders
 
     # ---- build on rank 0, replicate over NVLink ---------------------------------------------------
@@ -239,7 +247,7 @@ def run_ours(args):
         algo = 280.0 * N  # refit 140 B + build 140 B per collider
         rebuild = {"ms": ms, "colliders": N, "launches_per_update": (l1 - l0) // K, "algorithmic_bytes": algo,
                    "achieved_gbs": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak,
-                   "what": "propagate + refit + Morton + 6-pass radix sort + hierarchy/bounds, device-resident TRS, back-to-back on one stream"}
+                   "what": f"propagate + refit + Morton + {cs.stats()['sort_passes']}-pass radix sort + hierarchy/bounds, device-resident TRS, back-to-back on one stream"}
     if world > 1:
         from engine_b200 import dist as b2dist
 
@@ -251,7 +259,7 @@ def run_ours(args):
 
     # ---- this rank's ray shard ----------------------------------------------------------------------
     R = args.rays
-    rays_np = make_rays(R, rank)
+    rays_np = make_rays(R, rank, args.workload)
     h_rays = torch.from_numpy(rays_np).pin_memory()
     h_out = torch.empty(R * 36, dtype=torch.uint8).pin_memory()
     d_rays = h_rays.cuda()
@@ -337,6 +345,7 @@ def main():
     ap.add_argument("--colliders", type=int, default=1_000_000)
     ap.add_argument("--rays", type=int, default=16 * 1024 * 1024, help="rays per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="config3", choices=["config3", "config5"], help="config3: uniform 1M (the headline); config5: clustered (use --colliders 10000000)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
