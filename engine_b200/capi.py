@@ -41,7 +41,7 @@ class Stats(C.Structure):
 SYMBOLS = [
     "b2col_abi_version", "b2col_create", "b2col_destroy", "b2col_last_error", "b2col_sync", "b2col_stream",
     "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_set_world_matrices", "b2col_set_colliders",
-    "b2col_update", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
+    "b2col_update", "b2col_propagate", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
     "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats",
     "b2col_bvh_blob", "b2col_bvh_export_blob", "b2col_bvh_import_blob", "b2col_event_record", "b2col_event_elapsed_ms",
 ]
@@ -80,6 +80,7 @@ def load() -> C.CDLL:
     lib.b2col_set_world_matrices.argtypes = [vp, u32, vp]
     lib.b2col_set_colliders.argtypes = [vp, u32, vp, vp]
     lib.b2col_update.argtypes = [vp]
+    lib.b2col_propagate.argtypes = [vp]
     lib.b2col_raycast_batch.argtypes = [vp, vp, sz, vp, C.c_int]
     lib.b2col_raycast_device.argtypes = [vp, vp, sz, vp, C.c_int]
     lib.b2col_upload_ref_bvh.argtypes = [vp, vp, sz]

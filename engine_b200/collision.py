@@ -102,6 +102,12 @@ class CollisionSystem:
             self.sync()
 
     # -- queries -------------------------------------------------------------------------------
+    def propagate(self, wait: bool = True) -> None:
+        """TransformSystem::onUpdate alone (reference src/system_transform.cpp:12-38): world matrices on the device."""
+        self._ck(self.lib.b2col_propagate(self.h))
+        if wait:
+            self.sync()
+
     def get_raycasts(self, rays, mode: int = MODE_LBVH, out: np.ndarray | None = None) -> np.ndarray:
         rays = _rays(rays)
         n = rays.shape[0]

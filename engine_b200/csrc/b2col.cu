@@ -703,6 +703,7 @@ struct b2col_ctx {
     // entities
     uint32_t n_entities = 0;
     bool have_hierarchy = false, have_trs = false, world_external = false;
+    bool world_fresh = false;  // d_world already holds the matrices of the current hierarchy + TRS (b2col_propagate)
     std::vector<uint32_t> level_offsets;  // host; level k = [off[k], off[k+1]) in d_level_entities
     DevBuf d_parent, d_level_entities, d_pos, d_rot, d_scl, d_world;
     // colliders
@@ -948,6 +949,7 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
     ctx->n_entities = n_entities;
     ctx->have_hierarchy = true;
     ctx->have_trs = false;
+    ctx->world_fresh = false;
     return B2COL_OK;
 }
 
@@ -966,6 +968,7 @@ static b2col_status set_trs_common(b2col_ctx* ctx, uint32_t n_entities, const fl
     CU(cudaMemcpyAsync(ctx->d_scl.p, scl3, rows * 12, kind, ctx->stream));
     ctx->have_trs = true;
     ctx->world_external = false;
+    ctx->world_fresh = false;
     return B2COL_OK;
 }
 
@@ -1017,6 +1020,30 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     return B2COL_OK;
 }
 
+static b2col_status enqueue_propagate(b2col_ctx* ctx)
+{
+    const size_t rows = (size_t)ctx->n_entities + 1;
+    GUARD(ensure(ctx, ctx->d_world, rows * 64));
+    const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
+    for (size_t k = 0; k < n_levels; ++k) {
+        const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
+        if (!cnt) continue;
+        LAUNCH(ctx, k_propagate_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+               ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>());
+    }
+    return B2COL_OK;
+}
+
+b2col_status b2col_propagate(b2col_ctx* ctx)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (!(ctx->have_hierarchy && ctx->have_trs)) return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs");
+    CU(cudaSetDevice(ctx->device));
+    GUARD(enqueue_propagate(ctx));
+    ctx->world_fresh = true;
+    return B2COL_OK;
+}
+
 b2col_status b2col_update(b2col_ctx* ctx)
 {
     if (!ctx) return B2COL_ERR_INVALID;
@@ -1025,19 +1052,9 @@ b2col_status b2col_update(b2col_ctx* ctx)
         return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
     CU(cudaSetDevice(ctx->device));
     const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
-    const size_t rows = (size_t)E + 1;
 
     // ---- a1: world matrices -------------------------------------------------------------------
-    if (!ctx->world_external) {
-        GUARD(ensure(ctx, ctx->d_world, rows * 64));
-        const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
-        for (size_t k = 0; k < n_levels; ++k) {
-            const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
-            if (!cnt) continue;
-            LAUNCH(ctx, k_propagate_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
-                   ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>());
-        }
-    }
+    if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));
 
     // ---- allocate the frame's buffers -----------------------------------------------------------
     const size_t blob_bytes = blob_size_for(n);

@@ -8,6 +8,7 @@
 #include <typeinfo>
 
 #include "b2col.h"
+#include "b2col_scene_ctx.h"
 #include "component_transform.h"
 #include "scene.h"
 
@@ -20,11 +21,11 @@ CollisionSystem::CollisionSystem(Scene* scene)
     : System(scene, {typeid(TransformComponent).hash_code(), typeid(ColliderComponent).hash_code()})
 {
     // error convention of the reference: exceptions (caught in main, reference test/src/main.cpp:29-35)
-    const b2col_status st = b2col_create(&ctx_, nullptr);
-    if (st != B2COL_OK) throw std::runtime_error(std::string("b2col_create: ") + b2col_last_error(nullptr));
+    shared_ = B2colAcquire(scene);  // one context per Scene, shared with the drop-in TransformSystem if that is in use
+    ctx_ = shared_->ctx;
 }
 
-CollisionSystem::~CollisionSystem() { b2col_destroy(ctx_); }
+CollisionSystem::~CollisionSystem() { B2colRelease(m_scene); }
 
 void CollisionSystem::Check(int status, const char* what) const
 {
@@ -42,7 +43,6 @@ void CollisionSystem::onUpdate(float ts)
     (void)ts;
     // world matrices of every entity, indexed by entity ID (row 0 unused) — what TransformSystem just wrote
     const uint32_t n_entities = m_scene->next_entity_id_ - 1u;
-    gather_world_.resize(16u * (static_cast<std::size_t>(n_entities) + 1u));
     gather_entities_.clear();
     gather_boxes_.clear();
     for (Entity entity : m_entities) {  // ascending IDs (std::set), the reference's own iteration order
@@ -50,12 +50,19 @@ void CollisionSystem::onUpdate(float ts)
         gather_entities_.push_back(entity);
         gather_boxes_.push_back(c->aabb);
     }
-    // Only collider entities' matrices are read by the refit, so only those rows are filled.
-    for (Entity entity : gather_entities_) {
-        const auto* t = m_scene->GetComponent<TransformComponent>(entity);
-        std::memcpy(&gather_world_[16u * entity], &t->world_matrix, 64);
+    if (shared_->transforms_on_device && shared_->n_entities == n_entities) {
+        // the drop-in TransformSystem of this Scene has already put this frame's world matrices on the device
     }
-    Check(b2col_set_world_matrices(ctx_, n_entities, gather_world_.data()), "b2col_set_world_matrices");
+    else {
+        // reference TransformSystem on the CPU: upload TransformComponent::world_matrix.  Only collider entities'
+        // matrices are read by the refit, so only those rows are filled.
+        gather_world_.resize(16u * (static_cast<std::size_t>(n_entities) + 1u));
+        for (Entity entity : gather_entities_) {
+            const auto* t = m_scene->GetComponent<TransformComponent>(entity);
+            std::memcpy(&gather_world_[16u * entity], &t->world_matrix, 64);
+        }
+        Check(b2col_set_world_matrices(ctx_, n_entities, gather_world_.data()), "b2col_set_world_matrices");
+    }
     Check(b2col_set_colliders(ctx_, static_cast<uint32_t>(gather_entities_.size()), gather_entities_.data(),
                               reinterpret_cast<const b2col_aabb*>(gather_boxes_.data())),
           "b2col_set_colliders");

@@ -72,6 +72,7 @@ class CollisionSystem : public System {
     void SyncDebugBvh();
 
    private:
+    struct B2colSceneCtx* shared_ = nullptr;
     b2col_ctx* ctx_ = nullptr;
     std::size_t colliders_inserted_ = 0;
     std::vector<uint32_t> gather_entities_;

@@ -142,6 +142,11 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n_colliders, const uin
  * Enqueued on the ctx stream; returns without waiting.  n_colliders == 0 yields an empty tree and
  * every query misses (the reference abort()s, :136 -> :208 — deliberate divergence). */
 b2col_status b2col_update(b2col_ctx* ctx);
+/* replaces: TransformSystem::onUpdate alone (src/system_transform.cpp:12-38) — for callers that replace the
+ * reference's TransformSystem and CollisionSystem separately (engine_b200/shim/system_transform.cpp): world
+ * matrices from the current hierarchy + TRS, enqueued on the ctx stream.  A following b2col_update reuses them
+ * (no second propagation) until the TRS or the hierarchy are set again. */
+b2col_status b2col_propagate(b2col_ctx* ctx);
 
 /* ---- queries -------------------------------------------------------------------------------- */
 /* replaces: CollisionSystem::GetRaycast (src/system_collisions.cpp:160-199), batched.

@@ -268,6 +268,9 @@ class RefEngine:
         return out
 
 
+DROPIN2_SO = os.path.join(os.path.dirname(DROPIN_SO), "libdropin2_engine.so")
+
+
 class DropinEngine(RefEngine):
     """The reference's Scene / ECS / TransformSystem with engine_b200/shim's CollisionSystem compiled in
     place of the reference's (oracle/_ref/libdropin_engine.so, needs a GPU at run time)."""
@@ -283,3 +286,15 @@ class DropinEngine(RefEngine):
         out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
         self.lib.refh_raycast_batch(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(out))
         return out
+
+
+class Dropin2Engine(DropinEngine):
+    """As DropinEngine, with engine_b200/shim/with_transform's TransformSystem replacing the reference's too
+    (oracle/_ref/libdropin2_engine.so): TRS gather -> GPU propagation -> world_matrix scatter, matrices kept on
+    the device for the collision refit."""
+
+    SO = DROPIN2_SO
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(DROPIN2_SO)

@@ -10,7 +10,7 @@ import torch
 from conftest import SCENE_FIXTURES, assert_raycast_equal, load_golden
 from emu_loader import Emu
 from engine_b200 import capi, synth
-from oracle.oracle import DropinEngine, RefEngine
+from oracle.oracle import Dropin2Engine, DropinEngine, RefEngine
 
 pytestmark = pytest.mark.gpu
 
@@ -342,3 +342,31 @@ def test_dropin_shim_inside_reference_scene(port):
     ent, box = port.tree_leaves_dfs(exported)
     _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
     assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), "frame 2", ignore_entity_on=ties > 0)
+
+
+@pytest.mark.skipif(not (Dropin2Engine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_dropin_transform_and_collision_shims_inside_reference_scene(port):
+    """SURVEY.md 8(f) row 1: the reference's Scene::Update with BOTH systems replaced — TransformSystem (AoS
+    TransformComponent gather -> b2col_propagate -> world_matrix scatter) and CollisionSystem (refit on the
+    matrices that stayed on the device).  world_matrix must equal the reference's bit for bit, raycasts too."""
+    s = synth.hierarchy_scene(3000, 40, seed=17, extent=150)
+    ids = np.arange(1, s.n_entities + 1, dtype=np.uint32)
+    rays = np.concatenate([synth.random_rays(4000, seed=96, extent=170, normalised=False), synth.axis_rays(500, seed=97, extent=150)])
+    engines = []
+    for cls in (RefEngine, Dropin2Engine):
+        e = cls()
+        e.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+        e.add_colliders(s.collider_entity, s.collider_aabb)
+        e.scene_update()
+        engines.append(e)
+    ref, drop = engines
+    for frame in range(3):
+        assert (bits(drop.world_matrices(ids)) == bits(ref.world_matrices(ids))).all(), f"world_matrix differs in frame {frame}"
+        exported = drop.bvh()
+        ent, box = port.tree_leaves_dfs(exported)
+        _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
+        assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), f"frame {frame}", ignore_entity_on=ties > 0)
+        synth.perturb_roots(s, 40, frame + 1)
+        for e in engines:
+            e.set_trs(ids, s.pos[1:], s.rot[1:], s.scl[1:])
+            e.scene_update()
