@@ -33,6 +33,7 @@ class Stats(C.Structure):
     _fields_ = [
         ("n_entities", C.c_uint32), ("n_colliders", C.c_uint32), ("n_levels", C.c_uint32), ("n_internal_nodes", C.c_uint32),
         ("root", C.c_uint32), ("sort_passes", C.c_uint32), ("kernel_launches", C.c_uint64), ("bvh_bytes", C.c_uint64),
+        ("full_builds", C.c_uint64), ("refits", C.c_uint64),
         ("scene_min", C.c_float * 3), ("scene_max", C.c_float * 3),
     ]
 
@@ -41,7 +42,7 @@ class Stats(C.Structure):
 SYMBOLS = [
     "b2col_abi_version", "b2col_create", "b2col_destroy", "b2col_last_error", "b2col_sync", "b2col_stream",
     "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_set_world_matrices", "b2col_set_colliders",
-    "b2col_update", "b2col_propagate", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
+    "b2col_update", "b2col_propagate", "b2col_refit", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
     "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats",
     "b2col_bvh_blob", "b2col_bvh_export_blob", "b2col_bvh_import_blob", "b2col_event_record", "b2col_event_elapsed_ms",
 ]
@@ -81,6 +82,7 @@ def load() -> C.CDLL:
     lib.b2col_set_colliders.argtypes = [vp, u32, vp, vp]
     lib.b2col_update.argtypes = [vp]
     lib.b2col_propagate.argtypes = [vp]
+    lib.b2col_refit.argtypes = [vp]
     lib.b2col_raycast_batch.argtypes = [vp, vp, sz, vp, C.c_int]
     lib.b2col_raycast_device.argtypes = [vp, vp, sz, vp, C.c_int]
     lib.b2col_upload_ref_bvh.argtypes = [vp, vp, sz]

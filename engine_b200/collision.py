@@ -101,6 +101,12 @@ class CollisionSystem:
         if wait:
             self.sync()
 
+    def on_update_refit(self, ts: float = 0.0, wait: bool = True) -> None:
+        """Refit-only frame (the reference's TODO at src/system_collisions.cpp:116-120): same tree shape, new boxes."""
+        self._ck(self.lib.b2col_refit(self.h))
+        if wait:
+            self.sync()
+
     # -- queries -------------------------------------------------------------------------------
     def propagate(self, wait: bool = True) -> None:
         """TransformSystem::onUpdate alone (reference src/system_transform.cpp:12-38): world matrices on the device."""

@@ -266,6 +266,21 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
     }
 }
 
+// Header fields every build needs besides the bounds: leaf / node counts and the quantisation grid of the
+// traversal nodes, derived from the box bounds k_refit reduced into the header.  One thread.
+__device__ void finish_header(BlobHeader* hdr, uint32_t n, float T)
+{
+    hdr->magic = BLOB_MAGIC;
+    hdr->n_leaves = n;
+    hdr->n_nodes = n > 1u ? n - 1u : 1u;
+    float bmin[3], bmax[3];
+    for (int k = 0; k < 3; ++k) {
+        bmin[k] = ordered_to_float(~hdr->box_min_inv[k]);
+        bmax[k] = ordered_to_float(hdr->box_max[k]);
+    }
+    hdr->grid = make_grid(bmin, bmax, T);
+}
+
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway).
 __global__ void __launch_bounds__(256)
@@ -299,18 +314,12 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
         const uint32_t c = shist[p][threadIdx.x];
         if (c) atomicAdd(&ghist[p * RS_RADIX + threadIdx.x], c);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        hdr->magic = BLOB_MAGIC;
-        hdr->n_leaves = n;
-        hdr->n_nodes = n > 1u ? n - 1u : 1u;
-        float bmin[3], bmax[3];
-        for (int k = 0; k < 3; ++k) {
-            bmin[k] = ordered_to_float(~hdr->box_min_inv[k]);
-            bmax[k] = ordered_to_float(hdr->box_max[k]);
-        }
-        hdr->grid = make_grid(bmin, bmax, T);
-    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, n, T);
 }
+
+// Refit-only frames (b2col_refit) skip k_morton: this fills the header fields k_morton would have written,
+// from the bounds k_refit has just reduced.
+__global__ void k_header(uint32_t n, BlobHeader* hdr, float T) { finish_header(hdr, n, T); }
 
 // LBVH hierarchy + bounds, production form: traversal structure only, merged in grid space — the per-thread
 // climb of build_from_leaf_q (b2col_bvh.cuh), with the arrival exchange moved into SHARED memory for every
@@ -722,6 +731,8 @@ struct b2col_ctx {
     size_t blob_bytes = 0;
     uint32_t tree_leaves = 0;  // leaves of the tree currently in the blob
     bool have_tree = false;
+    bool topology_valid = false;  // keys / leaf order in d_keys/d_vals[sorted_side] describe the tree in the blob and the current collider set (b2col_refit)
+    uint64_t full_builds = 0, refits = 0;
     // reference-topology tree
     DevBuf d_ref_nodes, d_flag;
     uint32_t n_ref_nodes = 0;
@@ -1017,6 +1028,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     }
     ctx->n_colliders = n;
     ctx->have_colliders = true;
+    ctx->topology_valid = false;  // a new collider set needs a new tree
     return B2COL_OK;
 }
 
@@ -1062,8 +1074,10 @@ b2col_status b2col_update(b2col_ctx* ctx)
     ctx->blob_bytes = blob_bytes;
     ctx->tree_leaves = n;
     CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
+    ctx->topology_valid = false;
     if (n == 0) {
         ctx->have_tree = true;  // empty tree: header says n_leaves = 0, every query misses
+        ctx->topology_valid = true;
         return B2COL_OK;
     }
     if (ctx->max_col_entity > E)
@@ -1126,6 +1140,36 @@ b2col_status b2col_update(b2col_ctx* ctx)
     LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
            ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx));
     ctx->have_tree = true;
+    ctx->topology_valid = true;
+    ++ctx->full_builds;
+    return B2COL_OK;
+}
+
+b2col_status b2col_refit(b2col_ctx* ctx)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (!ctx->topology_valid || !ctx->have_tree || ctx->tree_leaves != ctx->n_colliders)
+        return fail(ctx, B2COL_ERR_STATE, "b2col_refit needs a tree built by b2col_update on this ctx for the current collider set");
+    if (!ctx->world_external && !(ctx->have_hierarchy && ctx->have_trs))
+        return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t n = ctx->n_colliders;
+    if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));
+    if (n == 0) return B2COL_OK;
+    if (ctx->max_col_entity > ctx->n_entities)
+        return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, ctx->n_entities);
+    // Same tree shape, new boxes: the hierarchy is a pure function of the SORTED KEYS of the last full build, which
+    // are still in d_keys/d_vals[sorted_side], so k_build re-emits the same nodes (same indices, same leaf order —
+    // the order that decides tie winners) around the boxes k_refit has just written.  Skips Morton + the radix sort.
+    CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
+    ctx->exact_nodes_valid = false;
+    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
+           ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx));
+    LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), ctx->T);
+    const int side = ctx->sorted_side;
+    LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
+           ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx));
+    ++ctx->refits;
     return B2COL_OK;
 }
 
@@ -1310,6 +1354,8 @@ b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out)
     out->n_levels = ctx->level_offsets.empty() ? 0 : (uint32_t)ctx->level_offsets.size() - 1;
     out->sort_passes = (uint32_t)ctx->passes;
     out->kernel_launches = ctx->launches;
+    out->full_builds = ctx->full_builds;
+    out->refits = ctx->refits;
     if (ctx->have_tree && ctx->d_blob.p) {
         CU(cudaSetDevice(ctx->device));
         BlobHeader h;
@@ -1359,6 +1405,7 @@ b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t byt
     ctx->blob_bytes = bytes;
     ctx->tree_leaves = h.n_leaves;
     ctx->have_tree = true;
+    ctx->topology_valid = false;  // a foreign tree: its sorted keys are not on this ctx
     return B2COL_OK;
 }
 

@@ -63,10 +63,24 @@ void CollisionSystem::onUpdate(float ts)
         }
         Check(b2col_set_world_matrices(ctx_, n_entities, gather_world_.data()), "b2col_set_world_matrices");
     }
-    Check(b2col_set_colliders(ctx_, static_cast<uint32_t>(gather_entities_.size()), gather_entities_.data(),
-                              reinterpret_cast<const b2col_aabb*>(gather_boxes_.data())),
-          "b2col_set_colliders");
-    Check(b2col_update(ctx_), "b2col_update");
+    const bool same_set = have_build_ && gather_entities_ == device_entities_ &&
+                          (gather_boxes_.empty() || std::memcmp(gather_boxes_.data(), device_boxes_.data(), gather_boxes_.size() * sizeof(AABB)) == 0);
+    if (same_set && rebuild_interval > 1 && frames_since_build_ + 1 < rebuild_interval) {
+        Check(b2col_refit(ctx_), "b2col_refit");
+        ++frames_since_build_;
+    }
+    else {
+        if (!same_set) {
+            Check(b2col_set_colliders(ctx_, static_cast<uint32_t>(gather_entities_.size()), gather_entities_.data(),
+                                      reinterpret_cast<const b2col_aabb*>(gather_boxes_.data())),
+                  "b2col_set_colliders");
+            device_entities_ = gather_entities_;
+            device_boxes_ = gather_boxes_;
+        }
+        Check(b2col_update(ctx_), "b2col_update");
+        have_build_ = true;
+        frames_since_build_ = 0;
+    }
     if (keep_debug_bvh) SyncDebugBvh();
 }
 

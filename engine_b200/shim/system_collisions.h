@@ -71,6 +71,13 @@ class CollisionSystem : public System {
     bool keep_debug_bvh = false;
     void SyncDebugBvh();
 
+    // Full rebuild every `rebuild_interval` frames; the frames in between only refit (b2col_refit: same tree
+    // shape, new boxes — the reference's own TODO, src/system_collisions.cpp:116-120).  1 = the reference's
+    // behaviour, rebuild every frame (:121).  A frame whose collider set (entities or local AABBs) differs from
+    // the previous frame's always rebuilds.  Query results do not depend on this setting except for the winner
+    // among exactly tied hits.
+    unsigned rebuild_interval = 1;
+
    private:
     struct B2colSceneCtx* shared_ = nullptr;
     b2col_ctx* ctx_ = nullptr;
@@ -78,6 +85,10 @@ class CollisionSystem : public System {
     std::vector<uint32_t> gather_entities_;
     std::vector<AABB> gather_boxes_;
     std::vector<float> gather_world_;
+    std::vector<uint32_t> device_entities_;  // the collider set currently on the device
+    std::vector<AABB> device_boxes_;
+    unsigned frames_since_build_ = 0;
+    bool have_build_ = false;
     void Check(int status, const char* what) const;
 };
 

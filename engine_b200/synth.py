@@ -280,3 +280,28 @@ def game_rays(n_frames: int, seed: int = 9) -> np.ndarray:
         out[f, 20, 0:3] = p
         out[f, 20, 3:6] = (0.0, 0.0, -1.0)
     return out.reshape(-1, 6)
+
+
+def game_inputs(n_frames: int, seed: int = 10) -> np.ndarray:
+    """Scripted player input for the headless test game (reference test/src/camera_controller.cpp:40-70 reads
+    these through the InputManager): rows of (movex, movey, lookx, looky, sprint, jump).  Piecewise-constant
+    walking / strafing / turning segments with occasional sprints and jumps, so that the player lands on the land
+    tiles, runs into boxes and staircases, climbs, jumps under things and falls off edges."""
+    rng = np.random.default_rng(seed)
+    out = np.zeros((n_frames, 6), np.float32)
+    f = 0
+    while f < n_frames:
+        seg = int(rng.integers(20, 90))
+        movey = float(rng.choice([1.0, 1.0, 1.0, 0.5, 0.0, -1.0]))
+        movex = float(rng.choice([0.0, 0.0, 1.0, -1.0, 0.25]))
+        turn = float(rng.choice([0.0, 0.0, 6.0, -6.0, 25.0, -25.0]))  # mouse counts per frame (x 0.003 rad)
+        look = float(rng.choice([0.0, 0.0, 3.0, -3.0]))
+        sprint = float(rng.random() < 0.3)
+        out[f : f + seg, 0] = movex
+        out[f : f + seg, 1] = movey
+        out[f : f + seg, 2] = turn
+        out[f : f + seg, 3] = look
+        out[f : f + seg, 4] = sprint
+        f += seg
+    out[:, 5] = (rng.random(n_frames) < 0.02).astype(np.float32)
+    return out

@@ -102,6 +102,7 @@ typedef struct b2col_stats {
     uint32_t sort_passes;
     uint64_t kernel_launches;   /* cumulative count of this library's kernel launches on this ctx */
     uint64_t bvh_bytes;         /* device bytes of the traversal structure (nodes + leaf entity table) */
+    uint64_t full_builds, refits; /* b2col_update / b2col_refit calls that built or re-bounded a tree */
     float scene_min[3], scene_max[3]; /* centroid bounds used for the Morton grid */
 } b2col_stats;
 
@@ -147,6 +148,15 @@ b2col_status b2col_update(b2col_ctx* ctx);
  * matrices from the current hierarchy + TRS, enqueued on the ctx stream.  A following b2col_update reuses them
  * (no second propagation) until the TRS or the hierarchy are set again. */
 b2col_status b2col_propagate(b2col_ctx* ctx);
+/* The refit-only frame the reference leaves as a TODO (src/system_collisions.cpp:116-120: "only rebuild the
+ * BVH if an entity has moved / been added"): propagate world matrices, refit world AABBs
+ * and re-bound the EXISTING tree bottom-up — same topology and leaf order as the last b2col_update, new boxes —
+ * skipping the Morton pass and the radix sort.  Query results stay exact (the tree is still a valid bounding
+ * hierarchy of the current boxes and ties keep resolving by leaf order); only traversal cost grows as the
+ * colliders drift from where they were sorted, so callers interleave it with b2col_update (the shim's
+ * rebuild_interval).  B2COL_ERR_STATE unless b2col_update has built a tree on this ctx for the current
+ * collider set.  Enqueued on the ctx stream. */
+b2col_status b2col_refit(b2col_ctx* ctx);
 
 /* ---- queries -------------------------------------------------------------------------------- */
 /* replaces: CollisionSystem::GetRaycast (src/system_collisions.cpp:160-199), batched.

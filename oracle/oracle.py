@@ -267,6 +267,27 @@ class RefEngine:
         self.lib.refh_normalize(_p(v), _p(out))
         return out
 
+    # -- the test game's player controller, headless (oracle/game_harness.cpp) --------------
+    GAME_STATE = ("px", "py", "pz", "vx", "vy", "vz", "qx", "qy", "qz", "qw", "yaw", "pitch", "grounded")
+
+    def add_camera(self, pos3, batched: bool = False) -> int:
+        """Camera entity + CameraControllerComponent + the controller system at index 0 (reference
+        test/src/game.cpp:92-109): the UNMODIFIED reference controller, or (drop-in builds) the batched port."""
+        self.lib.gameh_add_camera.restype = C.c_uint32
+        cam = int(self.lib.gameh_add_camera(self.h, _p(_f32(pos3, (3,))), C.c_int(1 if batched else 0)))
+        if cam == 0:
+            raise RuntimeError("the batched controller only exists in the drop-in builds")
+        self.n_entities += 1
+        return cam
+
+    def run_game(self, input6, dt: float = 1.0 / 60.0) -> np.ndarray:
+        """One Scene::Update(dt) per input row (movex, movey, lookx, looky, sprint, jump); returns (frames, 16)
+        float32 player state per frame, columns GAME_STATE (+ 3 spare)."""
+        inp = _f32(input6).reshape(-1, 6)
+        out = np.zeros((inp.shape[0], 16), np.float32)
+        self.lib.gameh_run(self.h, C.c_size_t(inp.shape[0]), _p(inp), C.c_float(dt), _p(out))
+        return out
+
 
 DROPIN2_SO = os.path.join(os.path.dirname(DROPIN_SO), "libdropin2_engine.so")
 
@@ -286,6 +307,15 @@ class DropinEngine(RefEngine):
         out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
         self.lib.refh_raycast_batch(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(out))
         return out
+
+    def batched_counters(self) -> dict:
+        out = np.zeros(4, np.uint64)
+        self.lib.gameh_batched_counters(self.h, _p(out))
+        return dict(zip(("raycast_calls", "rays_cast", "frames", "recasts"), (int(x) for x in out)))
+
+    def set_rebuild_interval(self, interval: int) -> None:
+        """engine_b200/shim CollisionSystem::rebuild_interval: refit-only frames between full rebuilds."""
+        self.lib.gameh_set_rebuild_interval(self.h, C.c_uint(interval))
 
 
 class Dropin2Engine(DropinEngine):

@@ -29,11 +29,9 @@
 
 using namespace engine;
 
+#include "harness_types.h"  // struct Harness: the Scene (+ a headless Application stand-in nothing on this path dereferences)
+
 namespace {
-struct Harness {
-    Scene scene{nullptr};  // Application* is never dereferenced on this path
-    std::vector<Entity> colliders;
-};
 static_assert(sizeof(Ray) == 24, "Ray layout");
 static_assert(sizeof(Raycast) == 36, "Raycast layout");
 static_assert(sizeof(AABB) == 24, "AABB layout");

@@ -1,0 +1,36 @@
+// TEST INFRASTRUCTURE — headless stand-in for the reference's include/application.h, so that the UNMODIFIED
+// reference test/src/camera_controller.cpp (the game's collision-response caller) compiles
+// without SDL / Vulkan: same accessor names, scripted input instead of a window.  Only the members that file
+// touches exist.  The real Application is never constructed on this path (Scene(nullptr) elsewhere in the
+// harness); here Scene receives a pointer to this object and only camera_controller.cpp dereferences it.
+#pragma once
+#include <functional>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <glm/gtc/constants.hpp>
+#include <glm/vec3.hpp>
+
+#include "debug_line.h"
+
+namespace engine {
+class Window;
+class InputManager;
+class SceneManager;
+
+class Application {
+   public:
+    Application();
+    ~Application();
+    std::vector<DebugLine> debug_lines{};
+    Window* getWindow() { return window_.get(); }
+    InputManager* getInputManager() { return input_.get(); }
+    SceneManager* getSceneManager() { return scenes_.get(); }
+
+   private:
+    std::unique_ptr<Window> window_;
+    std::unique_ptr<InputManager> input_;
+    std::unique_ptr<SceneManager> scenes_;
+};
+}  // namespace engine

@@ -280,6 +280,55 @@ def test_config4_dynamic_frames(CollisionSystem, port, emu):
         assert_raycast_equal(got[sel], port.raycast_tree(cs.bvh, rays[sel], nthreads=8), f"frame {frame}")
 
 
+def test_refit_only_frames(CollisionSystem, port):
+    """b2col_refit (the reference's TODO at src/system_collisions.cpp:116-120): after one full
+    build, frames that only move colliders keep the tree shape and re-bound it.  Every frame: world matrices and
+    world AABBs bit-exact, leaf order unchanged, the exported tree is a valid reference-format tree over the NEW
+    boxes, and rays agree with the reference traversal of that tree and with brute force."""
+    n, roots = 120_000, 150
+    s = synth.hierarchy_scene(n, roots, extent=400)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    with pytest.raises(capi.B2ColError) as ei:
+        cs.on_update_refit()  # no tree yet
+    assert ei.value.status == capi.ERR_STATE
+    cs.on_update()
+    order0 = cs.leaf_order()
+    rays = np.concatenate([synth.random_rays(40_000, seed=83, extent=400), synth.axis_rays(4_000, seed=84, extent=400)])
+    launches = cs.stats()["kernel_launches"]
+    for frame in range(1, 4):
+        synth.perturb_roots(s, roots, frame)
+        cs.set_trs(s.pos, s.rot, s.scl)
+        cs.on_update_refit()
+        world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+        assert (bits(cs.world_matrices()) == bits(world[1:])).all(), f"frame {frame}: world matrices"
+        want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+        boxes = cs.world_aabbs()
+        assert (bits(boxes) == bits(want_boxes)).all(), f"frame {frame}: world AABBs"
+        assert (cs.leaf_order() == order0).all(), "refit must not reorder leaves"
+        got = cs.get_raycasts(rays)
+        exported = cs.bvh
+        sel = np.arange(0, rays.shape[0], 8)
+        assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), f"refit frame {frame} vs reference traversal")
+        bsel = np.arange(0, rays.shape[0], 200)
+        brute = port.raycast_brute(s.collider_entity[order0], boxes[order0], rays[bsel], nthreads=8)
+        assert_raycast_equal(got[bsel], brute, f"refit frame {frame} vs brute force")
+    st = cs.stats()
+    assert st["full_builds"] == 1 and st["refits"] == 3
+    # 3 refit frames = 3 x (propagate levels + k_refit + k_header + k_build) + 3 x (k_trace + export kernels): far fewer than rebuilds
+    assert st["kernel_launches"] > launches
+    # a full rebuild afterwards gives the same answers again (different tree, same hits away from ties)
+    cs.on_update()
+    again = cs.get_raycasts(rays)
+    same = again["hit_entity"] == got["hit_entity"]
+    assert (again["hit"] == got["hit"]).all() and (again["distance"][same] == got["distance"][same]).all()
+    assert same.mean() > 0.999  # the rest are exact ties resolved by a different leaf order
+    # changing the collider set invalidates the topology
+    cs.set_colliders(s.collider_entity[:-1], s.collider_aabb[:-1])
+    with pytest.raises(capi.B2ColError):
+        cs.on_update_refit()
+
+
 def test_device_resident_and_replicated_tree(CollisionSystem):
     """raycast_device on torch CUDA buffers == host path; a second context that imports the BVH blob
     (what each rank does after the NCCL broadcast) answers identically."""
@@ -370,3 +419,62 @@ def test_dropin_transform_and_collision_shims_inside_reference_scene(port):
         for e in engines:
             e.set_trs(ids, s.pos[1:], s.rot[1:], s.scl[1:])
             e.scene_update()
+
+
+def _game(cls, scene, cam_pos, batched=False, rebuild_interval=1):
+    e = cls()
+    e.create_entities(scene.parent[1:], scene.pos[1:], scene.rot[1:], scene.scl[1:])
+    e.add_colliders(scene.collider_entity, scene.collider_aabb)
+    e.add_camera(cam_pos, batched=batched)
+    if rebuild_interval != 1:
+        e.set_rebuild_interval(rebuild_interval)
+    return e
+
+
+@pytest.mark.skipif(not (DropinEngine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_game_player_controller_trajectories():
+    """the test game's own collision response (UNMODIFIED reference
+    test/src/camera_controller.cpp, headless, scripted input) driving the player through the scene for 900 frames:
+    (a) inside the all-reference engine, (b) with the drop-in CollisionSystem answering its 21 GetRaycast calls per
+    frame, (c) with the batched port (one GetRaycasts call per frame) — and (d) the batched port with refit-only
+    frames between rebuilds.  The player's state must be identical in every frame."""
+    s = synth.game_scene(140)
+    inp = synth.game_inputs(900)
+    cam = (8.0, 2.0, 4.0)
+    want = _game(RefEngine, s, cam).run_game(inp)
+    assert want[:, 12].sum() > 100, "the scripted walk should spend time on the ground"
+    single = _game(DropinEngine, s, cam).run_game(inp)
+    assert (bits(single) == bits(want)).all(), f"drop-in CollisionSystem under the reference controller: first differing frame {np.argwhere((bits(single) != bits(want)).any(1))[:1]}"
+    eb = _game(DropinEngine, s, cam, batched=True)
+    batched = eb.run_game(inp)
+    assert (bits(batched) == bits(want)).all(), f"batched controller: first differing frame {np.argwhere((bits(batched) != bits(want)).any(1))[:1]}"
+    c = eb.batched_counters()
+    assert c["frames"] == 900 and c["raycast_calls"] <= 900 + c["recasts"] and c["rays_cast"] <= 21 * 900 + c["recasts"]
+    assert c["recasts"] < 450, c  # wall pushes are the exception, so most frames need exactly one call
+    er = _game(DropinEngine, s, cam, batched=True, rebuild_interval=8)
+    refit = er.run_game(inp)
+    assert (bits(refit) == bits(want)).all(), "refit-only frames between rebuilds must not change the trajectory"
+
+
+@pytest.mark.skipif(not (Dropin2Engine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_game_with_moving_colliders_and_refit_interval(port):
+    """Both systems replaced, colliders moving every few frames, rebuild_interval = 4: raycasts after each
+    frame still equal the reference's (refit frames keep the tree exact)."""
+    s = synth.hierarchy_scene(2500, 30, seed=19, extent=120)
+    ids = np.arange(1, s.n_entities + 1, dtype=np.uint32)
+    rays = np.concatenate([synth.random_rays(3000, seed=98, extent=140, normalised=False), synth.axis_rays(400, seed=99, extent=120)])
+    ref, drop = RefEngine(), Dropin2Engine()
+    for e in (ref, drop):
+        e.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+        e.add_colliders(s.collider_entity, s.collider_aabb)
+    drop.set_rebuild_interval(4)
+    for frame in range(6):
+        synth.perturb_roots(s, 30, frame + 1)
+        for e in (ref, drop):
+            e.set_trs(ids, s.pos[1:], s.rot[1:], s.scl[1:])
+            e.scene_update()
+        assert (bits(drop.world_matrices(ids)) == bits(ref.world_matrices(ids))).all(), f"world_matrix differs in frame {frame}"
+        exported = drop.bvh()
+        ent, box = port.tree_leaves_dfs(exported)
+        _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
+        assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), f"frame {frame}", ignore_entity_on=ties > 0)
