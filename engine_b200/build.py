@@ -26,6 +26,25 @@ NVCC_FLAGS = [
 ]
 
 
+# host-only C++: collider ingestion from .glb files (include/b2col_gltf.h)
+HOST = os.path.join(HERE, "host")
+GLTF_LIB = os.path.join(HERE, "libb2col_gltf.so")
+GLTF_SOURCES = ["gltf_colliders.cpp", "gltf_capi.cpp"]
+GLTF_HEADERS = ["gltf_colliders.h", "../../include/b2col_gltf.h"]
+
+
+def build_gltf(force: bool = False) -> str:
+    if not force and os.path.exists(GLTF_LIB):
+        t = os.path.getmtime(GLTF_LIB)
+        if not any(os.path.getmtime(os.path.join(HOST, f)) > t for f in GLTF_SOURCES + GLTF_HEADERS):
+            return GLTF_LIB
+    cxx = os.environ.get("CXX", "g++")
+    # -ffp-contract=off: DecomposeTransform's sums of squares must round like the reference build's (no FMA)
+    subprocess.check_call([cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-Wall", "-Wextra", "-o", GLTF_LIB,
+                           *[os.path.join(HOST, s) for s in GLTF_SOURCES]])
+    return GLTF_LIB
+
+
 def stale() -> bool:
     if not os.path.exists(LIB):
         return True
@@ -37,6 +56,8 @@ def build(force: bool = False, verbose: bool = False, out: str | None = None) ->
     global LIB
     if out:
         LIB, force = out, True
+    if not out:
+        build_gltf(force)
     if not force and not stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

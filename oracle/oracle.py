@@ -267,6 +267,37 @@ class RefEngine:
         self.lib.refh_normalize(_p(v), _p(out))
         return out
 
+    # -- the reference glTF loader, headless (oracle/gltf_harness.cpp) -------------------------
+    def load_gltf(self, path: str, is_static: bool = True, impl: str = "reference") -> dict:
+        """loadGLTF (reference src/gltf_loader.cpp:101-684) into this engine's Scene.  Returns what it created on the
+        collision path: the new entities in creation order (ids, parent, pos, rot xyzw, scl, tags) and the colliders
+        among them (entity, aabb)."""
+        L = self.lib
+        L.gltfh_load.restype = C.c_uint32
+        L.gltfh_entity_count.restype = C.c_uint32
+        L.gltfh_dump_colliders.restype = C.c_uint32
+        L.gltfh_last_error.restype = C.c_char_p
+        before = int(L.gltfh_entity_count(self.h))
+        # impl "shim": engine_b200/shim's loadGLTFColliders creating entities in the same reference Scene
+        L.gltfh_load_b2.restype = C.c_uint32
+        fn = L.gltfh_load if impl == "reference" else L.gltfh_load_b2
+        root = int(fn(self.h, path.encode(), C.c_int(1 if is_static else 0)))
+        if root == 0:
+            raise RuntimeError(f"{impl} glTF load failed: " + (L.gltfh_last_error() or b"").decode())
+        n = int(L.gltfh_entity_count(self.h)) - before
+        self.n_entities += n
+        parent = np.zeros(n, np.uint32)
+        pos, rot, scl = np.zeros((n, 3), np.float32), np.zeros((n, 4), np.float32), np.zeros((n, 3), np.float32)
+        static = np.zeros(n, np.uint8)
+        tags = np.zeros((n, 64), np.uint8)
+        L.gltfh_dump_entities(self.h, C.c_uint32(before + 1), C.c_uint32(n), _p(parent), _p(pos), _p(rot), _p(scl), _p(static), _p(tags))
+        k = int(L.gltfh_dump_colliders(self.h, None, None))
+        ent, box = np.zeros(k, np.uint32), np.zeros((k, 6), np.float32)
+        L.gltfh_dump_colliders(self.h, _p(ent), _p(box))
+        keep = ent > before
+        return dict(root=root, first=before + 1, ids=np.arange(before + 1, before + 1 + n, dtype=np.uint32), parent=parent, pos=pos, rot=rot, scl=scl,
+                    is_static=static, tags=[bytes(t).split(b"\0")[0].decode() for t in tags], collider_entity=ent[keep], collider_aabb=box[keep])
+
     # -- the test game's player controller, headless (oracle/game_harness.cpp; SURVEY.md 8f row 2) --------------
     GAME_STATE = ("px", "py", "pz", "vx", "vy", "vz", "qx", "qy", "qz", "qw", "yaw", "pitch", "grounded")
 

@@ -4,6 +4,7 @@
 // touches exist.  The real Application is never constructed on this path (Scene(nullptr) elsewhere in the
 // harness); here Scene receives a pointer to this object and only camera_controller.cpp dereferences it.
 #pragma once
+#include <filesystem>
 #include <functional>
 #include <memory>
 #include <string>
@@ -18,6 +19,7 @@ namespace engine {
 class Window;
 class InputManager;
 class SceneManager;
+class Renderer;
 
 class Application {
    public:
@@ -27,6 +29,11 @@ class Application {
     Window* getWindow() { return window_.get(); }
     InputManager* getInputManager() { return input_.get(); }
     SceneManager* getSceneManager() { return scenes_.get(); }
+    // the glTF loader (reference src/gltf_loader.cpp) asks for the renderer and for built-in resources; headless
+    // there is neither: stubs/gltf/renderer.h is an empty Renderer, resources are null handles
+    Renderer* getRenderer() { return nullptr; }
+    template <typename T>
+    std::shared_ptr<T> getResource(const std::string&) { return {}; }
 
    private:
     std::unique_ptr<Window> window_;

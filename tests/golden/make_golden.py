@@ -120,7 +120,67 @@ def kat_fixture():
     print("kat", len(rays), "ray/box pairs,", int(hit.sum()), "hits;", len(mats), "transformBox;", len(nv), "normalize")
 
 
+def gltf_fixture():
+    """Collider ingestion: what the UNMODIFIED reference loadGLTF (src/gltf_loader.cpp) creates
+    for (a) synthetic .glb files from tests/gltf_synth.py — the bytes are stored too — and (b) the reference's own
+    models under test/res/models (only the derived entity / collider arrays are stored, not the assets)."""
+    import glob
+    import tempfile
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from gltf_synth import make_glb
+
+    out = {}
+    names = []
+
+    def record(key, path):
+        try:
+            g = RefEngine().load_gltf(path)
+        except RuntimeError as ex:
+            out[key + "/error"] = np.frombuffer(str(ex).encode(), np.uint8)
+            print(key, "reference throws:", ex)
+            return
+        for k in ("parent", "pos", "rot", "scl", "collider_entity", "collider_aabb"):
+            out[f"{key}/{k}"] = g[k]
+        out[key + "/tags"] = np.frombuffer("\n".join(g["tags"]).encode(), np.uint8)
+        print(key, "entities", len(g["ids"]), "colliders", len(g["collider_entity"]))
+
+    for seed in range(12):
+        data = make_glb(seed, n_nodes=6 + 3 * seed, n_meshes=1 + seed % 5, flavour=["mixed", "single_scene"][seed % 2])
+        key = f"synth{seed}"
+        with tempfile.TemporaryDirectory() as d:
+            path = os.path.join(d, key + ".glb")
+            open(path, "wb").write(data)
+            record(key, path)
+        out[key + "/glb"] = np.frombuffer(data, np.uint8)
+        names.append(key)
+    for path in sorted(glob.glob("/root/reference/test/res/models/*.glb")):
+        key = "model_" + os.path.basename(path)[:-4]
+        record(key, path)
+        names.append(key)
+    out["names"] = np.frombuffer("\n".join(names).encode(), np.uint8)
+    np.savez_compressed(os.path.join(OUT, "gltf.npz"), **out)
+
+
+def game_fixture():
+    """The test game's player controller: 600 frames of the UNMODIFIED reference
+    test/src/camera_controller.cpp + reference CollisionSystem under scripted input."""
+    s = synth.game_scene(140)
+    r = load_ref(s)
+    r.add_camera((8.0, 2.0, 4.0))
+    inp = synth.game_inputs(600)
+    state = r.run_game(inp)
+    np.savez_compressed(os.path.join(OUT, "game_traj.npz"), input=inp, state=state, camera=np.array([8.0, 2.0, 4.0], np.float32))
+    print("game_traj frames", len(inp), "grounded", int(state[:, 12].sum()))
+
+
 if __name__ == "__main__":
+    if "--only-new" in sys.argv:
+        gltf_fixture()
+        game_fixture()
+        sys.exit(0)
+    gltf_fixture()
+    game_fixture()
     kat_fixture()
     scene_fixture("game600", synth.game_scene(600), np.concatenate([synth.game_rays(100), synth.random_rays(2000, extent=100, normalised=False)]))
     scene_fixture("hier1500", synth.hierarchy_scene(1500, 20, extent=50, negative_scale_fraction=0.1), synth.random_rays(4000, extent=60, normalised=False))

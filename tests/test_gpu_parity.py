@@ -478,3 +478,27 @@ def test_game_with_moving_colliders_and_refit_interval(port):
         ent, box = port.tree_leaves_dfs(exported)
         _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
         assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), f"frame {frame}", ignore_entity_on=ties > 0)
+
+
+def test_gltf_ingested_scene_end_to_end(CollisionSystem, port):
+    """.glb -> b2col_gltf (entities, TRS, colliders) -> set_hierarchy / set_trs /
+    set_colliders -> update -> raycast; world AABBs and hits against the oracle."""
+    from engine_b200 import gltf
+    from gltf_synth import make_glb
+
+    s = synth.uniform_boxes(200, seed=61, extent=40)
+    roots = [gltf.append_to_scene(s, make_glb(seed, n_nodes=40, n_meshes=5), stem=f"file{seed}") for seed in (21, 22, 23)]
+    assert roots[0] == 201 and s.n_colliders > 260
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+    assert (bits(cs.world_matrices()) == bits(world[1:])).all()
+    want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+    boxes = cs.world_aabbs()
+    assert (bits(boxes) == bits(want_boxes)).all()
+    rays = synth.random_rays(20_000, seed=62, extent=45)
+    order = cs.leaf_order()
+    got = cs.get_raycasts(rays)
+    assert got["hit"].sum() > 1000
+    assert_raycast_equal(got, port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8), "glTF scene vs brute force")
