@@ -151,21 +151,22 @@ constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
 // kernels
 // =================================================================================================
 
-// TransformSystem::onUpdate (reference src/system_transform.cpp:12-38), one hierarchy level per launch:
-// entities of depth k only depend on depth k-1, which the previous launch finished.
-// world: 16 floats per entity, column-major, indexed by entity ID.
-__global__ void __launch_bounds__(256)
-k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent,
-                  const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world)
+// Scene bounds accumulated by the refit (12 words of the per-frame scratch, all zero between frames):
+//   [0..2] ~ordered(min centroid)   [3..5] ordered(max centroid)      -> Morton grid
+//   [6..8] ~ordered(min finite box coordinate)   [9..11] ordered(max) -> quantisation grid of the traversal nodes
+// raised with atomicMax; finish_header copies them into the blob header.
+constexpr int BOUNDS_WORDS = 12;
+constexpr uint32_t NO_COLLIDER = 0xFFFFFFFFu;
+
+// world matrix of entity e (reference src/system_transform.cpp:22-36): local T*R*S, times the parent's world matrix
+__device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restrict__ parent, const float* __restrict__ pos3, const float4* __restrict__ rot4,
+                                             const float* __restrict__ scl3, const float4* world, float* W)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    const uint32_t e = level_entities[i];
     const float4 q4 = __ldg(rot4 + e);
     const float p[3] = {__ldg(pos3 + 3 * (size_t)e), __ldg(pos3 + 3 * (size_t)e + 1), __ldg(pos3 + 3 * (size_t)e + 2)};
     const float s[3] = {__ldg(scl3 + 3 * (size_t)e), __ldg(scl3 + 3 * (size_t)e + 1), __ldg(scl3 + 3 * (size_t)e + 2)};
     const float q[4] = {q4.x, q4.y, q4.z, q4.w};
-    float L[16], W[16];
+    float L[16];
     local_matrix(p, q, s, L);
     const uint32_t par = __ldg(parent + e);
     if (par != 0u) {
@@ -182,55 +183,42 @@ k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, c
 #pragma unroll
         for (int k = 0; k < 16; ++k) W[k] = L[k];
     }
-    float4* ow = world + 4 * (size_t)e;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
 }
 
-// Refit loop (reference src/system_collisions.cpp:123-132): world AABB = transformBox(local, world_matrix).
-// Also reduces the centroid bounds of the scene (for the Morton grid) into the blob header.
-__global__ void __launch_bounds__(256)
-k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
-        Aabb24* __restrict__ world_aabb, BlobHeader* hdr)
+// transformBox of collider c under matrix M (reference src/system_collisions.cpp:14-41,123-132); folds the box into
+// the thread's running bounds
+__device__ __forceinline__ void refit_one(uint32_t c, const float* M, const Aabb24* __restrict__ col_local, Aabb24* __restrict__ world_aabb, float* cmin,
+                                          float* cmax)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    // [0..2] centroid bounds (Morton grid), [3..5] bounds of all finite box coordinates (node quantisation grid)
-    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
-    if (i < n) {
-        const uint32_t e = __ldg(col_entity + i);
-        float M[16];
-        const float4* pw = world + 4 * (size_t)e;
+    const float2* lp = reinterpret_cast<const float2*>(col_local + c);
+    const float2 l0 = __ldg(lp), l1 = __ldg(lp + 1), l2 = __ldg(lp + 2);
+    const float lmin[3] = {l0.x, l0.y, l1.x}, lmax[3] = {l1.y, l2.x, l2.y};
+    const Box b = transform_box(lmin, lmax, M);
+    float2* op = reinterpret_cast<float2*>(world_aabb + c);
+    op[0] = make_float2(b.lo[0], b.lo[1]);
+    op[1] = make_float2(b.lo[2], b.hi[0]);
+    op[2] = make_float2(b.hi[1], b.hi[2]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float4 v = pw[c];
-            M[4 * c] = v.x; M[4 * c + 1] = v.y; M[4 * c + 2] = v.z; M[4 * c + 3] = v.w;
+    for (int k = 0; k < 3; ++k) {
+        const float ctr = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
+        if (isfinite(ctr)) {
+            cmin[k] = ctr;
+            cmax[k] = ctr;
         }
-        const float2* lp = reinterpret_cast<const float2*>(col_local + i);
-        const float2 l0 = __ldg(lp), l1 = __ldg(lp + 1), l2 = __ldg(lp + 2);
-        const float lmin[3] = {l0.x, l0.y, l1.x}, lmax[3] = {l1.y, l2.x, l2.y};
-        const Box b = transform_box(lmin, lmax, M);
-        float2* op = reinterpret_cast<float2*>(world_aabb + i);
-        op[0] = make_float2(b.lo[0], b.lo[1]);
-        op[1] = make_float2(b.lo[2], b.hi[0]);
-        op[2] = make_float2(b.hi[1], b.hi[2]);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float c = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
-            if (isfinite(c)) {
-                cmin[k] = c;
-                cmax[k] = c;
-            }
-            if (isfinite(b.lo[k])) {
-                cmin[3 + k] = b.lo[k];
-                cmax[3 + k] = b.lo[k];
-            }
-            if (isfinite(b.hi[k])) {
-                cmin[3 + k] = fminf(cmin[3 + k], b.hi[k]);
-                cmax[3 + k] = fmaxf(cmax[3 + k], b.hi[k]);
-            }
+        if (isfinite(b.lo[k])) {
+            cmin[3 + k] = b.lo[k];
+            cmax[3 + k] = b.lo[k];
+        }
+        if (isfinite(b.hi[k])) {
+            cmin[3 + k] = fminf(cmin[3 + k], b.hi[k]);
+            cmax[3 + k] = fmaxf(cmax[3 + k], b.hi[k]);
         }
     }
-    // block reduction: warp shuffles, then one atomic per warp and axis
+}
+
+// block reduction of the per-thread bounds: warp shuffles, then one atomic per block and word (256-thread blocks)
+__device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t* bounds)
+{
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
 #pragma unroll
@@ -257,26 +245,90 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
             b = fmaxf(b, smax[w][k]);
         }
         if (a <= b) {  // false when the block saw no finite value
-            // bounds_min_inv/bounds_max and box_min_inv/box_max are laid out as two consecutive groups of 3+3 words
-            uint32_t* mn = k < 3 ? &hdr->bounds_min_inv[k] : &hdr->box_min_inv[k - 3];
-            uint32_t* mx = k < 3 ? &hdr->bounds_max[k] : &hdr->box_max[k - 3];
-            atomicMax(mn, ~float_to_ordered(a));
-            atomicMax(mx, float_to_ordered(b));
+            const int base = k < 3 ? 0 : 6, kk = k < 3 ? k : k - 3;
+            atomicMax(&bounds[base + kk], ~float_to_ordered(a));
+            atomicMax(&bounds[base + 3 + kk], float_to_ordered(b));
         }
     }
 }
 
+// TransformSystem::onUpdate (reference src/system_transform.cpp:12-38), one hierarchy level per launch:
+// entities of depth k only depend on depth k-1, which the previous launch finished.
+// world: 16 floats per entity, column-major, indexed by entity ID.
+__global__ void __launch_bounds__(256)
+k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent,
+                  const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t e = level_entities[i];
+    float W[16];
+    entity_world(e, parent, pos3, rot4, scl3, world, W);
+    float4* ow = world + 4 * (size_t)e;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
+}
+
+// The same level, FUSED with the refit of the colliders that sit on this level's entities (b2col_update's normal
+// path): the world matrix is still in registers when transformBox needs it, so the refit's 64-byte re-read per
+// collider and one launch disappear.  col_of_entity[e] = index of e's collider or NO_COLLIDER.
+__global__ void __launch_bounds__(256)
+k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
+                        const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
+                        const Aabb24* __restrict__ col_local, Aabb24* __restrict__ world_aabb, uint32_t* bounds)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
+    if (i < count) {
+        const uint32_t e = level_entities[i];
+        float W[16];
+        entity_world(e, parent, pos3, rot4, scl3, world, W);
+        float4* ow = world + 4 * (size_t)e;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
+        const uint32_t c = __ldg(col_of_entity + e);
+        if (c != NO_COLLIDER) refit_one(c, W, col_local, world_aabb, cmin, cmax);
+    }
+    bounds_reduce(cmin, cmax, bounds);
+}
+
+// Refit loop alone (reference src/system_collisions.cpp:123-132): world AABB = transformBox(local, world_matrix), for
+// callers that supply world matrices themselves or propagate separately.  Also reduces the scene bounds.
+__global__ void __launch_bounds__(256)
+k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
+        Aabb24* __restrict__ world_aabb, uint32_t* bounds)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
+    if (i < n) {
+        const uint32_t e = __ldg(col_entity + i);
+        float M[16];
+        const float4* pw = world + 4 * (size_t)e;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float4 v = pw[c];
+            M[4 * c] = v.x; M[4 * c + 1] = v.y; M[4 * c + 2] = v.z; M[4 * c + 3] = v.w;
+        }
+        refit_one(i, M, col_local, world_aabb, cmin, cmax);
+    }
+    bounds_reduce(cmin, cmax, bounds);
+}
+
 // Header fields every build needs besides the bounds: leaf / node counts and the quantisation grid of the
 // traversal nodes, derived from the box bounds k_refit reduced into the header.  One thread.
-__device__ void finish_header(BlobHeader* hdr, uint32_t n, float T)
+__device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t n, float T)
 {
     hdr->magic = BLOB_MAGIC;
     hdr->n_leaves = n;
     hdr->n_nodes = n > 1u ? n - 1u : 1u;
     float bmin[3], bmax[3];
     for (int k = 0; k < 3; ++k) {
-        bmin[k] = ordered_to_float(~hdr->box_min_inv[k]);
-        bmax[k] = ordered_to_float(hdr->box_max[k]);
+        hdr->bounds_min_inv[k] = bounds[k];
+        hdr->bounds_max[k] = bounds[3 + k];
+        hdr->box_min_inv[k] = bounds[6 + k];
+        hdr->box_max[k] = bounds[9 + k];
+        bmin[k] = ordered_to_float(~bounds[6 + k]);
+        bmax[k] = ordered_to_float(bounds[9 + k]);
     }
     hdr->grid = make_grid(bmin, bmax, T);
 }
@@ -284,7 +336,7 @@ __device__ void finish_header(BlobHeader* hdr, uint32_t n, float T)
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway).
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
@@ -293,8 +345,8 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
     float smin[3], sinv[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const float lo = ordered_to_float(~hdr->bounds_min_inv[k]);
-        const float hi = ordered_to_float(hdr->bounds_max[k]);
+        const float lo = ordered_to_float(~bounds[k]);
+        const float hi = ordered_to_float(bounds[3 + k]);
         const float ext = hi - lo;
         smin[k] = lo;
         sinv[k] = (ext > 0.0f && isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
@@ -314,12 +366,12 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, int
         const uint32_t c = shist[p][threadIdx.x];
         if (c) atomicAdd(&ghist[p * RS_RADIX + threadIdx.x], c);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, n, T);
+    if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, bounds, n, T);
 }
 
 // Refit-only frames (b2col_refit) skip k_morton: this fills the header fields k_morton would have written,
 // from the bounds k_refit has just reduced.
-__global__ void k_header(uint32_t n, BlobHeader* hdr, float T) { finish_header(hdr, n, T); }
+__global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T) { finish_header(hdr, bounds, n, T); }
 
 // LBVH hierarchy + bounds, production form: traversal structure only, merged in grid space — the per-thread
 // climb of build_from_leaf_q (b2col_bvh.cuh), with the arrival exchange moved into SHARED memory for every
@@ -336,8 +388,11 @@ __global__ void k_header(uint32_t n, BlobHeader* hdr, float T) { finish_header(h
 constexpr int BUILD_BLOCK = 256;
 __global__ void __launch_bounds__(BUILD_BLOCK)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
-        const uint32_t* __restrict__ col_entity, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr)
+        const uint32_t* __restrict__ col_entity, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
 {
+    // The frame's zero-initialised scratch (scene bounds, digit histograms, tile tickets, look-back words) has been
+    // consumed by the kernels before this one: wipe it here for the next frame instead of a memset per frame.
+    for (uint32_t w = blockIdx.x * BUILD_BLOCK + threadIdx.x; w < scratch_words; w += gridDim.x * BUILD_BLOCK) scratch[w] = 0u;
     __shared__ uint32_t s_lev[BUILD_BLOCK + 1];     // s_lev[j] = level of split b0-1+j (j = 0: left boundary, j = BUILD_BLOCK: right boundary)
     __shared__ uint32_t s_wmax[2][BUILD_BLOCK / 32];
     __shared__ uint8_t s_local[BUILD_BLOCK + 1];
@@ -725,6 +780,11 @@ struct b2col_ctx {
     bool exact_nodes_valid = false;      // d_nodes_full matches the tree in the blob
     void* xch_ready = nullptr;           // the d_xch allocation whose words are all in the "nobody arrived" state
     size_t zero_bytes = 0;
+    bool scratch_clean = false;          // d_zero[0, zero_bytes) is all zero (left so by the last k_build)
+    // fused propagate + refit: collider index of every entity (NO_COLLIDER = none); needs one collider per entity at most
+    std::vector<uint32_t> h_col_entity;
+    DevBuf d_col_of_entity;
+    bool fuse_map_valid = false, fusable = false;
     int sorted_side = 0;
     // traversal structure: one allocation [BlobHeader | QNode x (N-1) | LeafRec x N]
     DevBuf d_blob;
@@ -743,6 +803,11 @@ struct b2col_ctx {
     size_t e2e_chunk = 2u << 20;
     int trace_grid = 148 * 8, fetch_threshold = 25;
     cudaEvent_t events[16] = {};
+    // dev: B2COL_PHASE_EVENTS=1 records an event after every phase of b2col_update / b2col_refit (b2col_debug_phase_ms)
+    bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
+    bool phase_timing = false;
+    cudaEvent_t phase_ev[16] = {};
+    int n_phase = 0;
 };
 
 namespace {
@@ -810,6 +875,11 @@ inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
     const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
     return reinterpret_cast<LeafRec*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader) + n_nodes * sizeof(QNode));
 }
+
+#define PHASE(ctx_)                                                                                         \
+    do {                                                                                                    \
+        if ((ctx_)->phase_timing && (ctx_)->n_phase < 16) cudaEventRecord((ctx_)->phase_ev[(ctx_)->n_phase++], (ctx_)->stream); \
+    } while (0)
 
 #define GUARD(st_expr)                      \
     do {                                    \
@@ -891,6 +961,10 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
+        if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
+        if (c->phase_timing)
+            for (auto& ev : c->phase_ev) cudaEventCreate(&ev);
         if (const char* e = getenv("B2COL_TRACE_FETCH_THRESHOLD")) c->fetch_threshold = std::min(32, std::max(1, atoi(e)));
         c->trace_grid = sms * per_sm;
     }
@@ -904,7 +978,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
-                      &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
+                      &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
                       &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& ev : ctx->events)
@@ -961,6 +1035,7 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
     ctx->have_hierarchy = true;
     ctx->have_trs = false;
     ctx->world_fresh = false;
+    ctx->fuse_map_valid = false;
     return B2COL_OK;
 }
 
@@ -1019,6 +1094,8 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
         max_e = std::max(max_e, h_entity[i]);
     }
     ctx->max_col_entity = max_e;
+    ctx->h_col_entity.assign(h_entity, h_entity + n);
+    ctx->fuse_map_valid = false;
     GUARD(ensure(ctx, ctx->d_col_entity, (size_t)n * 4 + 4));
     GUARD(ensure(ctx, ctx->d_col_local, (size_t)n * 24 + 8));
     if (n) {
@@ -1029,6 +1106,16 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->n_colliders = n;
     ctx->have_colliders = true;
     ctx->topology_valid = false;  // a new collider set needs a new tree
+    return B2COL_OK;
+}
+
+// hierarchy + bounds from the sorted keys in d_keys/d_vals[side]
+static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
+{
+    LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+           ctx->d_world_aabb.as<Aabb24>(), ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
+           ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+    ctx->scratch_clean = true;  // k_build leaves every scratch word zero
     return B2COL_OK;
 }
 
@@ -1056,6 +1143,79 @@ b2col_status b2col_propagate(b2col_ctx* ctx)
     return B2COL_OK;
 }
 
+namespace {
+
+// per-frame scratch, all zero when a frame starts (k_build wipes it for the next one):
+//   [bounds: 16 words][digit histograms: RS_MAX_PASSES x 256][tile tickets: 16][look-back words of every pass]
+constexpr size_t SCRATCH_BOUNDS_WORDS = 16;
+static_assert(BOUNDS_WORDS <= (int)SCRATCH_BOUNDS_WORDS, "bounds fit their scratch slot");
+inline uint32_t* scratch_bounds(const b2col_ctx* c) { return c->d_zero.as<uint32_t>(); }
+inline uint32_t* scratch_ghist(const b2col_ctx* c) { return c->d_zero.as<uint32_t>() + SCRATCH_BOUNDS_WORDS; }
+inline uint32_t* scratch_tickets(const b2col_ctx* c) { return scratch_ghist(c) + RS_MAX_PASSES * RS_RADIX; }
+inline uint32_t* scratch_lookback(const b2col_ctx* c) { return scratch_tickets(c) + 16; }
+
+// make sure the scratch exists at `bytes` and is zero
+b2col_status prepare_scratch(b2col_ctx* ctx, size_t bytes)
+{
+    void* before = ctx->d_zero.p;
+    GUARD(ensure(ctx, ctx->d_zero, bytes));
+    if (ctx->d_zero.p != before || bytes > ctx->zero_bytes) ctx->scratch_clean = false;  // new memory, or words k_build never wiped
+    ctx->zero_bytes = bytes;
+    if (!ctx->scratch_clean) CU(cudaMemsetAsync(ctx->d_zero.p, 0, bytes, ctx->stream));
+    ctx->scratch_clean = false;  // about to be used; k_build restores it
+    return B2COL_OK;
+}
+
+// entity -> collider index map of the fused propagate + refit kernel; fusable only with at most one collider per entity
+b2col_status prepare_fuse_map(b2col_ctx* ctx)
+{
+    if (ctx->fuse_map_valid) return B2COL_OK;
+    const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
+    ctx->fusable = false;
+    ctx->fuse_map_valid = true;
+    if (n == 0 || ctx->max_col_entity > E || ctx->h_col_entity.size() != n) return B2COL_OK;
+    std::vector<uint32_t> map((size_t)E + 1, NO_COLLIDER);
+    for (uint32_t c = 0; c < n; ++c) {
+        uint32_t& slot = map[ctx->h_col_entity[c]];
+        if (slot != NO_COLLIDER) return B2COL_OK;  // two colliders on one entity: keep the separate refit kernel
+        slot = c;
+    }
+    GUARD(ensure(ctx, ctx->d_col_of_entity, ((size_t)E + 1) * 4));
+    CU(cudaMemcpyAsync(ctx->d_col_of_entity.p, map.data(), ((size_t)E + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));  // `map` is a local
+    ctx->fusable = true;
+    return B2COL_OK;
+}
+
+// a1 + a2: world matrices and world AABBs of the frame (+ scene bounds into the scratch)
+b2col_status enqueue_transform_refit(b2col_ctx* ctx)
+{
+    const uint32_t n = ctx->n_colliders;
+    const bool propagate = !ctx->world_external && !ctx->world_fresh;
+    if (propagate && ctx->fusable && !ctx->no_fuse) {
+        const size_t rows = (size_t)ctx->n_entities + 1;
+        GUARD(ensure(ctx, ctx->d_world, rows * 64));
+        const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
+        for (size_t k = 0; k < n_levels; ++k) {
+            const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
+            if (!cnt) continue;
+            LAUNCH(ctx, k_propagate_refit_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+                   ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_of_entity.as<uint32_t>(),
+                   ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<Aabb24>(), scratch_bounds(ctx));
+        }
+        PHASE(ctx);
+        return B2COL_OK;
+    }
+    if (propagate) GUARD(enqueue_propagate(ctx));
+    PHASE(ctx);
+    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
+           ctx->d_world_aabb.as<Aabb24>(), scratch_bounds(ctx));
+    PHASE(ctx);
+    return B2COL_OK;
+}
+
+}  // namespace
+
 b2col_status b2col_update(b2col_ctx* ctx)
 {
     if (!ctx) return B2COL_ERR_INVALID;
@@ -1064,18 +1224,18 @@ b2col_status b2col_update(b2col_ctx* ctx)
         return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
     CU(cudaSetDevice(ctx->device));
     const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
-
-    // ---- a1: world matrices -------------------------------------------------------------------
-    if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));
+    ctx->n_phase = 0;
+    PHASE(ctx);  // 0: start
 
     // ---- allocate the frame's buffers -----------------------------------------------------------
     const size_t blob_bytes = blob_size_for(n);
     GUARD(ensure(ctx, ctx->d_blob, blob_bytes));
     ctx->blob_bytes = blob_bytes;
     ctx->tree_leaves = n;
-    CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
     ctx->topology_valid = false;
     if (n == 0) {
+        if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));  // world matrices are still the caller's to read back
+        CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
         ctx->have_tree = true;  // empty tree: header says n_leaves = 0, every query misses
         ctx->topology_valid = true;
         return B2COL_OK;
@@ -1108,37 +1268,35 @@ b2col_status b2col_update(b2col_ctx* ctx)
     }
     ctx->passes = (3 * ctx->bits - ctx->drop + RS_BITS - 1) / RS_BITS;
     const uint32_t tiles = cdiv(n, RS_TILE);
-    const size_t hist_bytes = (size_t)RS_MAX_PASSES * RS_RADIX * 4;
-    const size_t ticket_bytes = 64;
     const size_t lb_words_per_pass = ((size_t)tiles + (tiles + LB_GROUP - 1) / LB_GROUP) * RS_RADIX;  // tile counts + group status
-    const size_t lb_bytes = (size_t)ctx->passes * lb_words_per_pass * 4;
-    ctx->zero_bytes = hist_bytes + ticket_bytes + lb_bytes;
-    GUARD(ensure(ctx, ctx->d_zero, ctx->zero_bytes));
-    CU(cudaMemsetAsync(ctx->d_zero.p, 0, ctx->zero_bytes, ctx->stream));
-    uint32_t* ghist = ctx->d_zero.as<uint32_t>();
-    uint32_t* tickets = ghist + RS_MAX_PASSES * RS_RADIX;
-    uint32_t* lookback = tickets + 16;
+    GUARD(prepare_scratch(ctx, (SCRATCH_BOUNDS_WORDS + (size_t)RS_MAX_PASSES * RS_RADIX + 16 + (size_t)ctx->passes * lb_words_per_pass) * 4));
+    if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
+    uint32_t* ghist = scratch_ghist(ctx);
+    uint32_t* tickets = scratch_tickets(ctx);
+    uint32_t* lookback = scratch_lookback(ctx);
+    PHASE(ctx);  // 1: set-up
 
-    // ---- a2: refit + centroid bounds ------------------------------------------------------------
-    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
-           ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx));
+    // ---- a1 + a2: world matrices, world AABBs, scene bounds ---------------------------------------
+    GUARD(enqueue_transform_refit(ctx));  // phases 2 (propagate) and 3 (refit); one phase when fused
 
     // ---- a4: LBVH build -------------------------------------------------------------------------
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T, ctx->d_keys[0].as<uint64_t>(),
-               ctx->d_vals[0].as<uint32_t>(), ghist);
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), scratch_bounds(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T,
+               ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
+    PHASE(ctx);  // morton
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
         LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
                lookback + (size_t)p * lb_words_per_pass, tickets + p);
         side ^= 1;
+        PHASE(ctx);  // radix pass p
     }
     ctx->sorted_side = side;
-    LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
-           ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx));
+    GUARD(launch_build(ctx, n, side));
+    PHASE(ctx);  // last: build
     ctx->have_tree = true;
     ctx->topology_valid = true;
     ++ctx->full_builds;
@@ -1154,21 +1312,24 @@ b2col_status b2col_refit(b2col_ctx* ctx)
         return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
     CU(cudaSetDevice(ctx->device));
     const uint32_t n = ctx->n_colliders;
-    if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));
-    if (n == 0) return B2COL_OK;
+    ctx->n_phase = 0;
+    if (n == 0) {
+        if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));
+        return B2COL_OK;
+    }
     if (ctx->max_col_entity > ctx->n_entities)
         return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, ctx->n_entities);
     // Same tree shape, new boxes: the hierarchy is a pure function of the SORTED KEYS of the last full build, which
     // are still in d_keys/d_vals[sorted_side], so k_build re-emits the same nodes (same indices, same leaf order —
-    // the order that decides tie winners) around the boxes k_refit has just written.  Skips Morton + the radix sort.
-    CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
+    // the order that decides tie winners) around the boxes the refit has just written.  Skips Morton + the radix sort.
+    GUARD(prepare_scratch(ctx, ctx->zero_bytes));
+    if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
     ctx->exact_nodes_valid = false;
-    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
-           ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx));
-    LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), ctx->T);
-    const int side = ctx->sorted_side;
-    LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(), ctx->d_world_aabb.as<Aabb24>(),
-           ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx));
+    PHASE(ctx);
+    GUARD(enqueue_transform_refit(ctx));
+    LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
+    GUARD(launch_build(ctx, n, ctx->sorted_side));
+    PHASE(ctx);
     ++ctx->refits;
     return B2COL_OK;
 }
@@ -1407,6 +1568,17 @@ b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t byt
     ctx->have_tree = true;
     ctx->topology_valid = false;  // a foreign tree: its sorted keys are not on this ctx
     return B2COL_OK;
+}
+
+// dev only (not in include/b2col.h): ms between consecutive phase events of the last b2col_update; returns the count
+int b2col_debug_phase_ms(b2col_ctx* ctx, float* out, int cap)
+{
+    if (!ctx || !ctx->phase_timing || ctx->n_phase < 2) return 0;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    int k = 0;
+    for (int i = 1; i < ctx->n_phase && k < cap; ++i, ++k) cudaEventElapsedTime(out + k, ctx->phase_ev[i - 1], ctx->phase_ev[i]);
+    return k;
 }
 
 #ifdef B2_SORT_TIMING

@@ -20,7 +20,14 @@ def main():
         for _ in range(K):
             cs.on_update(wait=False)
         cs.event_record(1)
-        print(f"{name:32s} update {cs.event_elapsed_ms(0, 1) / K * 1e3:8.1f} us", flush=True)
+        upd = cs.event_elapsed_ms(0, 1) / K * 1e3
+        for _ in range(5):
+            cs.on_update_refit(wait=False)
+        cs.event_record(2)
+        for _ in range(K):
+            cs.on_update_refit(wait=False)
+        cs.event_record(3)
+        print(f"{name:32s} update {upd:8.1f} us   refit-only {cs.event_elapsed_ms(2, 3) / K * 1e3:8.1f} us", flush=True)
         cs.close()
 
 
