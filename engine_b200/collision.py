@@ -24,9 +24,9 @@ def _rays(rays) -> np.ndarray:
 
 
 class CollisionSystem:
-    def __init__(self, device: int = 0, max_distance: float = 1000.0, morton_bits_per_axis: int = 0):
+    def __init__(self, device: int = 0, max_distance: float = 1000.0, morton_bits_per_axis: int = 0, use_cuda_graph: bool = False):
         self.lib = capi.load()
-        cfg = capi.Config(device=device, max_distance=max_distance, morton_bits_per_axis=morton_bits_per_axis, use_cuda_graph=0)
+        cfg = capi.Config(device=device, max_distance=max_distance, morton_bits_per_axis=morton_bits_per_axis, use_cuda_graph=int(use_cuda_graph))
         h = C.c_void_p()
         st = self.lib.b2col_create(C.byref(h), C.byref(cfg))
         if st != capi.OK:

@@ -187,17 +187,19 @@ __device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restr
 
 // transformBox of collider c under matrix M (reference src/system_collisions.cpp:14-41,123-132); folds the box into
 // the thread's running bounds
-__device__ __forceinline__ void refit_one(uint32_t c, const float* M, const Aabb24* __restrict__ col_local, Aabb24* __restrict__ world_aabb, float* cmin,
-                                          float* cmax)
+// The result is stored as a 32-byte record {lo, hi, entity, collider index} — the layout of a LeafRec, one sector —
+// so that the build's gather by primitive index costs ONE sector per leaf (a 24-byte AABB at 24-byte stride
+// straddles two sectors half of the time, and the entity ID was a third).
+__device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const float* M, const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec,
+                                          float* cmin, float* cmax)
 {
     const float2* lp = reinterpret_cast<const float2*>(col_local + c);
     const float2 l0 = __ldg(lp), l1 = __ldg(lp + 1), l2 = __ldg(lp + 2);
     const float lmin[3] = {l0.x, l0.y, l1.x}, lmax[3] = {l1.y, l2.x, l2.y};
     const Box b = transform_box(lmin, lmax, M);
-    float2* op = reinterpret_cast<float2*>(world_aabb + c);
-    op[0] = make_float2(b.lo[0], b.lo[1]);
-    op[1] = make_float2(b.lo[2], b.hi[0]);
-    op[2] = make_float2(b.hi[1], b.hi[2]);
+    float4* op = reinterpret_cast<float4*>(world_rec + c);
+    op[0] = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
+    op[1] = make_float4(b.hi[1], b.hi[2], __uint_as_float(entity), __uint_as_float(c));
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float ctr = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
@@ -275,7 +277,7 @@ k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, c
 __global__ void __launch_bounds__(256)
 k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
                         const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
-                        const Aabb24* __restrict__ col_local, Aabb24* __restrict__ world_aabb, uint32_t* bounds)
+                        const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
@@ -287,7 +289,7 @@ k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t co
 #pragma unroll
         for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
         const uint32_t c = __ldg(col_of_entity + e);
-        if (c != NO_COLLIDER) refit_one(c, W, col_local, world_aabb, cmin, cmax);
+        if (c != NO_COLLIDER) refit_one(c, e, W, col_local, world_rec, cmin, cmax);
     }
     bounds_reduce(cmin, cmax, bounds);
 }
@@ -296,7 +298,7 @@ k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t co
 // callers that supply world matrices themselves or propagate separately.  Also reduces the scene bounds.
 __global__ void __launch_bounds__(256)
 k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
-        Aabb24* __restrict__ world_aabb, uint32_t* bounds)
+        LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
@@ -309,7 +311,7 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
             const float4 v = pw[c];
             M[4 * c] = v.x; M[4 * c + 1] = v.y; M[4 * c + 2] = v.z; M[4 * c + 3] = v.w;
         }
-        refit_one(i, M, col_local, world_aabb, cmin, cmax);
+        refit_one(i, e, M, col_local, world_rec, cmin, cmax);
     }
     bounds_reduce(cmin, cmax, bounds);
 }
@@ -336,7 +338,7 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway).
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
@@ -353,9 +355,9 @@ k_morton(uint32_t n, const Aabb24* __restrict__ world_aabb, BlobHeader* hdr, con
     }
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float2* bp = reinterpret_cast<const float2*>(world_aabb + i);
-        const float2 b0 = bp[0], b1 = bp[1], b2 = bp[2];
-        const float lo[3] = {b0.x, b0.y, b1.x}, hi[3] = {b1.y, b2.x, b2.y};
+        const float4* bp = reinterpret_cast<const float4*>(world_rec + i);
+        const float4 b0 = bp[0], b1 = bp[1];
+        const float lo[3] = {b0.x, b0.y, b0.z}, hi[3] = {b0.w, b1.x, b1.y};
         const uint64_t key = morton_key(lo, hi, smin, sinv, bits, drop);
         keys[i] = key;
         vals[i] = i;
@@ -385,10 +387,11 @@ __global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, fl
 // (the split between sorted positions p and p+1) spans the leaves between the nearest HIGHER splits on either
 // side, so it is local iff a higher split exists on both sides within the block, counting the block's two
 // boundary splits: prefix-max(level)[p-1] > level[p] < suffix-max(level)[p+1].
+// (Measured and dropped, profiles/r1_d_experiments.txt: writing the leaf records from the last radix pass, where the
+// gathers are independent — the pass grew by 14 us, this kernel shrank by 4: here the gather hides under the climb.)
 constexpr int BUILD_BLOCK = 256;
 __global__ void __launch_bounds__(BUILD_BLOCK)
-k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
-        const uint32_t* __restrict__ col_entity, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
+k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
 {
     // The frame's zero-initialised scratch (scene bounds, digit histograms, tile tickets, look-back words) has been
     // consumed by the kernels before this one: wipe it here for the next frame instead of a memset per frame.
@@ -409,14 +412,7 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     uint64_t key = 0ull;
     uint32_t lev_l = LEVEL_END;
     if (valid) {
-        const uint32_t prim = sorted_prim[i];
-        const float2* bp = reinterpret_cast<const float2*>(world_aabb + prim);
-        const float2 b0v = __ldg(bp), b1v = __ldg(bp + 1), b2v = __ldg(bp + 2);
-        LeafRec rec;
-        rec.lo[0] = b0v.x; rec.lo[1] = b0v.y; rec.lo[2] = b1v.x;
-        rec.hi[0] = b1v.y; rec.hi[1] = b2v.x; rec.hi[2] = b2v.y;
-        rec.entity = __ldg(col_entity + prim);
-        rec.prim = prim;
+        const LeafRec rec = DevOps::load_leaf(&world_rec[sorted_prim[i]]);  // one 256-bit load: the world record IS the leaf record
         DevOps::store_leaf(&leaves[i], rec);
         box = quantise_box(rec.lo, rec.hi, grid);
         key = keys[i];
@@ -516,7 +512,7 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
 // Same hierarchy with exact (full-precision) two-slot nodes: only run on demand, as the source of the
 // BiTreeNode export (b2col_export_bitreenode).  Writes nothing into the traversal structure.
 __global__ void __launch_bounds__(256)
-k_build_exact(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const Aabb24* __restrict__ world_aabb,
+k_build_exact(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_aabb,
               const uint32_t* __restrict__ col_entity, Node* nodes, uint32_t* other_bound, const BlobHeader* hdr, uint32_t* root_out)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -804,6 +800,14 @@ struct b2col_ctx {
     int trace_grid = 148 * 8, fetch_threshold = 25;
     cudaEvent_t events[16] = {};
     // dev: B2COL_PHASE_EVENTS=1 records an event after every phase of b2col_update / b2col_refit (b2col_debug_phase_ms)
+    // CUDA graphs of the frame's kernel sequence (cfg.use_cuda_graph): [0] full update, [1] refit-only frame
+    struct GraphSlot {
+        cudaGraphExec_t exec = nullptr;
+        uint64_t key[4] = {0, 0, 0, 0};
+        uint64_t launches = 0;
+    } graphs[2];
+    bool use_graph = false;
+    uint64_t buffers_gen = 0, shape_gen = 0, graph_replays = 0;
     bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
     bool phase_timing = false;
     cudaEvent_t phase_ev[16] = {};
@@ -851,6 +855,7 @@ b2col_status ensure(b2col_ctx* ctx, DevBuf& b, size_t bytes)
     const size_t want = bytes + bytes / 8 + 256;  // slack: scenes grow a little every frame
     CU(cudaMalloc(&b.p, want));
     b.cap = want;
+    ++ctx->buffers_gen;  // captured graphs hold the old pointers
     return B2COL_OK;
 }
 
@@ -963,6 +968,8 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
+        c->use_graph = cfg && cfg->use_cuda_graph != 0;
+        if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
         if (c->phase_timing)
             for (auto& ev : c->phase_ev) cudaEventCreate(&ev);
         if (const char* e = getenv("B2COL_TRACE_FETCH_THRESHOLD")) c->fetch_threshold = std::min(32, std::max(1, atoi(e)));
@@ -981,6 +988,8 @@ void b2col_destroy(b2col_ctx* ctx)
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
                       &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
+    for (auto& g : ctx->graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->pipe_events) cudaEventDestroy(ev);
@@ -1036,6 +1045,7 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
     ctx->have_trs = false;
     ctx->world_fresh = false;
     ctx->fuse_map_valid = false;
+    ++ctx->shape_gen;
     return B2COL_OK;
 }
 
@@ -1080,6 +1090,7 @@ b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const
     CU(cudaStreamSynchronize(ctx->stream));
     ctx->n_entities = n_entities;
     ctx->world_external = true;
+    ++ctx->shape_gen;
     return B2COL_OK;
 }
 
@@ -1096,6 +1107,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->max_col_entity = max_e;
     ctx->h_col_entity.assign(h_entity, h_entity + n);
     ctx->fuse_map_valid = false;
+    ++ctx->shape_gen;
     GUARD(ensure(ctx, ctx->d_col_entity, (size_t)n * 4 + 4));
     GUARD(ensure(ctx, ctx->d_col_local, (size_t)n * 24 + 8));
     if (n) {
@@ -1113,7 +1125,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
 static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
 {
     LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
-           ctx->d_world_aabb.as<Aabb24>(), ctx->d_col_entity.as<uint32_t>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
+           ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
            ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
     ctx->scratch_clean = true;  // k_build leaves every scratch word zero
     return B2COL_OK;
@@ -1193,15 +1205,13 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
     const uint32_t n = ctx->n_colliders;
     const bool propagate = !ctx->world_external && !ctx->world_fresh;
     if (propagate && ctx->fusable && !ctx->no_fuse) {
-        const size_t rows = (size_t)ctx->n_entities + 1;
-        GUARD(ensure(ctx, ctx->d_world, rows * 64));
         const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
         for (size_t k = 0; k < n_levels; ++k) {
             const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
             if (!cnt) continue;
             LAUNCH(ctx, k_propagate_refit_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
                    ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_of_entity.as<uint32_t>(),
-                   ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<Aabb24>(), scratch_bounds(ctx));
+                   ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
         }
         PHASE(ctx);
         return B2COL_OK;
@@ -1209,8 +1219,91 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
     if (propagate) GUARD(enqueue_propagate(ctx));
     PHASE(ctx);
     LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
-           ctx->d_world_aabb.as<Aabb24>(), scratch_bounds(ctx));
+           ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
     PHASE(ctx);
+    return B2COL_OK;
+}
+
+inline size_t lookback_words_per_pass(uint32_t tiles) { return ((size_t)tiles + (tiles + LB_GROUP - 1) / LB_GROUP) * RS_RADIX; }  // tile counts + group status
+
+// The frame's kernels, nothing else (no allocation, no memset, no synchronisation): capturable.
+//   full:  [propagate+refit per level | propagate per level, refit] , Morton, radix passes, hierarchy
+//   !full: [ ... same transform/refit ... ], header, hierarchy on the sorted keys of the last full build
+b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
+{
+    const uint32_t n = ctx->n_colliders;
+    GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
+    if (!full) {
+        LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
+        GUARD(launch_build(ctx, n, ctx->sorted_side));
+        PHASE(ctx);
+        return B2COL_OK;
+    }
+    const uint32_t tiles = cdiv(n, RS_TILE);
+    const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
+    uint32_t* ghist = scratch_ghist(ctx);
+    {
+        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T,
+               ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
+    }
+    PHASE(ctx);  // morton
+    int side = 0;
+    for (int p = 0; p < ctx->passes; ++p) {
+        LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
+               scratch_lookback(ctx) + (size_t)p * lb_words_per_pass, scratch_tickets(ctx) + p);
+        side ^= 1;
+        PHASE(ctx);  // radix pass p
+    }
+    ctx->sorted_side = side;
+    GUARD(launch_build(ctx, n, side));
+    PHASE(ctx);  // last: build
+    return B2COL_OK;
+}
+
+// enqueue_frame, through a CUDA graph when the context asks for one: captured once per (shape, buffers) and replayed
+// — one launch per frame instead of 7-10, and no host-side gaps between the short kernels of the sort.
+b2col_status run_frame(b2col_ctx* ctx, bool full)
+{
+    if (!ctx->use_graph || ctx->phase_timing) return enqueue_frame(ctx, full);
+    b2col_ctx::GraphSlot& g = ctx->graphs[full ? 0 : 1];
+    const bool propagate = !ctx->world_external && !ctx->world_fresh;
+    const uint64_t key[4] = {ctx->buffers_gen, ctx->shape_gen,
+                             (uint64_t)propagate | ((uint64_t)(ctx->fusable && !ctx->no_fuse) << 1) | ((uint64_t)ctx->passes << 8) | ((uint64_t)ctx->bits << 16) |
+                                 ((uint64_t)ctx->drop << 24) | ((uint64_t)ctx->sorted_side << 32),
+                             ((uint64_t)ctx->n_colliders << 32) | ctx->n_entities};
+    if (g.exec && memcmp(g.key, key, sizeof key) == 0) {
+        CU(cudaGraphLaunch(g.exec, ctx->stream));
+        ctx->launches += g.launches;
+        ++ctx->graph_replays;
+        if (full) ctx->sorted_side = ctx->passes & 1;
+        ctx->scratch_clean = true;
+        return B2COL_OK;
+    }
+    if (g.exec) {
+        cudaGraphExecDestroy(g.exec);
+        g.exec = nullptr;
+    }
+    const uint64_t before = ctx->launches;
+    CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    const b2col_status st = enqueue_frame(ctx, full);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    if (st != B2COL_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+    }
+    if (e != cudaSuccess || !graph) return fail(ctx, B2COL_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    const cudaError_t ei = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) {
+        g.exec = nullptr;
+        return fail(ctx, B2COL_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+    }
+    g.launches = ctx->launches - before;
+    memcpy(g.key, key, sizeof key);
+    CU(cudaGraphLaunch(g.exec, ctx->stream));
     return B2COL_OK;
 }
 
@@ -1242,7 +1335,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     }
     if (ctx->max_col_entity > E)
         return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, E);
-    GUARD(ensure(ctx, ctx->d_world_aabb, (size_t)n * 24 + 8));
+    GUARD(ensure(ctx, ctx->d_world_aabb, (size_t)n * sizeof(LeafRec)));  // 32-byte records {world AABB, entity, collider index}
     GUARD(ensure(ctx, ctx->d_keys[0], (size_t)n * 8));
     GUARD(ensure(ctx, ctx->d_keys[1], (size_t)n * 8));
     GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
@@ -1268,35 +1361,12 @@ b2col_status b2col_update(b2col_ctx* ctx)
     }
     ctx->passes = (3 * ctx->bits - ctx->drop + RS_BITS - 1) / RS_BITS;
     const uint32_t tiles = cdiv(n, RS_TILE);
-    const size_t lb_words_per_pass = ((size_t)tiles + (tiles + LB_GROUP - 1) / LB_GROUP) * RS_RADIX;  // tile counts + group status
+    const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     GUARD(prepare_scratch(ctx, (SCRATCH_BOUNDS_WORDS + (size_t)RS_MAX_PASSES * RS_RADIX + 16 + (size_t)ctx->passes * lb_words_per_pass) * 4));
     if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
-    uint32_t* ghist = scratch_ghist(ctx);
-    uint32_t* tickets = scratch_tickets(ctx);
-    uint32_t* lookback = scratch_lookback(ctx);
+    if (!ctx->world_external) GUARD(ensure(ctx, ctx->d_world, ((size_t)E + 1) * 64));
     PHASE(ctx);  // 1: set-up
-
-    // ---- a1 + a2: world matrices, world AABBs, scene bounds ---------------------------------------
-    GUARD(enqueue_transform_refit(ctx));  // phases 2 (propagate) and 3 (refit); one phase when fused
-
-    // ---- a4: LBVH build -------------------------------------------------------------------------
-    {
-        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<Aabb24>(), blob_hdr(ctx), scratch_bounds(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T,
-               ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
-    }
-    PHASE(ctx);  // morton
-    int side = 0;
-    for (int p = 0; p < ctx->passes; ++p) {
-        LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
-               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
-               lookback + (size_t)p * lb_words_per_pass, tickets + p);
-        side ^= 1;
-        PHASE(ctx);  // radix pass p
-    }
-    ctx->sorted_side = side;
-    GUARD(launch_build(ctx, n, side));
-    PHASE(ctx);  // last: build
+    GUARD(run_frame(ctx, true));
     ctx->have_tree = true;
     ctx->topology_valid = true;
     ++ctx->full_builds;
@@ -1325,11 +1395,9 @@ b2col_status b2col_refit(b2col_ctx* ctx)
     GUARD(prepare_scratch(ctx, ctx->zero_bytes));
     if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
     ctx->exact_nodes_valid = false;
+    if (!ctx->world_external) GUARD(ensure(ctx, ctx->d_world, ((size_t)ctx->n_entities + 1) * 64));
     PHASE(ctx);
-    GUARD(enqueue_transform_refit(ctx));
-    LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
-    GUARD(launch_build(ctx, n, ctx->sorted_side));
-    PHASE(ctx);
+    GUARD(run_frame(ctx, false));
     ++ctx->refits;
     return B2COL_OK;
 }
@@ -1440,7 +1508,7 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
         GUARD(ensure(ctx, ctx->d_nodes_full, (size_t)(n - 1) * sizeof(Node)));
         CU(cudaMemsetAsync(ctx->d_other_bound.p, 0xFF, (size_t)n * 4 + 4, ctx->stream));
         LAUNCH(ctx, k_build_exact, cdiv(n, 256), 256, n, ctx->d_keys[ctx->sorted_side].as<uint64_t>(), ctx->d_vals[ctx->sorted_side].as<uint32_t>(),
-               ctx->d_world_aabb.as<Aabb24>(), ctx->d_col_entity.as<uint32_t>(), ctx->d_nodes_full.as<Node>(), ctx->d_other_bound.as<uint32_t>(), blob_hdr(ctx),
+               ctx->d_world_aabb.as<LeafRec>(), ctx->d_col_entity.as<uint32_t>(), ctx->d_nodes_full.as<Node>(), ctx->d_other_bound.as<uint32_t>(), blob_hdr(ctx),
                ctx->d_other_bound.as<uint32_t>() + n);
         ctx->exact_nodes_valid = true;
     }
@@ -1490,7 +1558,7 @@ b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out)
     if (!ctx->have_tree || ctx->tree_leaves != ctx->n_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_update has not run");
     if (!ctx->n_colliders) return B2COL_OK;
     CU(cudaSetDevice(ctx->device));
-    CU(cudaMemcpyAsync(h_out, ctx->d_world_aabb.p, (size_t)ctx->n_colliders * 24, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpy2DAsync(h_out, 24, ctx->d_world_aabb.p, sizeof(LeafRec), 24, ctx->n_colliders, cudaMemcpyDeviceToHost, ctx->stream));  // the AABB of each 32-byte record
     CU(cudaStreamSynchronize(ctx->stream));
     return B2COL_OK;
 }
@@ -1517,6 +1585,7 @@ b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out)
     out->kernel_launches = ctx->launches;
     out->full_builds = ctx->full_builds;
     out->refits = ctx->refits;
+    out->graph_replays = ctx->graph_replays;
     if (ctx->have_tree && ctx->d_blob.p) {
         CU(cudaSetDevice(ctx->device));
         BlobHeader h;

@@ -150,8 +150,8 @@ B2_HD Delta key_delta(const Key* keys, uint32_t i)
 }
 B2_HD bool delta_less(const Delta& a, const Delta& b) { return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo); }
 
-template <class Ops, class Key>
-B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
+template <class Ops, class Key, class BoxRec>  // BoxRec: anything with lo[3], hi[3] (Aabb24 on the host, the 32-byte world record on the device)
+B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const BoxRec* world_aabb,
                            const uint32_t* col_entity, Node* nodes, uint32_t* other_bound, const Grid& grid, QNode* qnodes, LeafRec* leaves,
                            uint32_t* root_out)
 {

@@ -103,6 +103,7 @@ typedef struct b2col_stats {
     uint64_t kernel_launches;   /* cumulative count of this library's kernel launches on this ctx */
     uint64_t bvh_bytes;         /* device bytes of the traversal structure (nodes + leaf entity table) */
     uint64_t full_builds, refits; /* b2col_update / b2col_refit calls that built or re-bounded a tree */
+    uint64_t graph_replays;     /* frames that ran as a replay of a captured CUDA graph (cfg.use_cuda_graph) */
     float scene_min[3], scene_max[3]; /* centroid bounds used for the Morton grid */
 } b2col_stats;
 
