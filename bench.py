@@ -193,6 +193,9 @@ def workload_config(args):
 
 # -------------------------------------------------------------------------------------------------
 def run_ours(args):
+    # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; this program's stdout is one JSON line
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
     import torch.distributed as dist
 
@@ -321,7 +324,15 @@ def run_ours(args):
     peak, peak_src = measured_peak_gbs()
     algo_bytes = 60.0 * R + 64.0 * (N - 1)  # 24 B ray in + 36 B Raycast out, node set once
     achieved = algo_bytes / (step_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    traffic = None  # dram__bytes_read + dram__bytes_write of one launch of this kernel on this workload, from the committed ncu capture
+    try:
+        tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_d_traffic.json")))
+        if (tr["workload"], tr["colliders"], tr["rays"]) == (args.workload, N, R):
+            traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "algorithmic_bytes": algo_bytes,
                 "kernel": "k_trace_lbvh", "peak_source": peak_src,
                 "note": "primary figure = compulsory stream bytes only; traversal at 1M AABBs is L2/latency-bound, not HBM-bound (SURVEY.md 8(d))"}
 

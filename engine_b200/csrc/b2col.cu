@@ -807,6 +807,8 @@ struct b2col_ctx {
         uint64_t launches = 0;
     } graphs[2];
     bool use_graph = false;
+    // a captured graph stays valid while no device buffer moved (buffers_gen), the hierarchy's level structure is the
+    // same (shape_gen) and the counts / flags in the key are; the DATA in the buffers may change freely
     uint64_t buffers_gen = 0, shape_gen = 0, graph_replays = 0;
     bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
     bool phase_timing = false;
@@ -1090,7 +1092,6 @@ b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const
     CU(cudaStreamSynchronize(ctx->stream));
     ctx->n_entities = n_entities;
     ctx->world_external = true;
-    ++ctx->shape_gen;
     return B2COL_OK;
 }
 
@@ -1107,7 +1108,6 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->max_col_entity = max_e;
     ctx->h_col_entity.assign(h_entity, h_entity + n);
     ctx->fuse_map_valid = false;
-    ++ctx->shape_gen;
     GUARD(ensure(ctx, ctx->d_col_entity, (size_t)n * 4 + 4));
     GUARD(ensure(ctx, ctx->d_col_local, (size_t)n * 24 + 8));
     if (n) {

@@ -17,7 +17,9 @@ B2colSceneCtx* B2colAcquire(Scene* scene)
 {
     B2colSceneCtx& e = registry()[scene];
     if (!e.ctx) {
-        const b2col_status st = b2col_create(&e.ctx, nullptr);
+        b2col_config cfg{};
+        cfg.use_cuda_graph = 1;  // frames of an unchanged scene shape replay one captured graph
+        const b2col_status st = b2col_create(&e.ctx, &cfg);
         if (st != B2COL_OK) {
             registry().erase(scene);
             throw std::runtime_error(std::string("b2col_create: ") + b2col_last_error(nullptr));
