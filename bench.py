@@ -193,9 +193,11 @@ def workload_config(args):
 
 # -------------------------------------------------------------------------------------------------
 def run_ours(args):
-    # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; this program's stdout is one JSON line
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # This program's stdout is ONE JSON line, but NCCL writes its version banner to the process's stdout when the first
+    # communicator comes up: park fd 1 on stderr until the line is printed.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
 
@@ -206,7 +208,11 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — engine_b200 has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = None
     if world > 1:
+        from engine_b200 import dist as b2dist_early
+
+        numa = b2dist_early.bind_to_gpu_numa_node(local)  # before any pinned allocation
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if rank == 0:
         b2build.build()
@@ -296,9 +302,16 @@ def run_ours(args):
     cs.sync()
     barrier()
     wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    launches = cs.stats()["kernel_launches"] - launches0  # kernels launched inside the timed region
+    if rank == 0:
+        # nvidia-smi needs ~100 ms per sample and the timed region may be shorter: keep the SAME load running (untimed)
+        # until at least three samples have been taken under it
+        t_wait = time.perf_counter()
+        while len(sampler.rows) < 3 and time.perf_counter() - t_wait < 3.0 and sampler.proc is not None:
+            cs.raycast_device(d_rays, R, d_out)
+            cs.sync()
     clocks = sampler.stop() if rank == 0 else None
     dev_ms = cs.event_elapsed_ms(2, 3)
-    launches = cs.stats()["kernel_launches"] - launches0
     step_ms = max_over_ranks(dev_ms) / args.steps
     value = world * R / (step_ms * 1e-3) / 1e6
     hits = int((d_out.view(R, 36)[:, 32] != 0).sum().item())
@@ -315,6 +328,23 @@ def run_ours(args):
     barrier()
     e2e_value = world * R / (e2e_ms * 1e-3) / 1e6
     same = bool((h_out.view(R, 36)[:: max(R // 4096, 1)] == d_out.view(R, 36)[:: max(R // 4096, 1)].cpu()).all().item())
+
+    # ---- hits gathered back to rank 0 over NVLink (NCCL gather), reported separately ------------
+    gather_ms = None
+    if world > 1:
+        from engine_b200 import dist as b2dist
+
+        into = torch.empty(world * d_out.numel(), dtype=torch.uint8, device="cuda") if rank == 0 else None
+        b2dist.gather_hits_device(d_out, dst=0, into=into)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            b2dist.gather_hits_device(d_out, dst=0, into=into)
+        barrier()
+        gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / 3
+        if rank == 0:
+            assert bool((into.view(world, -1)[0][: 36 * 4096] == d_out[: 36 * 4096]).all().item())
+        del into
 
     if rank != 0:
         if world > 1:
@@ -345,13 +375,15 @@ def run_ours(args):
                         "sample": f"first {n} rays of the same batch, one pass, {arm.kind} GetRaycast on a binned-SAH tree injected into bvh_ (reference BuildNode is O(N^2): 1M not buildable)",
                         "setup_s": arm.setup_s}
 
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 36, "ms_per_step": e2e_ms,
                 "matches_device_path": same},
         "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks,
-        "rebuild": rebuild, "bvh_broadcast_ms": bcast_ms, "hit_fraction": hits / R, "wall_ms_timed_region": wall_ms,
+        "rebuild": rebuild, "bvh_broadcast_ms": bcast_ms, "hits_gather_ms": gather_ms, "numa_cpulist_rank0": numa, "hit_fraction": hits / R, "wall_ms_timed_region": wall_ms,
     }))
     if world > 1:
         dist.destroy_process_group()

@@ -86,3 +86,51 @@ def raycast_sharded(trace_fn: Callable[[np.ndarray], np.ndarray], rays: np.ndarr
         a, b = shard_bounds(n, world, r)
         ob[a * item : b * item] = parts[r][: (b - a) * item].cpu().numpy()
     return out
+
+
+def gather_hits_device(d_out: torch.Tensor, dst: int = 0, group=None, into: torch.Tensor | None = None):
+    """Device-resident flavour of the result gather: every rank's Raycast bytes (equal sizes) land, in rank order, in
+    one tensor on `dst` (NCCL gather over NVLink; `into` lets the caller reuse the world x n destination).  Returns the
+    gathered tensor on dst, None elsewhere.  Shards are contiguous slices of the batch, so the concatenation IS the
+    unsharded result."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    parts = None
+    if rank == dst:
+        if into is None:
+            into = torch.empty(world * d_out.numel(), dtype=d_out.dtype, device=d_out.device)
+        parts = list(into.view(world, -1).unbind(0))
+    dist.gather(d_out, parts, dst=dst, group=group)
+    return into if rank == dst else None
+
+
+def bind_to_gpu_numa_node(device_index: int) -> str | None:
+    """Pin this process (and the pinned host buffers it allocates afterwards) to the CPUs of the NUMA node its GPU hangs
+    off — what `numactl --cpunodebind` would do per rank.  With 8 ranks on a two-socket host, staging buffers on the
+    far socket halve the PCIe copy rate.  Best effort: returns the cpulist it bound to, or None."""
+    try:
+        import os
+
+        import pynvml
+
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        index = int(visible.split(",")[device_index]) if visible and all(v.strip().isdigit() for v in visible.split(",")) else device_index
+        bus_id = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus_id = bus_id.decode() if isinstance(bus_id, bytes) else bus_id
+        domain, rest = bus_id.lower().split(":", 1)
+        pci = f"{domain[-4:]}:{rest}"
+        node = int(open(f"/sys/bus/pci/devices/{pci}/numa_node").read())
+        if node < 0:
+            return None
+        cpulist = open(f"/sys/devices/system/node/node{node}/cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return cpulist
+    except Exception:
+        return None

@@ -61,6 +61,16 @@ def _worker(rank, world, port, n_rays, q):
 
         out = b2dist.raycast_sharded(trace_fn, rays, RAYCAST_DTYPE, cpu, dst=0)
         assert traced == [hi - lo]
+        # device-resident flavour of the gather (here: CPU tensors over gloo), equal-sized shards
+        even = n_rays - n_rays % world
+        lo2, hi2 = b2dist.shard_bounds(even, world, rank)
+        mine = torch.from_numpy(port_lib.raycast_tree(state["tree"], rays[lo2:hi2]).view(np.uint8).reshape(-1).copy())
+        gathered = b2dist.gather_hits_device(mine, dst=0)
+        if rank == 0:
+            want = port_lib.raycast_tree(state["tree"], rays[:even]).view(np.uint8).reshape(-1)
+            assert (gathered.numpy() == want).all()
+        else:
+            assert gathered is None
         if rank == 0:
             whole = port_lib.raycast_tree(state["tree"], rays)
             q.put(bool((out.view(np.uint8) == whole.view(np.uint8)).all()) and int(whole["hit"].sum()) > 0)
