@@ -796,7 +796,9 @@ struct b2col_ctx {
     DevBuf d_rays, d_hits, d_counter;
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
     std::vector<cudaEvent_t> pipe_events;
-    size_t e2e_chunk = 2u << 20;
+    // rays per chunk of the host-buffer pipeline: largest, first (tools/tune_e2e.py on B200, 16M rays: 256K -> 1M: 12.55 ms;
+    // 128K -> 2M: 13.1; 256K -> 512K: 14.1 — smaller chunks leave the persistent trace kernel too few rays per launch)
+    size_t e2e_chunk = 1u << 20, e2e_first_chunk = 256u << 10;
     int trace_grid = 148 * 8, fetch_threshold = 25;
     cudaEvent_t events[16] = {};
     // dev: B2COL_PHASE_EVENTS=1 records an event after every phase of b2col_update / b2col_refit (b2col_debug_phase_ms)
@@ -968,6 +970,8 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
+        if (const char* e = getenv("B2COL_E2E_FIRST_CHUNK")) c->e2e_first_chunk = std::max<size_t>(1024, (size_t)atoll(e));
+        c->e2e_chunk = std::max(c->e2e_chunk, c->e2e_first_chunk);
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
@@ -1416,25 +1420,27 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
     CU(cudaSetDevice(ctx->device));
     GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
     GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
-    const size_t chunk = ctx->e2e_chunk;
-    if (mode == B2COL_MODE_LBVH && n >= 2 * chunk) {
-        // Large batch: pipeline in chunks over three streams so that the upload of chunk c+1, the trace of
-        // chunk c and the download of chunk c-1 overlap (PCIe is full duplex).  Needs page-locked host
-        // buffers to actually overlap; with pageable memory the copies serialise but stay correct.
+    if (mode == B2COL_MODE_LBVH && n >= 2 * ctx->e2e_first_chunk) {
+        // Pipeline in chunks over three streams so that the upload of chunk c+1, the trace of chunk c and the
+        // download of chunk c-1 overlap (PCIe is full duplex).  The download is the long pole (36 of the 60 bytes per
+        // ray), so the schedule is about starting it early: chunk sizes ramp up from e2e_first_chunk by doubling to
+        // e2e_chunk — the first results leave the device after ~0.2 ms instead of after a full-size chunk.  Needs
+        // page-locked host buffers to actually overlap; with pageable memory the copies serialise but stay correct.
         if (!ctx->stream_in) {
             CU(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
             CU(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
         }
-        const size_t n_chunks = (n + chunk - 1) / chunk;
-        while (ctx->pipe_events.size() < 2 * n_chunks) {
-            cudaEvent_t ev;
-            CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-            ctx->pipe_events.push_back(ev);
-        }
         b2col_ray* d_r = ctx->d_rays.as<b2col_ray>();
         b2col_raycast* d_h = ctx->d_hits.as<b2col_raycast>();
-        for (size_t c = 0; c < n_chunks; ++c) {
-            const size_t off = c * chunk, m = std::min(chunk, n - off);
+        size_t off = 0, m = ctx->e2e_first_chunk, c = 0;
+        while (off < n) {
+            m = std::min(m, n - off);
+            if (n - off - m < ctx->e2e_first_chunk) m = n - off;  // no tiny tail chunk
+            while (ctx->pipe_events.size() < 2 * (c + 1)) {
+                cudaEvent_t ev;
+                CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+                ctx->pipe_events.push_back(ev);
+            }
             cudaEvent_t ev_in = ctx->pipe_events[2 * c], ev_k = ctx->pipe_events[2 * c + 1];
             CU(cudaMemcpyAsync(d_r + off, h_rays + off, m * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream_in));
             CU(cudaEventRecord(ev_in, ctx->stream_in));
@@ -1443,6 +1449,9 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
             CU(cudaEventRecord(ev_k, ctx->stream));
             CU(cudaStreamWaitEvent(ctx->stream_out, ev_k, 0));
             CU(cudaMemcpyAsync(h_out + off, d_h + off, m * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream_out));
+            off += m;
+            ++c;
+            m = std::min(2 * m, ctx->e2e_chunk);
         }
         CU(cudaStreamSynchronize(ctx->stream_out));
         CU(cudaStreamSynchronize(ctx->stream));
