@@ -794,6 +794,14 @@ struct b2col_ctx {
     uint32_t n_ref_nodes = 0;
     // staging for host-buffer queries
     DevBuf d_rays, d_hits, d_counter;
+    // few-ray calls (GetRaycast: a batch of one): rays and results travel through ONE mapped, page-locked staging
+    // block the kernel reads / writes directly, and the work counter comes from a pool of pre-zeroed slots — the call
+    // is a single kernel launch + one synchronize, no copy or memset operations
+    static constexpr size_t SMALL_MAX = 32, SMALL_SLOTS = 2048;
+    void* h_small = nullptr;   // [SMALL_MAX rays | SMALL_MAX results], cudaHostAllocMapped
+    void* d_small = nullptr;   // device address of the same block
+    DevBuf d_small_counters;   // SMALL_SLOTS x u64, all zero beyond small_next
+    size_t small_next = SMALL_SLOTS;
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
     std::vector<cudaEvent_t> pipe_events;
     // rays per chunk of the host-buffer pipeline: largest, first (tools/tune_e2e.py on B200, 16M rays: 256K -> 1M: 12.55 ms;
@@ -812,6 +820,7 @@ struct b2col_ctx {
     // a captured graph stays valid while no device buffer moved (buffers_gen), the hierarchy's level structure is the
     // same (shape_gen) and the counts / flags in the key are; the DATA in the buffers may change freely
     uint64_t buffers_gen = 0, shape_gen = 0, graph_replays = 0;
+    bool no_small_path = false;  // dev: B2COL_NO_SMALL=1 sends few-ray calls through the copy path (A/B timing)
     bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
     bool phase_timing = false;
     cudaEvent_t phase_ev[16] = {};
@@ -974,6 +983,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         c->e2e_chunk = std::max(c->e2e_chunk, c->e2e_first_chunk);
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
         if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
         if (c->phase_timing)
@@ -996,6 +1006,8 @@ void b2col_destroy(b2col_ctx* ctx)
         release(*b);
     for (auto& g : ctx->graphs)
         if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    release(ctx->d_small_counters);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->pipe_events) cudaEventDestroy(ev);
@@ -1418,6 +1430,27 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
     if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
     if (n == 0) return B2COL_OK;
     CU(cudaSetDevice(ctx->device));
+    if (mode == B2COL_MODE_LBVH && n <= b2col_ctx::SMALL_MAX && ctx->have_tree && ctx->tree_leaves > 0 && !ctx->no_small_path) {
+        if (!ctx->h_small) {
+            CU(cudaHostAlloc(&ctx->h_small, b2col_ctx::SMALL_MAX * (sizeof(b2col_ray) + sizeof(b2col_raycast)), cudaHostAllocMapped));
+            CU(cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0));
+            GUARD(ensure(ctx, ctx->d_small_counters, b2col_ctx::SMALL_SLOTS * 8));
+        }
+        if (ctx->small_next >= b2col_ctx::SMALL_SLOTS) {  // every slot used once: zero them all again (once per SMALL_SLOTS calls)
+            CU(cudaMemsetAsync(ctx->d_small_counters.p, 0, b2col_ctx::SMALL_SLOTS * 8, ctx->stream));
+            ctx->small_next = 0;
+        }
+        b2col_ray* hr = static_cast<b2col_ray*>(ctx->h_small);
+        b2col_raycast* ho = reinterpret_cast<b2col_raycast*>(hr + b2col_ctx::SMALL_MAX);
+        const b2col_ray* dr = static_cast<const b2col_ray*>(ctx->d_small);
+        b2col_raycast* dout = reinterpret_cast<b2col_raycast*>(const_cast<b2col_ray*>(dr) + b2col_ctx::SMALL_MAX);
+        memcpy(hr, h_rays, n * sizeof(b2col_ray));
+        LAUNCH(ctx, k_trace_lbvh, 1, TRACE_BLOCK, dr, (unsigned long long)n, dout, blob_hdr(ctx), blob_qnodes(ctx), blob_leaves(ctx, ctx->tree_leaves), ctx->T,
+               ctx->d_small_counters.as<unsigned long long>() + ctx->small_next++, ctx->fetch_threshold);
+        CU(cudaStreamSynchronize(ctx->stream));
+        memcpy(h_out, ho, n * sizeof(b2col_raycast));
+        return B2COL_OK;
+    }
     GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
     GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
     if (mode == B2COL_MODE_LBVH && n >= 2 * ctx->e2e_first_chunk) {

@@ -502,3 +502,27 @@ def test_gltf_ingested_scene_end_to_end(CollisionSystem, port):
     got = cs.get_raycasts(rays)
     assert got["hit"].sum() > 1000
     assert_raycast_equal(got, port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8), "glTF scene vs brute force")
+
+
+def test_few_ray_calls_equal_batch(CollisionSystem):
+    """GetRaycast is a batch of one: calls of 1..32 rays take the mapped-staging path (one launch, no copies); they must
+    return exactly what the same rays return inside a large batch, across more calls than the counter pool has slots."""
+    s = synth.uniform_boxes(30_000, seed=93, extent=120)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    rays = synth.random_rays(6000, seed=94, extent=130)
+    want = cs.get_raycasts(rays)
+    launches = cs.stats()["kernel_launches"]
+    got = np.zeros_like(want)
+    i, k = 0, 0
+    while i < len(rays):
+        m = 1 if k < 2200 else 1 + (k * 7) % 32
+        got[i : i + m] = cs.get_raycasts(rays[i : i + m])
+        i += m
+        k += 1
+    assert k > 2100  # more calls than counter slots: the pool was recycled at least once
+    assert (got.view(np.uint8) == want.view(np.uint8)).all()
+    assert cs.stats()["kernel_launches"] - launches == k
+    one = cs.get_raycast(rays[0, :3], rays[0, 3:])
+    assert one.tobytes() == want[0].tobytes()
