@@ -336,29 +336,32 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 }
 
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
-// registers here anyway).
+// registers here anyway).  The bit allocation (make_morton_plan) depends on the centroid bounds the refit has
+// just reduced: thread 0 of every block derives it once and shares it.
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int bits, int drop, int passes, float T, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
+    __shared__ MortonPlan s_plan;
     for (int p = 0; p < passes; ++p) shist[p][threadIdx.x] = 0u;
-    __syncthreads();
-    float smin[3], sinv[3];
+    if (threadIdx.x == 0) {
+        float cmin[3], cmax[3];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const float lo = ordered_to_float(~bounds[k]);
-        const float hi = ordered_to_float(bounds[3 + k]);
-        const float ext = hi - lo;
-        smin[k] = lo;
-        sinv[k] = (ext > 0.0f && isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
+        for (int k = 0; k < 3; ++k) {
+            cmin[k] = ordered_to_float(~bounds[k]);
+            cmax[k] = ordered_to_float(bounds[3 + k]);
+        }
+        s_plan = make_morton_plan(cmin, cmax, key_bits);
     }
+    __syncthreads();
+    const MortonPlan plan = s_plan;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float4* bp = reinterpret_cast<const float4*>(world_rec + i);
         const float4 b0 = bp[0], b1 = bp[1];
         const float lo[3] = {b0.x, b0.y, b0.z}, hi[3] = {b0.w, b1.x, b1.y};
-        const uint64_t key = morton_key(lo, hi, smin, sinv, bits, drop);
+        const uint64_t key = morton_key(lo, hi, plan);
         keys[i] = key;
         vals[i] = i;
         for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
@@ -1260,7 +1263,7 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
     uint32_t* ghist = scratch_ghist(ctx);
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), ctx->bits, ctx->drop, ctx->passes, ctx->T,
+        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, ctx->T,
                ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
     PHASE(ctx);  // morton

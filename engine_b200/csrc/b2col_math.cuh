@@ -251,22 +251,120 @@ B2_HD uint64_t spread3(uint32_t v)
     return x;
 }
 
-// Centroid (GetBoxCentroid, src/system_collisions.cpp:43-50: (min+max)*0.5f) quantised to `bits`
-// bits per axis inside the scene's centroid bounds, interleaved x (most significant), y, z; the lowest
-// `drop` bits of the interleaved code are discarded (e.g. bits = 11, drop = 1: a 32-bit key with 11,11,10
-// bits for x,y,z — four 8-bit radix passes).  Only steers tree topology; never affects which box a ray hits.
-B2_HD uint64_t morton_key(const float* lo, const float* hi, const float* smin, const float* sinv, int bits, int drop = 0)
+// Spread the low 32 bits of v so that there is one zero bit between consecutive bits.
+B2_HD uint64_t spread2(uint32_t v)
 {
-    const float maxq = (float)((1u << bits) - 1u);
+    uint64_t x = v;
+    x = (x | (x << 16)) & 0x0000ffff0000ffffull;
+    x = (x | (x << 8)) & 0x00ff00ff00ff00ffull;
+    x = (x | (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+    x = (x | (x << 2)) & 0x3333333333333333ull;
+    x = (x | (x << 1)) & 0x5555555555555555ull;
+    return x;
+}
+
+// ---- Morton keys with the bits handed out by extent ---------------------------------------------
+// A Morton code that gives every axis the same number of bits cuts a flat scene (a game world: 1000 x 1000 x 50)
+// into cells 20x thinner in z than in x and y, and the radix tree then splits along z where that separates
+// nothing (measured: 31 % fewer rays/s on BASELINE config 2 than with cubic cells, profiles/r1_e_morton_cells.jsonl).
+// The K key bits are therefore distributed so that the cells come out as cubic as powers of two allow: with the
+// axes ordered by centroid extent a >= b >= c, axis a gets d1 bits more than b and b gets d2 more than c
+// (d = how many times the smaller extent must be doubled to come within sqrt 2 of the larger).  The code is,
+// from the most significant bit: d1 bits of a alone, d2 rounds interleaving (a, b), nc rounds interleaving
+// (a, b, c); the lowest `drop` bits are discarded so that exactly K bits remain.  For a roughly cubic scene
+// d1 = d2 = 0 and this is the plain 3-way interleave.  Only steers tree topology; never affects which box a
+// ray hits.  Everything below is exact float / integer arithmetic shared by the kernel and the host-side
+// restatement of the tests.
+struct MortonPlan {
+    float smin[3], sinv[3];  // per ORIGINAL axis: q = (centroid - smin) * sinv, in [0, 2^qbits)
+    float qmax[3];           // 2^qbits - 1
+    int axis[3];             // a, b, c: original axis indices by decreasing extent
+    int shift_a;             // axis a is quantised to at most 21 bits; the code wants na = qbits_a + shift_a
+    int nc, d2, drop;
+};
+
+constexpr int MORTON_AXIS_BITS = 21;  // spread3 / float quantisation limit per axis
+
+// number of doublings that bring `small` within sqrt(2) of `big` (0 if already there), capped
+B2_HD int morton_ratio_steps(float big, float small, int cap)
+{
+    if (!(small > 0.0f)) return cap;
+    int d = 0;
+    float e = small;
+    while (d < cap && B2_MUL(e, 1.41421354f) < big) {
+        e = B2_MUL(e, 2.0f);
+        ++d;
+    }
+    return d;
+}
+
+// cmin / cmax: bounds of the finite centroids (an axis without any: cmin > cmax); key_bits <= 63
+B2_HD MortonPlan make_morton_plan(const float* cmin, const float* cmax, int key_bits)
+{
+    MortonPlan p;
+    float ext[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float e = B2_SUB(cmax[k], cmin[k]);
+        ext[k] = (e > 0.0f && e < B2_INF) ? e : 0.0f;
+        p.smin[k] = cmin[k];
+    }
+    // stable sort of the three axes by decreasing extent
+    int a = 0, b = 1, c = 2;
+    if (ext[b] > ext[a]) { const int t = a; a = b; b = t; }
+    if (ext[c] > ext[b]) { const int t = b; b = c; c = t; }
+    if (ext[b] > ext[a]) { const int t = a; a = b; b = t; }
+    p.axis[0] = a;
+    p.axis[1] = b;
+    p.axis[2] = c;
+    int d1 = morton_ratio_steps(ext[a], ext[b], key_bits);
+    int d2 = morton_ratio_steps(ext[b], ext[c], key_bits);
+    if (d1 > key_bits) d1 = key_bits;
+    if (2 * d2 > key_bits - d1) d2 = (key_bits - d1 + 1) / 2;
+    if (d2 > MORTON_AXIS_BITS) d2 = MORTON_AXIS_BITS;
+    int rest = key_bits - d1 - 2 * d2;
+    int nc = rest > 0 ? (rest + 2) / 3 : 0;
+    if (3 * nc + 2 * d2 + d1 > 63) nc = rest / 3;  // the undropped code must fit 64 bits
+    if (nc + d2 > MORTON_AXIS_BITS) nc = MORTON_AXIS_BITS - d2;  // axis b is limited to 21 bits (only reachable for key_bits > 42 on flat scenes)
+    int na = nc + d2 + d1;
+    const int total = 3 * nc + 2 * d2 + d1;
+    if (total < key_bits) na += key_bits - total;  // b and c are at their limit: the remaining bits go to a (low bits, zero)
+    const int qa = na > MORTON_AXIS_BITS ? MORTON_AXIS_BITS : na;
+    p.shift_a = na - qa;
+    p.nc = nc;
+    p.d2 = d2;
+    p.drop = total > key_bits ? total - key_bits : 0;
+    const int qbits[3] = {qa, nc + d2, nc};
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const int k = p.axis[r];
+        const float cells = (float)(1u << qbits[r]);
+        p.sinv[k] = ext[k] > 0.0f ? B2_DIV(cells, ext[k]) : 0.0f;
+        p.qmax[k] = B2_SUB(cells, 1.0f);
+    }
+    return p;
+}
+
+// Centroid (GetBoxCentroid, src/system_collisions.cpp:43-50: (min+max)*0.5f) -> key
+B2_HD uint64_t morton_key(const float* lo, const float* hi, const MortonPlan& p)
+{
     uint32_t q[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float c = B2_MUL(B2_ADD(lo[k], hi[k]), 0.5f);
-        float f = B2_MUL(B2_SUB(c, smin[k]), sinv[k]);  // in [0, 2^bits) for finite centroids
-        f = fminf(fmaxf(f, 0.0f), maxq);                // NaN -> 0 (fmaxf drops NaN)
+        float f = B2_MUL(B2_SUB(c, p.smin[k]), p.sinv[k]);  // in [0, 2^qbits) for finite centroids
+        f = fminf(fmaxf(f, 0.0f), p.qmax[k]);               // NaN -> 0 (fmaxf drops NaN)
         q[k] = (uint32_t)f;
     }
-    return ((spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2])) >> drop;
+    const uint32_t qa32 = p.axis[0] == 0 ? q[0] : (p.axis[0] == 1 ? q[1] : q[2]);
+    const uint32_t qb = p.axis[1] == 0 ? q[0] : (p.axis[1] == 1 ? q[1] : q[2]);
+    const uint32_t qc = p.axis[2] == 0 ? q[0] : (p.axis[2] == 1 ? q[1] : q[2]);
+    const uint64_t qa = (uint64_t)qa32 << p.shift_a;
+    const uint32_t mc = (1u << p.nc) - 1u, m2 = (1u << p.d2) - 1u;
+    const uint64_t low = (spread3((uint32_t)qa & mc) << 2) | (spread3(qb & mc) << 1) | spread3(qc);
+    const uint64_t mid = (spread2((uint32_t)(qa >> p.nc) & m2) << 1) | spread2(qb >> p.nc);
+    const uint64_t top = qa >> (p.nc + p.d2);
+    return ((((top << (2 * p.d2)) | mid) << (3 * p.nc)) | low) >> p.drop;
 }
 
 // Order-preserving float <-> uint map for atomicMin/atomicMax on floats.

@@ -88,15 +88,11 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
             if (std::isfinite(lo)) { bmin[k] = fminf(bmin[k], lo); bmax[k] = fmaxf(bmax[k], lo); }
             if (std::isfinite(hi)) { bmin[k] = fminf(bmin[k], hi); bmax[k] = fmaxf(bmax[k], hi); }
         }
-    float sinv[3];
-    for (int k = 0; k < 3; ++k) {
-        const float ext = smax[k] - smin[k];
-        sinv[k] = (ext > 0.0f && std::isfinite(ext)) ? (float)(1u << bits) / ext : 0.0f;
-    }
+    const MortonPlan plan = make_morton_plan(smin, smax, 3 * bits - drop);
     const Grid grid = make_grid(bmin, bmax, T);
     *grid_out = grid;
     std::vector<uint64_t> keys(n);
-    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, smin, sinv, bits, drop);
+    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(world_aabb[i].lo, world_aabb[i].hi, plan);
     std::vector<uint32_t> idx(n);
     std::iota(idx.begin(), idx.end(), 0u);
     std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
@@ -172,6 +168,16 @@ size_t emu_export(uint32_t n, const Node* nodes, uint32_t root, const LeafRec* l
         if (i + 1 < n) export_internal(i, n, root, nodes, leaves, tmp.data(), used.data());
     }
     return compact_export(tmp.data(), used.data(), cand, out, capacity);
+}
+
+// Morton plan + keys of a set of centroids (boxes lo = hi = centroid), for the tests of the bit allocation.
+// plan_out: axis a, b, c, shift_a, nc, d2, drop
+void emu_morton(uint32_t n, const float* centroids3, const float* cmin, const float* cmax, int key_bits, int* plan_out, uint64_t* keys_out)
+{
+    const MortonPlan p = make_morton_plan(cmin, cmax, key_bits);
+    plan_out[0] = p.axis[0]; plan_out[1] = p.axis[1]; plan_out[2] = p.axis[2];
+    plan_out[3] = p.shift_a; plan_out[4] = p.nc; plan_out[5] = p.d2; plan_out[6] = p.drop;
+    for (uint32_t i = 0; i < n; ++i) keys_out[i] = morton_key(centroids3 + 3 * (size_t)i, centroids3 + 3 * (size_t)i, p);
 }
 
 }  // extern "C"

@@ -76,6 +76,16 @@ class Emu:
         return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
                     sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
 
+    def morton(self, centroids, cmin, cmax, key_bits):
+        """(plan dict, keys) of engine_b200/csrc/b2col_math.cuh make_morton_plan / morton_key"""
+        c = np.ascontiguousarray(centroids, np.float32).reshape(-1, 3)
+        cmin, cmax = np.ascontiguousarray(cmin, np.float32), np.ascontiguousarray(cmax, np.float32)
+        plan = np.zeros(7, np.int32)
+        keys = np.zeros(c.shape[0], np.uint64)
+        self.lib.emu_morton(C.c_uint32(c.shape[0]), _p(c), _p(cmin), _p(cmax), C.c_int(key_bits), _p(plan), _p(keys))
+        names = ("a", "b", "c", "shift_a", "nc", "d2", "drop")
+        return dict(zip(names, (int(v) for v in plan))), keys
+
     def trace_lbvh(self, tree, rays, T=1000.0):
         from oracle.oracle import RAYCAST_DTYPE
 

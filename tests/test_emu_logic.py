@@ -187,3 +187,89 @@ def test_emu_quantised_nodes_are_conservative(emu, port, extent, offset, box):
     brute = port.raycast_brute(tree["leaf_entity"], boxes[tree["sorted_prim"]], rays, nthreads=4)
     assert_raycast_equal(got, brute, f"quantised traversal, extent {extent} offset {offset}")
     assert got["hit"].sum() > 0
+
+
+# ---------------------------------------------------------------------------------------------
+# Morton bit allocation (make_morton_plan / morton_key): the K key bits follow the scene's extents
+# ---------------------------------------------------------------------------------------------
+def _classic_interleave(q, bits):
+    key = np.zeros(q.shape[0], np.uint64)
+    for b in range(bits):
+        for k in range(3):
+            key |= ((q[:, k].astype(np.uint64) >> np.uint64(b)) & np.uint64(1)) << np.uint64(3 * b + (2 - k))
+    return key
+
+
+def test_morton_plan_cubic_scene_is_the_plain_interleave(emu):
+    rng = np.random.default_rng(1)
+    c = rng.uniform(-100, 100, (5000, 3)).astype(np.float32)
+    cmin, cmax = c.min(0), c.max(0)
+    for key_bits, bits in ((32, 11), (30, 10), (40, 14), (48, 16), (63, 21)):
+        plan, keys = emu.morton(c, cmin, cmax, key_bits)
+        assert plan["d2"] == 0 and plan["shift_a"] == 0 and plan["nc"] == bits and plan["drop"] == 3 * bits - key_bits
+        order = [plan["a"], plan["b"], plan["c"]]
+        sinv = np.float32(1 << bits) / (cmax - cmin)
+        q = np.clip((c - cmin) * sinv, 0, np.float32((1 << bits) - 1)).astype(np.uint32)
+        want = _classic_interleave(q[:, order], bits) >> np.uint64(plan["drop"])
+        assert (keys == want).all()
+        assert int(keys.max()) < (1 << key_bits)
+
+
+@pytest.mark.parametrize("ext,key_bits", [((1000, 1000, 50), 32), ((50, 1000, 1000), 32), ((1000, 3, 1000), 40), ((4000, 1, 1), 32), ((1, 1, 0), 32),
+                                          ((7, 0, 0), 32), ((1e6, 1e-3, 1.0), 48), ((1000, 900, 50), 63), ((3, 2, 1), 12), ((1000, 1000, 50), 48)])
+def test_morton_plan_follows_the_extents(emu, ext, key_bits):
+    rng = np.random.default_rng(2)
+    ext = np.asarray(ext, np.float32)
+    c = (rng.uniform(0, 1, (20000, 3)) * ext).astype(np.float32)
+    c[0], c[1] = 0, ext  # the bounds are attained
+    cmin, cmax = c.min(0), c.max(0)
+    plan, keys = emu.morton(c, cmin, cmax, key_bits)
+    axes = [plan["a"], plan["b"], plan["c"]]
+    assert sorted(axes) == [0, 1, 2]
+    e = (cmax - cmin)[axes]
+    assert e[0] >= e[1] >= e[2]
+    nc, d2 = plan["nc"], plan["d2"]
+    total = 3 * nc + 2 * d2
+    assert int(keys.max()) < (1 << key_bits)
+    assert plan["drop"] in (0, 1, 2)
+    # bits per axis: a gets the rest of the key
+    na = key_bits + plan["drop"] - total + nc + d2
+    nb, n_c = nc + d2, nc
+    assert na >= nb >= n_c >= 0 and na + nb + n_c == key_bits + plan["drop"]
+    # cells as cubic as powers of two allow: wherever two axes both received bits and both have an extent,
+    # their cell sizes are within a factor 2 * sqrt(2) of each other (sqrt 2 from the rounding, 2 from the dropped bits)
+    cells = [e[0] / 2.0**na, e[1] / 2.0**nb, e[2] / 2.0**n_c]
+    got_bits = [na, nb, n_c]
+    for i in range(3):
+        for j in range(i + 1, 3):
+            if e[i] > 0 and e[j] > 0 and got_bits[j] > 0 and got_bits[i] < 21 and got_bits[j] < 21:
+                r = cells[i] / cells[j]
+                assert 1 / 2.9 < r < 2.9, (plan, cells)
+    # an axis that received no bit must be the thinnest: its whole extent is no larger than ~1.5 cells of the others
+    if e[0] > 0 and na <= 21:
+        for j in (1, 2):
+            if got_bits[j] == 0:
+                assert e[j] <= cells[0] * 1.5
+    # the key is monotone along every axis (other coordinates fixed)
+    base = c[2:12]
+    for k in range(3):
+        if ext[k] == 0:
+            continue
+        line = np.repeat(base, 50, axis=0)
+        line[:, k] = np.tile(np.linspace(0, ext[k], 50, dtype=np.float32), base.shape[0])
+        _, lk = emu.morton(line, cmin, cmax, key_bits)
+        lk = lk.reshape(-1, 50).astype(np.int64) if key_bits < 63 else lk.reshape(-1, 50)
+        assert (lk[:, 1:] >= lk[:, :-1]).all()
+    # sorting by the key clusters space: with extents in all three axes, neighbours in key order are close
+    if (ext > 0).all() and key_bits >= 30:
+        o = np.argsort(keys, kind="stable")
+        d = np.linalg.norm(np.diff(c[o].astype(np.float64), axis=0), axis=1)
+        rand = np.linalg.norm(np.diff(c.astype(np.float64), axis=0), axis=1)
+        assert np.median(d) < 0.2 * np.median(rand)
+
+
+def test_morton_plan_flat_world_example(emu):
+    """BASELINE config 2's world: 1000 x 1000 x 50 -> z gets 4 bits fewer than x and y (50 * 2^4 = 800 ~ 1000)."""
+    c = np.array([[0, 0, 0], [1000, 1000, 50]], np.float32)
+    plan, _ = emu.morton(c, c.min(0), c.max(0), 32)
+    assert plan["c"] == 2 and plan["d2"] == 4 and plan["nc"] == 8 and plan["drop"] == 0 and plan["shift_a"] == 0  # x, y: 12 bits, z: 8

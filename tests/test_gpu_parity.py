@@ -259,6 +259,40 @@ def test_config3_1m_incoherent(CollisionSystem, port):
     assert np.allclose(loc[np.arange(len(axis)), axis][outside], face[outside], rtol=1e-4, atol=1e-2)
 
 
+def test_config5_clustered_skewed(CollisionSystem, port):
+    """Config 5 at a size the oracle finishes in seconds: Zipf-skewed Gaussian clusters + uniform background (long
+    runs of equal Morton prefixes, a deep lopsided tree, wide key), rays aimed at colliders so that most of them hit
+    inside a dense cluster, plus random rays.  Reference traversal of the exported tree on a sample, brute force
+    over all boxes on a smaller one, shard invariance, and the 40-bit key path (forced: 14 bits per axis)."""
+    n, n_rays = 1_500_000, 1 << 20
+    s = synth.clustered_boxes(n, seed=5, n_clusters=300)
+    rng = np.random.default_rng(55)
+    target = s.pos[1 + rng.integers(0, n, n_rays // 2)] + rng.uniform(-0.2, 0.2, (n_rays // 2, 3)).astype(np.float32)
+    origin = target + rng.standard_normal((n_rays // 2, 3)).astype(np.float32) * 80.0
+    aimed = np.concatenate([origin, target - origin], axis=1).astype(np.float32)  # unnormalised directions
+    rays = np.concatenate([aimed, synth.random_rays(n_rays // 2, seed=56, extent=2000.0)])
+    results = []
+    for bits_per_axis in (0, 14):
+        cs = CollisionSystem(morton_bits_per_axis=bits_per_axis)
+        cs.set_scene(s)
+        cs.on_update()
+        got = cs.get_raycasts(rays)
+        assert got["hit"][: n_rays // 2].mean() > 0.5, got["hit"][: n_rays // 2].mean()
+        parts = np.concatenate([cs.get_raycasts(rays[lo : lo + n_rays // 4]) for lo in range(0, n_rays, n_rays // 4)])
+        assert (parts.view(np.uint8) == got.view(np.uint8)).all()
+        exported = cs.bvh
+        sel = np.arange(0, n_rays, 64)
+        assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), f"config 5 ({bits_per_axis}) vs reference traversal")
+        order, boxes = cs.leaf_order(), cs.world_aabbs()
+        sel = np.arange(0, n_rays, 4096)
+        assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), f"config 5 ({bits_per_axis}) vs brute force")
+        results.append(got)
+    # two different trees over the same boxes: identical answers except on exact ties
+    a, b = results
+    same = a["hit_entity"] == b["hit_entity"]
+    assert (a["hit"] == b["hit"]).all() and (a["distance"] == b["distance"]).all() and same.mean() > 0.999
+
+
 def test_config4_dynamic_frames(CollisionSystem, port, emu):
     """Per-frame TRS change -> propagate + refit + rebuild; checked against the oracle every frame."""
     n, roots = 200_000, 200

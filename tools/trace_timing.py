@@ -1,0 +1,48 @@
+#!/usr/bin/env python
+"""Dev tool: device-resident trace throughput of one workload (use B2COL_LIB=variants/... to compare kernel variants)."""
+import argparse, json, os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="config3", choices=["config3", "config5", "config2", "city", "hier"])
+    ap.add_argument("--colliders", type=int, default=1_000_000)
+    ap.add_argument("--rays", type=int, default=1 << 24)
+    ap.add_argument("--steps", type=int, default=5)
+    a = ap.parse_args()
+    import torch
+    from engine_b200 import synth
+    from engine_b200.collision import CollisionSystem
+    if a.workload == "config3":
+        s, rays = synth.uniform_boxes(a.colliders), synth.random_rays(a.rays)
+    elif a.workload == "config5":
+        s, rays = synth.clustered_boxes(a.colliders), synth.random_rays(a.rays, seed=4, extent=2000.0)
+    elif a.workload == "hier":
+        s, rays = synth.hierarchy_scene(a.colliders, 1000), synth.random_rays(a.rays)
+    else:
+        s = synth.static_city(a.colliders)
+        w = int(np.sqrt(a.rays))
+        rays = synth.camera_rays(w, w) if a.workload == "config2" else synth.random_rays(a.rays, seed=4, extent=500.0)
+    R = rays.shape[0]
+    cs = CollisionSystem(device=0)
+    cs.set_scene(s)
+    cs.on_update()
+    d_rays = torch.from_numpy(rays).cuda()
+    d_out = torch.empty(R * 36, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    for _ in range(3):
+        cs.raycast_device(d_rays, R, d_out)
+    cs.sync()
+    cs.event_record(2)
+    for _ in range(a.steps):
+        cs.raycast_device(d_rays, R, d_out)
+    cs.event_record(3)
+    cs.sync()
+    ms = cs.event_elapsed_ms(2, 3) / a.steps
+    out = d_out.view(R, 36)
+    print(json.dumps({"lib": os.environ.get("B2COL_LIB", "default"), "workload": a.workload, "colliders": s.n_colliders, "rays": R, "ms": ms, "mrays_s": R / ms / 1e3,
+                      "hit_fraction": float((out[:, 32] != 0).float().mean().item()), "checksum": int(out[:, 24:28].contiguous().view(torch.int32).to(torch.int64).sum().item())}))
+
+if __name__ == "__main__":
+    main()
