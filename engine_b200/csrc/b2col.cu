@@ -142,7 +142,9 @@ struct BlobHeader {
     uint32_t box_min_inv[3];     // ~ordered(min finite box coordinate)
     uint32_t box_max[3];         //  ordered(max finite box coordinate)
     Grid grid;                   // quantisation grid of the traversal nodes (written by k_morton)
-    uint32_t reserved[39];
+    uint32_t trace_root;         // where k_trace_lbvh starts: `root`, or the compact copy of the root (k_top_layout)
+    uint32_t top_count;          // nodes in the compact copy of the top levels behind the leaf records (0: none)
+    uint32_t reserved[37];
 };
 static_assert(sizeof(BlobHeader) == 256, "blob header");
 constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
@@ -430,6 +432,8 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
             nd.w[7] = LEAF_BIT | 0u;
             DevOps::store_qnode(&qnodes[0], nd);
             hdr->root = 0u;
+            hdr->trace_root = 0u;
+            hdr->top_count = 0u;
         }
         return;
     }
@@ -507,8 +511,108 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         ref = p;
         if (lev_l == LEVEL_END && lev_r == LEVEL_END) {  // the range is the whole array
             hdr->root = p;
+            hdr->trace_root = p;  // k_top_layout, when it runs, redirects the traversal to its compact copy
+            hdr->top_count = 0u;
             return;
         }
+    }
+}
+
+// Compact copy of the top levels of the tree, for trees larger than L2.
+//
+// A node lives at its split position, so the few thousand nodes of the upper levels — visited by every ray — are
+// scattered over the whole node array, one L2 line and one 2 MB page each.  Where they fall is an accident of the
+// scene: on BASELINE config 5 (10M clustered colliders, 640 MB tree) the same tree traced at 2090 or 2630 Mrays/s
+// depending only on which axis led the Morton code (profiles/r1_e_top_layout.jsonl).  This kernel copies the top
+// TOP_LEVELS levels in breadth-first order into a contiguous block behind the leaf records (<= 512 KB) and points
+// the traversal at it (hdr->trace_root): 2730 Mrays/s whichever axis leads.  Copies refer to copies down to the
+// last copied level, whose child refs are the original ones; the original nodes stay where they are (the export
+// and the refit use them).  Node indices are relative to `qnodes` and LeafRec has the size of a QNode, so copy j
+// is node (n_nodes + n_leaves + j) and k_trace_lbvh needs no change.
+//
+// One block: level k's nodes are read (through `orig`, the copies' original indices), their internal children are
+// numbered by a block-wide prefix sum — the breadth-first positions of level k+1 — and the copies are written with
+// the remapped refs.  ~1 us per level; run only for trees that do not fit L2 (b2col_update decides).
+constexpr int TOP_LEVELS = 14;
+constexpr uint32_t TOP_CAP = (1u << TOP_LEVELS) - 1u;
+constexpr int TOP_BLOCK = 1024;
+constexpr int TOP_ITEMS = 4;
+__global__ void __launch_bounds__(TOP_BLOCK)
+k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base, uint32_t* orig, int levels)
+{
+    __shared__ uint32_t s_warp[TOP_BLOCK / 32];
+    __shared__ uint32_t s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) orig[0] = hdr->root;
+    __syncthreads();
+    uint32_t off = 0u, count = 1u;  // level k occupies copies [off, off + count)
+    for (int k = 0; k < levels && count != 0u; ++k) {
+        const bool last = k + 1 == levels;
+        uint32_t run = 0u;  // internal children numbered so far on this level
+        for (uint32_t base = 0u; base < count; base += TOP_BLOCK * TOP_ITEMS) {
+            // TOP_ITEMS consecutive nodes per thread (breadth-first order = thread order, then item order); all loads
+            // of a round are in flight together — the level is a chain of DRAM latencies otherwise
+            const uint32_t first = base + tid * TOP_ITEMS;
+            uint32_t src[TOP_ITEMS];
+            QNode nd[TOP_ITEMS];
+#pragma unroll
+            for (int j = 0; j < TOP_ITEMS; ++j) src[j] = first + j < count ? orig[off + first + j] : 0u;
+#pragma unroll
+            for (int j = 0; j < TOP_ITEMS; ++j)
+                if (first + j < count) nd[j] = DevOps::load_qnode(&qnodes[src[j]]);
+            uint32_t mine = 0u;
+#pragma unroll
+            for (int j = 0; j < TOP_ITEMS; ++j)
+                if (first + j < count) mine += ((nd[j].w[6] & LEAF_BIT) ? 0u : 1u) + ((nd[j].w[7] & LEAF_BIT) ? 0u : 1u);
+            // block-wide exclusive prefix sum of the internal-child counts
+            uint32_t incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) s_warp[warp] = incl;
+            __syncthreads();
+            if (warp == 0) {
+                uint32_t w = s_warp[lane];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
+                    if (lane >= o) w += v;
+                }
+                s_warp[lane] = w;
+                if (lane == 31) s_total = w;
+            }
+            __syncthreads();
+            uint32_t pre = run + (warp ? s_warp[warp - 1] : 0u) + incl - mine;
+            const uint32_t next = off + count;  // first copy of level k+1
+#pragma unroll
+            for (int j = 0; j < TOP_ITEMS; ++j) {
+                if (first + j < count) {
+                    if (!last) {
+                        if (!(nd[j].w[6] & LEAF_BIT)) {
+                            orig[next + pre] = nd[j].w[6];
+                            nd[j].w[6] = top_base + next + pre;
+                            ++pre;
+                        }
+                        if (!(nd[j].w[7] & LEAF_BIT)) {
+                            orig[next + pre] = nd[j].w[7];
+                            nd[j].w[7] = top_base + next + pre;
+                            ++pre;
+                        }
+                    }
+                    DevOps::store_qnode(&top[off + first + j], nd[j]);
+                }
+            }
+            run += s_total;
+            __syncthreads();  // s_warp / s_total are reused; orig[] of the next level is complete after the last round
+        }
+        off += count;
+        count = last ? 0u : run;
+    }
+    if (tid == 0) {
+        hdr->trace_root = top_base;
+        hdr->top_count = off;
     }
 }
 
@@ -607,7 +711,7 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t root = hdr->root;
+    const uint32_t root = hdr->trace_root;
     const Grid grid = hdr->grid;
     const float lim0 = float_pred(T);
     uint32_t l_node[LBVH_STACK];
@@ -774,6 +878,8 @@ struct b2col_ctx {
     bool have_colliders = false;
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
+    DevBuf d_top_orig;                           // k_top_layout: original index of every copied node
+    int top_levels = -1;                         // -1: automatic (trees larger than L2); dev override B2COL_TOP_LEVELS
     DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
     DevBuf d_nodes_full, d_other_bound;  // export only: full-precision two-slot nodes + their arrival words (k_build_exact)
     bool exact_nodes_valid = false;      // d_nodes_full matches the tree in the blob
@@ -884,10 +990,16 @@ void release(DevBuf& b)
 
 inline uint32_t cdiv(size_t a, size_t b) { return (uint32_t)((a + b - 1) / b); }
 
+// blob = [header | QNode x n_nodes | LeafRec x n_leaves | QNode x top_cap: compact copy of the top levels (k_top_layout)]
+inline size_t top_cap_for(uint32_t n_leaves)
+{
+    const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
+    return std::min<size_t>(TOP_CAP, n_nodes);
+}
 size_t blob_size_for(uint32_t n_leaves)
 {
     const size_t n_nodes = n_leaves > 1 ? n_leaves - 1 : 1;
-    return sizeof(BlobHeader) + n_nodes * sizeof(QNode) + (size_t)n_leaves * sizeof(LeafRec);
+    return sizeof(BlobHeader) + n_nodes * sizeof(QNode) + (size_t)n_leaves * sizeof(LeafRec) + top_cap_for(n_leaves) * sizeof(QNode);
 }
 inline BlobHeader* blob_hdr(const b2col_ctx* c) { return c->d_blob.as<BlobHeader>(); }
 inline QNode* blob_qnodes(const b2col_ctx* c) { return reinterpret_cast<QNode*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader)); }
@@ -987,6 +1099,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
         if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
         if (c->phase_timing)
@@ -1005,7 +1118,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
+                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_top_orig, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& g : ctx->graphs)
         if (g.exec) cudaGraphExecDestroy(g.exec);
@@ -1147,6 +1260,13 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
            ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
            ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
     ctx->scratch_clean = true;  // k_build leaves every scratch word zero
+    // Trees that do not fit L2: compact copy of the top levels (see k_top_layout).  Below ~2M colliders the whole tree is
+    // L2-resident and the copy buys nothing (measured at 1M: 1875 Mrays/s either way) but would cost the frame ~15 us.
+    const int levels = ctx->top_levels >= 0 ? ctx->top_levels : (n > (1u << 21) ? TOP_LEVELS : 0);
+    if (levels > 0 && n > 1u) {
+        QNode* top = reinterpret_cast<QNode*>(blob_leaves(ctx, n) + n);
+        LAUNCH(ctx, k_top_layout, 1, TOP_BLOCK, blob_hdr(ctx), blob_qnodes(ctx), top, (uint32_t)((n - 1u) + n), ctx->d_top_orig.as<uint32_t>(), std::min(levels, TOP_LEVELS));
+    }
     return B2COL_OK;
 }
 
@@ -1360,6 +1480,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_xch, (size_t)n * sizeof(Xch)));
+    GUARD(ensure(ctx, ctx->d_top_orig, (size_t)(TOP_CAP + 1u) * 4));
     if (ctx->d_xch.p != ctx->xch_ready) {  // new allocation: all arrival words "nobody has arrived" (k_build leaves them so)
         CU(cudaMemsetAsync(ctx->d_xch.p, 0xFF, ctx->d_xch.cap, ctx->stream));
         ctx->xch_ready = ctx->d_xch.p;

@@ -314,11 +314,11 @@ B2_HD MortonPlan make_morton_plan(const float* cmin, const float* cmax, int key_
     if (ext[b] > ext[a]) { const int t = a; a = b; b = t; }
     if (ext[c] > ext[b]) { const int t = b; b = c; c = t; }
     if (ext[b] > ext[a]) { const int t = a; a = b; b = t; }
+    int d1 = morton_ratio_steps(ext[a], ext[b], key_bits);
+    int d2 = morton_ratio_steps(ext[b], ext[c], key_bits);
     p.axis[0] = a;
     p.axis[1] = b;
     p.axis[2] = c;
-    int d1 = morton_ratio_steps(ext[a], ext[b], key_bits);
-    int d2 = morton_ratio_steps(ext[b], ext[c], key_bits);
     if (d1 > key_bits) d1 = key_bits;
     if (2 * d2 > key_bits - d1) d2 = (key_bits - d1 + 1) / 2;
     if (d2 > MORTON_AXIS_BITS) d2 = MORTON_AXIS_BITS;

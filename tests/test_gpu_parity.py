@@ -293,6 +293,69 @@ def test_config5_clustered_skewed(CollisionSystem, port):
     assert (a["hit"] == b["hit"]).all() and (a["distance"] == b["distance"]).all() and same.mean() > 0.999
 
 
+def test_compact_top_levels(CollisionSystem, port, monkeypatch):
+    """k_top_layout (trees larger than L2; forced here on a small scene): the copy behind the leaf records is the
+    breadth-first order of the top levels with refs remapped, the original nodes are untouched, and every ray gets
+    the same answer with and without it — after a full build and after a refit-only frame."""
+    n, levels = 200_000, 9
+    s = synth.clustered_boxes(n, seed=7, n_clusters=40)
+    rng = np.random.default_rng(70)
+    target = s.pos[1 + rng.integers(0, n, 100_000)]
+    origin = target + rng.standard_normal((100_000, 3)).astype(np.float32) * 60.0
+    rays = np.concatenate([np.concatenate([origin, target - origin], axis=1).astype(np.float32), synth.random_rays(50_000, seed=71, extent=2000.0),
+                           synth.axis_rays(5_000, seed=72, extent=2000.0)])
+    monkeypatch.setenv("B2COL_TOP_LEVELS", "0")
+    plain = CollisionSystem()
+    plain.set_scene(s)
+    plain.on_update()
+    want = plain.get_raycasts(rays)
+    assert want["hit"].sum() > 10_000
+    monkeypatch.setenv("B2COL_TOP_LEVELS", str(levels))
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    for frame in range(2):
+        if frame == 0:
+            cs.on_update()
+        else:
+            cs.on_update_refit()  # same boxes, same tree: the copy is regenerated
+        got = cs.get_raycasts(rays)
+        assert (got.view(np.uint8) == want.view(np.uint8)).all()
+        _, nbytes = cs.bvh_blob()
+        t = torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{cs.device}")
+        cs.bvh_export_blob(t, nbytes)
+        cs.sync()
+        words = t.cpu().numpy().view(np.uint32)
+        root, trace_root, top_count = int(words[3]), int(words[25]), int(words[26])
+        q = words[64 : 64 + 8 * (n - 1)].reshape(n - 1, 8)
+        q_plain, _ = read_blob(plain, n)
+        assert (q == q_plain).all(), "the original nodes must stay as built"
+        top_base = (n - 1) + n
+        assert trace_root == top_base
+        top = words[64 + 8 * top_base : 64 + 8 * (top_base + top_count)].reshape(top_count, 8)
+        # numpy restatement: breadth-first, slot 0 before slot 1
+        order, frontier, expect_refs = [], np.array([root], np.int64), []
+        for k in range(levels):
+            order.append(frontier)
+            kids = q[frontier, 6:8]
+            internal = (kids & 0x80000000) == 0
+            nxt = kids[internal].astype(np.int64)  # row-major: slot 0 then slot 1 of each node, in frontier order
+            refs = kids.copy()
+            if k + 1 < levels:
+                refs[internal] = top_base + sum(len(o) for o in order) + np.arange(nxt.shape[0], dtype=np.uint32)
+            expect_refs.append(refs)
+            frontier = nxt
+            if frontier.size == 0:
+                break
+        order, expect_refs = np.concatenate(order), np.concatenate(expect_refs)
+        assert top_count == order.shape[0]
+        assert (top[:, 0:6] == q[order, 0:6]).all()
+        assert (top[:, 6:8] == expect_refs).all()
+    # a replica that imports the blob traces through the copy as well
+    replica = CollisionSystem()
+    replica.bvh_import_blob(t, nbytes)
+    assert (replica.get_raycasts(rays).view(np.uint8) == want.view(np.uint8)).all()
+
+
 def test_config4_dynamic_frames(CollisionSystem, port, emu):
     """Per-frame TRS change -> propagate + refit + rebuild; checked against the oracle every frame."""
     n, roots = 200_000, 200

@@ -180,6 +180,7 @@ def main():
     t_conv = time.perf_counter() - t0
     out = words.copy()
     out[3] = root
+    out[25], out[26] = root, 0  # trace_root, top_count (no compact top copy)
     out[64 : 64 + 8 * (n - 1)] = q.reshape(-1)
     out[64 + 8 * (n - 1) : 64 + 8 * (n - 1) + 8 * n] = lf.reshape(-1)
     blob2 = torch.from_numpy(out.view(np.uint8)).cuda()
