@@ -915,7 +915,7 @@ struct b2col_ctx {
     std::vector<cudaEvent_t> pipe_events;
     // rays per chunk of the host-buffer pipeline: largest, first (tools/tune_e2e.py on B200, 16M rays: 256K -> 1M: 12.55 ms;
     // 128K -> 2M: 13.1; 256K -> 512K: 14.1 — smaller chunks leave the persistent trace kernel too few rays per launch)
-    size_t e2e_chunk = 1u << 20, e2e_first_chunk = 256u << 10;
+    size_t e2e_chunk = 1u << 20, e2e_first_chunk = 256u << 10, e2e_min_chunk = 64u << 10;
     int trace_grid = 148 * 8, fetch_threshold = 25;
     cudaEvent_t events[16] = {};
     // dev: B2COL_PHASE_EVENTS=1 records an event after every phase of b2col_update / b2col_refit (b2col_debug_phase_ms)
@@ -1095,6 +1095,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_E2E_FIRST_CHUNK")) c->e2e_first_chunk = std::max<size_t>(1024, (size_t)atoll(e));
+        if (const char* e = getenv("B2COL_E2E_MIN_CHUNK")) c->e2e_min_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         c->e2e_chunk = std::max(c->e2e_chunk, c->e2e_first_chunk);
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
@@ -1577,7 +1578,12 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
     }
     GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
     GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
-    if (mode == B2COL_MODE_LBVH && n >= 2 * ctx->e2e_first_chunk) {
+    // first chunk: e2e_first_chunk for large batches, halved down to e2e_min_chunk until the batch holds four of them: a
+    // 256K-ray call runs as 64K + 128K + 64K instead of upload -> trace -> download back to back (300 -> 384 Mrays/s, 512K:
+    // 521 -> 592; chunks below 64K cost more in launches and events than the overlap returns — tools/tune_e2e_small.py)
+    size_t first_chunk = ctx->e2e_first_chunk;
+    while (first_chunk > ctx->e2e_min_chunk && n < 4 * first_chunk) first_chunk >>= 1;
+    if (mode == B2COL_MODE_LBVH && n >= 4 * first_chunk) {
         // Pipeline in chunks over three streams so that the upload of chunk c+1, the trace of chunk c and the
         // download of chunk c-1 overlap (PCIe is full duplex).  The download is the long pole (36 of the 60 bytes per
         // ray), so the schedule is about starting it early: chunk sizes ramp up from e2e_first_chunk by doubling to
@@ -1589,10 +1595,10 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
         }
         b2col_ray* d_r = ctx->d_rays.as<b2col_ray>();
         b2col_raycast* d_h = ctx->d_hits.as<b2col_raycast>();
-        size_t off = 0, m = ctx->e2e_first_chunk, c = 0;
+        size_t off = 0, m = first_chunk, c = 0;
         while (off < n) {
             m = std::min(m, n - off);
-            if (n - off - m < ctx->e2e_first_chunk) m = n - off;  // no tiny tail chunk
+            if (n - off - m < first_chunk) m = n - off;  // no tiny tail chunk
             while (ctx->pipe_events.size() < 2 * (c + 1)) {
                 cudaEvent_t ev;
                 CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
