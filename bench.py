@@ -366,6 +366,24 @@ def run_ours(args):
                 "kernel": "k_trace_lbvh", "peak_source": peak_src,
                 "note": "primary figure = compulsory stream bytes only; traversal at 1M AABBs is L2/latency-bound, not HBM-bound (SURVEY.md 8(d))"}
 
+    # What actually binds the traversal: every node visit is one 32-byte gather per lane, and incoherent
+    # rays never share a line, so each visit costs one L1TEX wavefront; B200 sustains ~1.0 such gathers per clock per SM
+    # (tools/micro/gather_bench.cu: 0.99).  One extra, untimed pass in the counting mode measures the visits of this batch.
+    from engine_b200.capi import MODE_LBVH_COUNT
+
+    c0 = cs.trace_counters()
+    cs.raycast_device(d_rays, R, d_out, mode=MODE_LBVH_COUNT)
+    cs.sync()
+    c1 = cs.trace_counters()
+    visits = c1["node_visits"] - c0["node_visits"]
+    n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+    sm_hz = (clocks or {}).get("sm_mhz") or 1965.0
+    per_clk_sm = visits / (step_ms * 1e-3) / (n_sm * sm_hz * 1e6)
+    roofline["binding"] = {"resource": "L1TEX wavefronts: one 32-byte node gather per lane per visit", "node_visits_per_ray": visits / R,
+                           "achieved": per_clk_sm, "peak": 1.0, "unit": "node gathers/clk/SM", "frac": per_clk_sm / 1.0,
+                           "l2_to_sm_gbs": visits * 32.0 / (step_ms * 1e-3) / 1e9,
+                           "peak_source": "measured gather rate of an L2-resident table, tools/micro/gather_bench.cu (0.99); stack and ray traffic in shared memory share the pipe"}
+
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         arm = CpuArm(scene)

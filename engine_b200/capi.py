@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B2COL_LIB") or os.path.join(HERE, "libb2col.so")  # B2COL_LIB: dev override (kernel variants)
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_OVERFLOW = range(7)
-MODE_LBVH, MODE_REFTOPO = 0, 1
+MODE_LBVH, MODE_REFTOPO, MODE_LBVH_COUNT = 0, 1, 2
 
 # PODs — byte-identical to the reference's (include/system_collisions.h:13-24,40-48)
 RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3)])
@@ -43,7 +43,7 @@ SYMBOLS = [
     "b2col_abi_version", "b2col_create", "b2col_destroy", "b2col_last_error", "b2col_sync", "b2col_stream",
     "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_set_world_matrices", "b2col_set_colliders",
     "b2col_update", "b2col_propagate", "b2col_refit", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
-    "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats",
+    "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats", "b2col_get_trace_counters",
     "b2col_bvh_blob", "b2col_bvh_export_blob", "b2col_bvh_import_blob", "b2col_event_record", "b2col_event_elapsed_ms",
 ]
 
@@ -91,6 +91,7 @@ def load() -> C.CDLL:
     lib.b2col_get_world_aabbs.argtypes = [vp, vp]
     lib.b2col_get_leaf_order.argtypes = [vp, vp]
     lib.b2col_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    lib.b2col_get_trace_counters.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b2col_bvh_blob.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     lib.b2col_bvh_import_blob.argtypes = [vp, vp, sz]
     lib.b2col_bvh_export_blob.argtypes = [vp, vp, sz]

@@ -174,6 +174,12 @@ class CollisionSystem:
         d["scene_min"], d["scene_max"] = list(s.scene_min), list(s.scene_max)
         return d
 
+    def trace_counters(self) -> dict:
+        """totals over all MODE_LBVH_COUNT calls: BVH nodes fetched (one 32-byte sector each) and rays traced"""
+        v, r = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.b2col_get_trace_counters(self.h, C.byref(v), C.byref(r)))
+        return {"node_visits": int(v.value), "rays": int(r.value)}
+
     # -- multi-GPU -----------------------------------------------------------------------------
     def bvh_blob(self) -> tuple[int, int]:
         p, n = C.c_void_p(), C.c_size_t()

@@ -702,6 +702,9 @@ __device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t*
 // Per-lane registers: the grid-space ray (6 floats + 6 byte-permute selectors), node, stack pointers, best
 // (t, leaf), pruning limit, ray index.  The exact ray lives in shared memory (written once at fetch) for
 // the exact leaf tests and the epilogue.
+// COUNT (B2COL_MODE_LBVH_COUNT, a diagnostic instantiation): also adds the number of node visits to counter[1] — what
+// bench.py turns into the L1 wavefront rate, the resource that actually binds this kernel.
+template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
 k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
              const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
@@ -727,6 +730,7 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
     bool active = false;
     bool pending = false;    // this lane's ray is finished but its Raycast is not written yet
     bool exhausted = false;  // warp-uniform: the pool has no rays left
+    unsigned long long visits = 0ull;  // COUNT only
     auto exact_ray = [&]() {
         RayPre r;
 #pragma unroll
@@ -796,6 +800,7 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
                 if (pop) cur = (pt <= lim) ? pn : REF_EMPTY;
                 // ---- visit
                 if (cur != REF_EMPTY) {
+                    if (COUNT) ++visits;
                     const QNode nd = DevOps::load_qnode(&qnodes[cur]);
                     const VisitOut v = visit_node<DevOps>(best, lim, q, nd, leaves, T, exact_ray);
                     if (v.push) {
@@ -816,6 +821,11 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
             }
             if (__popc(__ballot_sync(0xffffffffu, active)) < keep_going) break;
         }
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
+        if (lane == 0 && visits) atomicAdd(counter + 1, visits);
     }
 }
 
@@ -878,6 +888,7 @@ struct b2col_ctx {
     bool have_colliders = false;
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
+    uint64_t counted_visits = 0, counted_rays = 0;  // B2COL_MODE_LBVH_COUNT totals
     DevBuf d_top_orig;                           // k_top_layout: original index of every copied node
     int top_levels = -1;                         // -1: automatic (trees larger than L2); dev override B2COL_TOP_LEVELS
     DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
@@ -1023,7 +1034,8 @@ inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
 b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode)
 {
     if (n == 0) return B2COL_OK;
-    if (mode == B2COL_MODE_LBVH) {
+    const bool count = mode == B2COL_MODE_LBVH_COUNT;
+    if (mode == B2COL_MODE_LBVH || count) {
         if (!ctx->have_tree) {
             // frame-0 behaviour of the reference: bvh_ is empty before the first onUpdate, every query misses (:167)
             CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
@@ -1033,11 +1045,22 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
             CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
             return B2COL_OK;
         }
-        GUARD(ensure(ctx, ctx->d_counter, 8));
-        CU(cudaMemsetAsync(ctx->d_counter.p, 0, 8, ctx->stream));
+        GUARD(ensure(ctx, ctx->d_counter, 16));
+        CU(cudaMemsetAsync(ctx->d_counter.p, 0, 16, ctx->stream));
         const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-        LAUNCH(ctx, k_trace_lbvh, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
-               blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+        if (count) {
+            LAUNCH(ctx, k_trace_lbvh<true>, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                   blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+            unsigned long long v = 0;
+            CU(cudaMemcpyAsync(&v, ctx->d_counter.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            ctx->counted_visits += v;
+            ctx->counted_rays += n;
+        }
+        else {
+            LAUNCH(ctx, k_trace_lbvh<false>, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                   blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+        }
     }
     else if (mode == B2COL_MODE_REFTOPO) {
         GUARD(ensure(ctx, ctx->d_flag, 4));
@@ -1091,7 +1114,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
     {   // persistent trace kernel: one resident wave of blocks
         int sms = 148, per_sm = 8;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh<false>, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_E2E_FIRST_CHUNK")) c->e2e_first_chunk = std::max<size_t>(1024, (size_t)atoll(e));
@@ -1570,7 +1593,7 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
         const b2col_ray* dr = static_cast<const b2col_ray*>(ctx->d_small);
         b2col_raycast* dout = reinterpret_cast<b2col_raycast*>(const_cast<b2col_ray*>(dr) + b2col_ctx::SMALL_MAX);
         memcpy(hr, h_rays, n * sizeof(b2col_ray));
-        LAUNCH(ctx, k_trace_lbvh, 1, TRACE_BLOCK, dr, (unsigned long long)n, dout, blob_hdr(ctx), blob_qnodes(ctx), blob_leaves(ctx, ctx->tree_leaves), ctx->T,
+        LAUNCH(ctx, k_trace_lbvh<false>, 1, TRACE_BLOCK, dr, (unsigned long long)n, dout, blob_hdr(ctx), blob_qnodes(ctx), blob_leaves(ctx, ctx->tree_leaves), ctx->T,
                ctx->d_small_counters.as<unsigned long long>() + ctx->small_next++, ctx->fetch_threshold);
         CU(cudaStreamSynchronize(ctx->stream));
         memcpy(h_out, ho, n * sizeof(b2col_raycast));
@@ -1743,6 +1766,14 @@ b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out)
     CU(cudaSetDevice(ctx->device));
     CU(cudaMemcpyAsync(h_out, ctx->d_vals[ctx->sorted_side].p, (size_t)ctx->n_colliders * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
+b2col_status b2col_get_trace_counters(b2col_ctx* ctx, uint64_t* node_visits, uint64_t* rays)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (node_visits) *node_visits = ctx->counted_visits;
+    if (rays) *rays = ctx->counted_rays;
     return B2COL_OK;
 }
 

@@ -91,8 +91,10 @@ typedef struct b2col_config {
 
 typedef enum b2col_mode {
     B2COL_MODE_LBVH = 0,    /* production: tree built on the GPU by b2col_update */
-    B2COL_MODE_REFTOPO = 1  /* walk a reference-format tree uploaded with b2col_upload_ref_bvh
+    B2COL_MODE_REFTOPO = 1, /* walk a reference-format tree uploaded with b2col_upload_ref_bvh
                                (exact reference semantics incl. tie winners; parity mode) */
+    B2COL_MODE_LBVH_COUNT = 2 /* diagnostic: B2COL_MODE_LBVH (identical results) that also counts node visits
+                               (b2col_get_trace_counters); synchronises, a little slower — never the timed path */
 } b2col_mode;
 
 typedef struct b2col_stats {
@@ -186,6 +188,9 @@ b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out);
  * depth-first leaf order of the tree, the order that decides tie winners */
 b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out);
 b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out);
+/* totals over all B2COL_MODE_LBVH_COUNT calls on this ctx: BVH nodes fetched (one 32-byte sector each — the
+ * unit the traversal's binding resource, L1 wavefronts, is counted in) and rays traced */
+b2col_status b2col_get_trace_counters(b2col_ctx* ctx, uint64_t* node_visits, uint64_t* rays);
 
 /* ---- multi-GPU replication ------------------------------------------------------------------- */
 /* The traversal structure lives in ONE contiguous device allocation so that it can be replicated

@@ -601,6 +601,36 @@ def test_gltf_ingested_scene_end_to_end(CollisionSystem, port):
     assert_raycast_equal(got, port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8), "glTF scene vs brute force")
 
 
+def test_counting_mode_matches_and_counts(CollisionSystem, emu):
+    """B2COL_MODE_LBVH_COUNT: same bytes out as the production mode; the node-visit total agrees with the host
+    execution of the same traversal (tests/emu visit histogram) to within the pruning-order slack (both prune with the
+    best hit so far; the kernel defers far children through a stack of entry distances exactly as the host loop does)."""
+    import ctypes as C
+
+    import emu_loader
+
+    s = synth.uniform_boxes(30_000, seed=95, extent=150)
+    rays = synth.random_rays(20_000, seed=96, extent=150)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    want = cs.get_raycasts(rays)
+    c0 = cs.trace_counters()
+    got = cs.get_raycasts(rays, capi.MODE_LBVH_COUNT)
+    c1 = cs.trace_counters()
+    assert (got.view(np.uint8) == want.view(np.uint8)).all()
+    assert c1["rays"] - c0["rays"] == rays.shape[0]
+    visits = c1["node_visits"] - c0["node_visits"]
+    tree = emu.build(cs.world_aabbs(), s.collider_entity)
+    hist = np.zeros(128, np.uint64)
+    tv, lt = C.c_uint64(0), C.c_uint64(0)
+    r6 = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+    emu.lib.emu_visit_histogram(emu_loader._p(tree["qnodes"]), emu_loader._p(tree["leaves"]), emu_loader._p(tree["grid"]), C.c_uint32(tree["root"]), emu_loader._p(r6),
+                                C.c_size_t(r6.shape[0]), C.c_float(1000.0), emu_loader._p(hist), C.c_int(128), C.byref(tv), C.byref(lt))
+    assert visits > rays.shape[0]
+    assert abs(visits - tv.value) <= 0.02 * tv.value, (visits, tv.value)
+
+
 def test_few_ray_calls_equal_batch(CollisionSystem):
     """GetRaycast is a batch of one: calls of 1..32 rays take the mapped-staging path (one launch, no copies); they must
     return exactly what the same rays return inside a large batch, across more calls than the counter pool has slots."""
