@@ -530,20 +530,26 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
 // and the refit use them).  Node indices are relative to `qnodes` and LeafRec has the size of a QNode, so copy j
 // is node (n_nodes + n_leaves + j) and k_trace_lbvh needs no change.
 //
-// One block: level k's nodes are read (through `orig`, the copies' original indices), their internal children are
+// One block: level k's nodes are read (through the frontier of original indices in shared memory), their internal children are
 // numbered by a block-wide prefix sum — the breadth-first positions of level k+1 — and the copies are written with
 // the remapped refs.  ~1 us per level; run only for trees that do not fit L2 (b2col_update decides).
 constexpr int TOP_LEVELS = 14;
 constexpr uint32_t TOP_CAP = (1u << TOP_LEVELS) - 1u;
 constexpr int TOP_BLOCK = 1024;
 constexpr int TOP_ITEMS = 4;
+constexpr uint32_t TOP_FRONTIER = 1u << (TOP_LEVELS - 1);  // nodes on the deepest copied level
+constexpr size_t TOP_SMEM = 2 * TOP_FRONTIER * sizeof(uint32_t);
 __global__ void __launch_bounds__(TOP_BLOCK)
-k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base, uint32_t* orig, int levels)
+k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base, int levels)
 {
+    // original indices of the current level's nodes and of the next level's, ping-pong (a level has <= 2^13 nodes)
+    extern __shared__ uint32_t s_frontier[];
     __shared__ uint32_t s_warp[TOP_BLOCK / 32];
     __shared__ uint32_t s_total;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) orig[0] = hdr->root;
+    uint32_t* cur_f = s_frontier;
+    uint32_t* next_f = s_frontier + TOP_FRONTIER;
+    if (tid == 0) cur_f[0] = hdr->root;
     __syncthreads();
     uint32_t off = 0u, count = 1u;  // level k occupies copies [off, off + count)
     for (int k = 0; k < levels && count != 0u; ++k) {
@@ -556,7 +562,7 @@ k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base
             uint32_t src[TOP_ITEMS];
             QNode nd[TOP_ITEMS];
 #pragma unroll
-            for (int j = 0; j < TOP_ITEMS; ++j) src[j] = first + j < count ? orig[off + first + j] : 0u;
+            for (int j = 0; j < TOP_ITEMS; ++j) src[j] = first + j < count ? cur_f[first + j] : 0u;
 #pragma unroll
             for (int j = 0; j < TOP_ITEMS; ++j)
                 if (first + j < count) nd[j] = DevOps::load_qnode(&qnodes[src[j]]);
@@ -591,12 +597,12 @@ k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base
                 if (first + j < count) {
                     if (!last) {
                         if (!(nd[j].w[6] & LEAF_BIT)) {
-                            orig[next + pre] = nd[j].w[6];
+                            next_f[pre] = nd[j].w[6];
                             nd[j].w[6] = top_base + next + pre;
                             ++pre;
                         }
                         if (!(nd[j].w[7] & LEAF_BIT)) {
-                            orig[next + pre] = nd[j].w[7];
+                            next_f[pre] = nd[j].w[7];
                             nd[j].w[7] = top_base + next + pre;
                             ++pre;
                         }
@@ -605,10 +611,13 @@ k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base
                 }
             }
             run += s_total;
-            __syncthreads();  // s_warp / s_total are reused; orig[] of the next level is complete after the last round
+            __syncthreads();  // s_warp / s_total are reused; the next level's frontier is complete after the last round
         }
         off += count;
         count = last ? 0u : run;
+        uint32_t* t = cur_f;
+        cur_f = next_f;
+        next_f = t;
     }
     if (tid == 0) {
         hdr->trace_root = top_base;
@@ -889,7 +898,6 @@ struct b2col_ctx {
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
     uint64_t counted_visits = 0, counted_rays = 0;  // B2COL_MODE_LBVH_COUNT totals
-    DevBuf d_top_orig;                           // k_top_layout: original index of every copied node
     int top_levels = -1;                         // -1: automatic (trees larger than L2); dev override B2COL_TOP_LEVELS
     DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
     DevBuf d_nodes_full, d_other_bound;  // export only: full-precision two-slot nodes + their arrival words (k_build_exact)
@@ -1123,6 +1131,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
+        cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
         if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
@@ -1142,7 +1151,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_top_orig, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
+                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& g : ctx->graphs)
         if (g.exec) cudaGraphExecDestroy(g.exec);
@@ -1289,7 +1298,9 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
     const int levels = ctx->top_levels >= 0 ? ctx->top_levels : (n > (1u << 21) ? TOP_LEVELS : 0);
     if (levels > 0 && n > 1u) {
         QNode* top = reinterpret_cast<QNode*>(blob_leaves(ctx, n) + n);
-        LAUNCH(ctx, k_top_layout, 1, TOP_BLOCK, blob_hdr(ctx), blob_qnodes(ctx), top, (uint32_t)((n - 1u) + n), ctx->d_top_orig.as<uint32_t>(), std::min(levels, TOP_LEVELS));
+        k_top_layout<<<1, TOP_BLOCK, TOP_SMEM, ctx->stream>>>(blob_hdr(ctx), blob_qnodes(ctx), top, (uint32_t)((n - 1u) + n), std::min(levels, TOP_LEVELS));
+        ++ctx->launches;
+        if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "launch of k_top_layout failed: %s", cudaGetErrorString(e));
     }
     return B2COL_OK;
 }
@@ -1504,7 +1515,6 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(ensure(ctx, ctx->d_vals[0], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_vals[1], (size_t)n * 4));
     GUARD(ensure(ctx, ctx->d_xch, (size_t)n * sizeof(Xch)));
-    GUARD(ensure(ctx, ctx->d_top_orig, (size_t)(TOP_CAP + 1u) * 4));
     if (ctx->d_xch.p != ctx->xch_ready) {  // new allocation: all arrival words "nobody has arrived" (k_build leaves them so)
         CU(cudaMemsetAsync(ctx->d_xch.p, 0xFF, ctx->d_xch.cap, ctx->stream));
         ctx->xch_ready = ctx->d_xch.p;
