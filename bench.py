@@ -392,6 +392,12 @@ def run_ours(args):
         cpu_baseline = {"value": n / secs / 1e6, "unit": UNIT, "cores": arm.threads, "kind": arm.kind,
                         "sample": f"first {n} rays of the same batch, one pass, {arm.kind} GetRaycast on a binned-SAH tree injected into bvh_ (reference BuildNode is O(N^2): 1M not buildable)",
                         "setup_s": arm.setup_s}
+        # the reference is single-threaded (src/application.cpp:390): the faithful figure, on a smaller sample
+        n1 = max(20000, min(n // (4 * arm.threads), n))
+        threads, arm.threads = arm.threads, 1
+        secs1 = arm.trace(rays_np[:n1])
+        arm.threads = threads
+        cpu_baseline["single_thread"] = {"value": n1 / secs1 / 1e6, "unit": UNIT, "sample": f"first {n1} rays of the same batch, one thread"}
 
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)

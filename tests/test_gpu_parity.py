@@ -180,6 +180,30 @@ def test_build_matches_host_restatement(CollisionSystem, emu, n, bits_per_axis):
         assert (cs.bvh.view(np.uint8) == emu.export(tree).view(np.uint8)).all()
 
 
+@pytest.mark.parametrize("squash,bits_per_axis", [((1.0, 1.0, 0.02), 0), ((0.03, 1.0, 1.0), 0), ((1.0, 0.0, 0.0), 0), ((1.0, 0.001, 0.2), 14), ((0.0, 0.0, 0.0), 0), ((1.0, 1.0, 0.05), 21)])
+def test_build_on_flat_and_degenerate_worlds(CollisionSystem, emu, port, squash, bits_per_axis):
+    """Worlds that are thin or flat along some axes: the Morton bits go to the axes that have an extent
+    (make_morton_plan); the device keys / sort / tree equal the host restatement bit for bit, and rays agree with brute force."""
+    n = 60_000
+    s = synth.uniform_boxes(n, seed=66, extent=300.0)
+    s.pos[1:] *= np.asarray(squash, np.float32)
+    cs = CollisionSystem(morton_bits_per_axis=bits_per_axis)
+    cs.set_scene(s)
+    cs.on_update()
+    boxes = cs.world_aabbs()
+    tree = emu.build(boxes, s.collider_entity, bits=bits_per_axis)
+    order = cs.leaf_order()
+    assert np.array_equal(order, tree["sorted_prim"])
+    qnodes, leaves = read_blob(cs, n)
+    assert np.array_equal(qnodes, tree["qnodes"]["w"]) and cs.stats()["root"] == tree["root"]
+    rays = synth.random_rays(3000, seed=67, extent=300.0)
+    rays[:, 0:3] *= np.maximum(np.asarray(squash, np.float32), 0.05)
+    got = cs.get_raycasts(rays)
+    sel = np.arange(0, 3000, 10)
+    assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), f"flat world {squash}")
+    assert_raycast_equal(got, port.raycast_tree(cs.bvh, rays, nthreads=8), f"flat world {squash} vs reference traversal")
+
+
 def test_duplicate_boxes_and_ties(CollisionSystem, port):
     s = synth.grid_boxes(12, 12, 12, spacing=3.0)
     # append exact duplicates of the first 300 boxes (new entities at the same place)
