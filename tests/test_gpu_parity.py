@@ -317,6 +317,41 @@ def test_config5_clustered_skewed(CollisionSystem, port):
     assert (a["hit"] == b["hit"]).all() and (a["distance"] == b["distance"]).all() and same.mean() > 0.999
 
 
+def test_config5_full_size_10m(CollisionSystem, port):
+    """BASELINE config 4 at its full collider count (10M clustered AABBs: 40-bit keys, 5 radix passes, a 640 MB tree with
+    the compact copy of its top levels switched on automatically).  Size-independent checks: brute force over all 10M
+    boxes on a small sample, the reference's traversal of the exported 10M-leaf tree on a larger one, shard invariance."""
+    n = 10_000_000
+    s = synth.clustered_boxes(n, seed=5)
+    rng = np.random.default_rng(58)
+    m = 1 << 17
+    target = s.pos[1 + rng.integers(0, n, m)] + rng.uniform(-0.1, 0.1, (m, 3)).astype(np.float32)
+    origin = target + rng.standard_normal((m, 3)).astype(np.float32) * 50.0
+    rays = np.concatenate([np.concatenate([origin, target - origin], axis=1).astype(np.float32), synth.random_rays(m, seed=59, extent=2000.0)])
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    st = cs.stats()
+    assert st["sort_passes"] == 5 and st["n_internal_nodes"] == n - 1
+    got = cs.get_raycasts(rays)
+    assert got["hit"][:m].mean() > 0.5
+    parts = np.concatenate([cs.get_raycasts(rays[lo : lo + m // 2]) for lo in range(0, 2 * m, m // 2)])
+    assert (parts.view(np.uint8) == got.view(np.uint8)).all()
+    _, nbytes = cs.bvh_blob()
+    hdr = torch.empty(256, dtype=torch.uint8, device=f"cuda:{cs.device}")
+    blob = torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{cs.device}")
+    cs.bvh_export_blob(blob, nbytes)
+    cs.sync()
+    words = blob[:256].cpu().numpy().view(np.uint32)
+    del blob, hdr
+    assert words[25] == (n - 1) + n and 1000 < words[26] <= 16383, "the traversal must start in the compact copy of the top levels"
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    sel = np.arange(0, 2 * m, 2 * m // 192)
+    assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=16), "10M vs brute force")
+    sel = np.arange(0, 2 * m, 16)
+    assert_raycast_equal(got[sel], port.raycast_tree(cs.bvh, rays[sel], nthreads=16), "10M vs reference traversal of the exported tree")
+
+
 def test_compact_top_levels(CollisionSystem, port, monkeypatch):
     """k_top_layout (trees larger than L2; forced here on a small scene): the copy behind the leaf records is the
     breadth-first order of the top levels with refs remapped, the original nodes are untouched, and every ray gets
