@@ -10,6 +10,7 @@ def main():
     ap.add_argument("--colliders", type=int, default=1_000_000)
     ap.add_argument("--rays", type=int, default=1 << 24)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--sort-rays", type=int, default=0, help="experiment: order the rays by (origin cell Morton code at this many bits per axis, direction octant) first")
     a = ap.parse_args()
     import torch
     from engine_b200 import synth
@@ -25,6 +26,16 @@ def main():
         w = int(np.sqrt(a.rays))
         rays = synth.camera_rays(w, w) if a.workload == "config2" else synth.random_rays(a.rays, seed=4, extent=500.0)
     R = rays.shape[0]
+    if a.sort_rays:
+        b = a.sort_rays
+        o = rays[:, 0:3]
+        q = np.clip(((o - o.min(0)) / (o.max(0) - o.min(0)) * (1 << b)).astype(np.int64), 0, (1 << b) - 1)
+        key = np.zeros(R, np.int64)
+        for bit in range(b):
+            for k in range(3):
+                key |= ((q[:, k] >> bit) & 1) << (3 * bit + (2 - k))
+        octant = (rays[:, 3] > 0).astype(np.int64) | ((rays[:, 4] > 0).astype(np.int64) << 1) | ((rays[:, 5] > 0).astype(np.int64) << 2)
+        rays = np.ascontiguousarray(rays[np.argsort((key << 3) | octant, kind="stable")])
     cs = CollisionSystem(device=0)
     cs.set_scene(s)
     cs.on_update()
@@ -41,7 +52,7 @@ def main():
     cs.sync()
     ms = cs.event_elapsed_ms(2, 3) / a.steps
     out = d_out.view(R, 36)
-    print(json.dumps({"lib": os.environ.get("B2COL_LIB", "default"), "workload": a.workload, "colliders": s.n_colliders, "rays": R, "ms": ms, "mrays_s": R / ms / 1e3,
+    print(json.dumps({"sort_rays": a.sort_rays, "lib": os.environ.get("B2COL_LIB", "default"), "workload": a.workload, "colliders": s.n_colliders, "rays": R, "ms": ms, "mrays_s": R / ms / 1e3,
                       "hit_fraction": float((out[:, 32] != 0).float().mean().item()), "checksum": int(out[:, 24:28].contiguous().view(torch.int32).to(torch.int64).sum().item())}))
 
 if __name__ == "__main__":
