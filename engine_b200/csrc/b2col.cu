@@ -153,6 +153,20 @@ constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
 // kernels
 // =================================================================================================
 
+// Programmatic dependent launch (frame path, ctx->pdl): consecutive kernels of a frame are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so kernel k+1 is set up and its blocks become resident while the last
+// blocks of kernel k drain; each frame kernel therefore waits HERE, before its first access to global memory, until the
+// grid before it has completed and its writes are visible.  A no-op when the kernel was launched the ordinary way.
+// Measured at 1M colliders (profiles/r1_e_pdl.txt): stream launches 191 -> 178 us per update, the same as one CUDA-graph
+// replay (178; graph + PDL: 178).  An early cudaTriggerProgrammaticLaunchCompletion() bought another 1.5 us and was left out.
+__device__ __forceinline__ void pdl_wait()
+{
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();
+#endif
+}
+
+
 // Scene bounds accumulated by the refit (12 words of the per-frame scratch, all zero between frames):
 //   [0..2] ~ordered(min centroid)   [3..5] ordered(max centroid)      -> Morton grid
 //   [6..8] ~ordered(min finite box coordinate)   [9..11] ordered(max) -> quantisation grid of the traversal nodes
@@ -263,6 +277,7 @@ __global__ void __launch_bounds__(256)
 k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent,
                   const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world)
 {
+    pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
     const uint32_t e = level_entities[i];
@@ -281,6 +296,7 @@ k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t co
                         const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
                         const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
+    pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
     if (i < count) {
@@ -302,6 +318,7 @@ __global__ void __launch_bounds__(256)
 k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
         LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
+    pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
     if (i < n) {
@@ -344,6 +361,7 @@ __global__ void __launch_bounds__(256)
 k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
+    pdl_wait();
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
     __shared__ MortonPlan s_plan;
     for (int p = 0; p < passes; ++p) shist[p][threadIdx.x] = 0u;
@@ -378,7 +396,11 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
 
 // Refit-only frames (b2col_refit) skip k_morton: this fills the header fields k_morton would have written,
 // from the bounds k_refit has just reduced.
-__global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T) { finish_header(hdr, bounds, n, T); }
+__global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T)
+{
+    pdl_wait();
+    finish_header(hdr, bounds, n, T);
+}
 
 // LBVH hierarchy + bounds, production form: traversal structure only, merged in grid space — the per-thread
 // climb of build_from_leaf_q (b2col_bvh.cuh), with the arrival exchange moved into SHARED memory for every
@@ -398,6 +420,7 @@ constexpr int BUILD_BLOCK = 256;
 __global__ void __launch_bounds__(BUILD_BLOCK)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
 {
+    pdl_wait();
     // The frame's zero-initialised scratch (scene bounds, digit histograms, tile tickets, look-back words) has been
     // consumed by the kernels before this one: wipe it here for the next frame instead of a memset per frame.
     for (uint32_t w = blockIdx.x * BUILD_BLOCK + threadIdx.x; w < scratch_words; w += gridDim.x * BUILD_BLOCK) scratch[w] = 0u;
@@ -542,6 +565,7 @@ constexpr size_t TOP_SMEM = 2 * TOP_FRONTIER * sizeof(uint32_t);
 __global__ void __launch_bounds__(TOP_BLOCK)
 k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base, int levels)
 {
+    pdl_wait();
     // original indices of the current level's nodes and of the next level's, ping-pong (a level has <= 2^13 nodes)
     extern __shared__ uint32_t s_frontier[];
     __shared__ uint32_t s_warp[TOP_BLOCK / 32];
@@ -898,6 +922,7 @@ struct b2col_ctx {
     DevBuf d_col_entity, d_col_local, d_world_aabb;
     // build scratch
     uint64_t counted_visits = 0, counted_rays = 0;  // B2COL_MODE_LBVH_COUNT totals
+    bool pdl = true;                             // programmatic dependent launch between the kernels of a frame (B2COL_PDL=0: off)
     int top_levels = -1;                         // -1: automatic (trees larger than L2); dev override B2COL_TOP_LEVELS
     DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
     DevBuf d_nodes_full, d_other_bound;  // export only: full-precision two-slot nodes + their arrival words (k_build_exact)
@@ -980,6 +1005,26 @@ b2col_status fail(b2col_ctx* ctx, b2col_status st, const char* fmt, ...)
         kern<<<(grid), (block), 0, (ctx_)->stream>>>(__VA_ARGS__);                        \
         ++(ctx_)->launches;                                                               \
         cudaError_t e_ = cudaGetLastError();                                              \
+        if (e_ != cudaSuccess)                                                            \
+            return fail((ctx_), B2COL_ERR_CUDA, "launch of %s failed: %s", #kern, cudaGetErrorString(e_)); \
+    } while (0)
+
+// Frame-path launch: as LAUNCH, with programmatic stream serialization when ctx->pdl (every kernel launched this way
+// starts with pdl_wait()).
+#define LAUNCH_FRAME(ctx_, kern, grid, block, smem, ...)                                  \
+    do {                                                                                  \
+        cudaLaunchConfig_t cfg_ = {};                                                     \
+        cfg_.gridDim = dim3(grid);                                                        \
+        cfg_.blockDim = dim3(block);                                                      \
+        cfg_.dynamicSmemBytes = (smem);                                                   \
+        cfg_.stream = (ctx_)->stream;                                                     \
+        cudaLaunchAttribute attr_[1];                                                     \
+        attr_[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                 \
+        attr_[0].val.programmaticStreamSerializationAllowed = 1;                          \
+        cfg_.attrs = attr_;                                                               \
+        cfg_.numAttrs = (ctx_)->pdl ? 1 : 0;                                              \
+        cudaError_t e_ = cudaLaunchKernelEx(&cfg_, kern, __VA_ARGS__);                    \
+        ++(ctx_)->launches;                                                               \
         if (e_ != cudaSuccess)                                                            \
             return fail((ctx_), B2COL_ERR_CUDA, "launch of %s failed: %s", #kern, cudaGetErrorString(e_)); \
     } while (0)
@@ -1132,6 +1177,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
+        if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
         if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
@@ -1289,7 +1335,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
 // hierarchy + bounds from the sorted keys in d_keys/d_vals[side]
 static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
 {
-    LAUNCH(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+    LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
            ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
            ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
     ctx->scratch_clean = true;  // k_build leaves every scratch word zero
@@ -1298,9 +1344,7 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
     const int levels = ctx->top_levels >= 0 ? ctx->top_levels : (n > (1u << 21) ? TOP_LEVELS : 0);
     if (levels > 0 && n > 1u) {
         QNode* top = reinterpret_cast<QNode*>(blob_leaves(ctx, n) + n);
-        k_top_layout<<<1, TOP_BLOCK, TOP_SMEM, ctx->stream>>>(blob_hdr(ctx), blob_qnodes(ctx), top, (uint32_t)((n - 1u) + n), std::min(levels, TOP_LEVELS));
-        ++ctx->launches;
-        if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "launch of k_top_layout failed: %s", cudaGetErrorString(e));
+        LAUNCH_FRAME(ctx, k_top_layout, 1, TOP_BLOCK, TOP_SMEM, blob_hdr(ctx), (const QNode*)blob_qnodes(ctx), top, (uint32_t)((n - 1u) + n), std::min(levels, TOP_LEVELS));
     }
     return B2COL_OK;
 }
@@ -1313,7 +1357,7 @@ static b2col_status enqueue_propagate(b2col_ctx* ctx)
     for (size_t k = 0; k < n_levels; ++k) {
         const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
         if (!cnt) continue;
-        LAUNCH(ctx, k_propagate_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+        LAUNCH_FRAME(ctx, k_propagate_level, cdiv(cnt, 256), 256, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
                ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>());
     }
     return B2COL_OK;
@@ -1383,7 +1427,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
         for (size_t k = 0; k < n_levels; ++k) {
             const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
             if (!cnt) continue;
-            LAUNCH(ctx, k_propagate_refit_level, cdiv(cnt, 256), 256, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+            LAUNCH_FRAME(ctx, k_propagate_refit_level, cdiv(cnt, 256), 256, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
                    ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_of_entity.as<uint32_t>(),
                    ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
         }
@@ -1392,7 +1436,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
     }
     if (propagate) GUARD(enqueue_propagate(ctx));
     PHASE(ctx);
-    LAUNCH(ctx, k_refit, cdiv(n, 256), 256, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
+    LAUNCH_FRAME(ctx, k_refit, cdiv(n, 256), 256, 0, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
            ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
     PHASE(ctx);
     return B2COL_OK;
@@ -1408,7 +1452,7 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
     const uint32_t n = ctx->n_colliders;
     GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
     if (!full) {
-        LAUNCH(ctx, k_header, 1, 1, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
+        LAUNCH_FRAME(ctx, k_header, 1, 1, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
         GUARD(launch_build(ctx, n, ctx->sorted_side));
         PHASE(ctx);
         return B2COL_OK;
@@ -1418,13 +1462,13 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
     uint32_t* ghist = scratch_ghist(ctx);
     {
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
-        LAUNCH(ctx, k_morton, grid, 256, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, ctx->T,
+        LAUNCH_FRAME(ctx, k_morton, grid, 256, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, ctx->T,
                ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
     PHASE(ctx);  // morton
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
-        LAUNCH(ctx, k_onesweep, tiles, RS_THREADS, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+        LAUNCH_FRAME(ctx, k_onesweep, tiles, RS_THREADS, 0, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
                scratch_lookback(ctx) + (size_t)p * lb_words_per_pass, scratch_tickets(ctx) + p);
         side ^= 1;

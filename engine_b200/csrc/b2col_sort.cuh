@@ -88,6 +88,9 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();  // frame path launches with programmatic stream serialization (b2col.cu, pdl_wait)
+#endif
     RS_STAMP(0);
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
 #pragma unroll
