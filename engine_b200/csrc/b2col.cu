@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -875,6 +876,22 @@ k_trace_reftopo(const b2col_ray* __restrict__ rays, size_t n_rays, b2col_raycast
     write_raycast(reinterpret_cast<uint32_t*>(out + i), r, h.hit, h.t, h.side, h.entity);
 }
 
+// Results to a page-locked host buffer by SM stores instead of the copy engine (host-buffer pipeline, d2h mode "sm").
+// With eight processes of one host copying at once and nothing else running, the copy engines of half of the GPUs were
+// starved to ~9 GB/s while plain stores from the SMs kept ~15-18 GB/s on every GPU (tools/micro/duplex_bench.cu: slowest
+// rank 80 -> 42 ms per step).  Inside the real pipeline the gain shrinks to 4 % at 8 GPUs and turns into a loss on one GPU,
+// so this leg is opt-in (B2COL_D2H_MODE=sm, or =auto to let b2col_raycast_batch measure both and keep the faster).
+__global__ void __launch_bounds__(256)
+k_copy_out(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, size_t n_words)
+{
+    const size_t n16 = n_words / 4;
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    const size_t stride = (size_t)gridDim.x * blockDim.x, first = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = first; i < n16; i += stride) d4[i] = s4[i];
+    for (size_t i = 4 * n16 + first; i < n_words; i += stride) dst[i] = src[i];
+}
+
 __global__ void __launch_bounds__(256)
 k_export(uint32_t n, const BlobHeader* __restrict__ hdr, const Node* __restrict__ nodes, const LeafRec* __restrict__ leaves, BiTreeNode60* out,
          uint8_t* used)
@@ -957,6 +974,14 @@ struct b2col_ctx {
     size_t small_next = SMALL_SLOTS;
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
     std::vector<cudaEvent_t> pipe_events;
+    // device->host leg of the pipeline: 0 = copy engine (default), 1 = SM stores (k_copy_out), -1 = measure both and keep the
+    // faster (big calls only); B2COL_D2H_MODE=ce|sm|auto.  Measured (profiles/r1_e_d2h_modes.txt): alone on the host the copy
+    // engine wins by far (1336 vs 743 Mrays/s: the copy kernel queues behind the persistent trace blocks); with eight
+    // processes sharing the host the SM stores win by 4 % (2130 vs 2044) — not worth a default that depends on the neighbours.
+    int d2h_policy = 0;
+    int n_sm = 148;
+    uint64_t d2h_calls = 0;
+    double d2h_ns_per_ray[2] = {0.0, 0.0};
     // rays per chunk of the host-buffer pipeline: largest, first (tools/tune_e2e.py on B200, 16M rays: 256K -> 1M: 12.55 ms;
     // 128K -> 2M: 13.1; 256K -> 512K: 14.1 — smaller chunks leave the persistent trace kernel too few rays per launch)
     size_t e2e_chunk = 1u << 20, e2e_first_chunk = 256u << 10, e2e_min_chunk = 64u << 10;
@@ -1167,6 +1192,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
     {   // persistent trace kernel: one resident wave of blocks
         int sms = 148, per_sm = 8;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        c->n_sm = sms;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh<false>, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
@@ -1178,6 +1204,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_D2H_MODE")) c->d2h_policy = !strcmp(e, "ce") ? 0 : (!strcmp(e, "sm") ? 1 : -1);
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
         if (const char* e = getenv("B2COL_GRAPH")) c->use_graph = atoi(e) != 0;
@@ -1672,6 +1699,29 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
         }
         b2col_ray* d_r = ctx->d_rays.as<b2col_ray>();
         b2col_raycast* d_h = ctx->d_hits.as<b2col_raycast>();
+        // device->host leg: copy engine, or SM stores when the buffer is page-locked (device-accessible through UVA) and
+        // 16-byte aligned.  Big calls time themselves: the first uses the copy engine, the second the SMs, later ones the
+        // faster of the two (every 32nd call tries the other again: what else runs on the host changes).
+        uint32_t* h_out_dev = nullptr;
+        {
+            cudaPointerAttributes pa{};
+            if (cudaPointerGetAttributes(&pa, h_out) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer && ((uintptr_t)pa.devicePointer & 15u) == 0)
+                h_out_dev = static_cast<uint32_t*>(pa.devicePointer);
+            else
+                cudaGetLastError();
+        }
+        const bool timed = n >= ((size_t)1 << 20);
+        int d2h = 0;
+        if (h_out_dev) {
+            if (ctx->d2h_policy >= 0) d2h = ctx->d2h_policy;
+            else if (timed) {
+                const uint64_t k = ctx->d2h_calls;
+                const int best = ctx->d2h_ns_per_ray[1] < ctx->d2h_ns_per_ray[0] ? 1 : 0;
+                d2h = k == 0 ? 0 : (k == 1 ? 1 : ((k & 31u) == 0 ? best ^ 1 : best));
+            }
+            else d2h = (ctx->d2h_calls >= 2 && ctx->d2h_ns_per_ray[1] < ctx->d2h_ns_per_ray[0]) ? 1 : 0;
+        }
+        const auto t_begin = std::chrono::steady_clock::now();
         size_t off = 0, m = first_chunk, c = 0;
         while (off < n) {
             m = std::min(m, n - off);
@@ -1688,13 +1738,26 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
             GUARD(enqueue_trace(ctx, d_r + off, m, d_h + off, mode));
             CU(cudaEventRecord(ev_k, ctx->stream));
             CU(cudaStreamWaitEvent(ctx->stream_out, ev_k, 0));
-            CU(cudaMemcpyAsync(h_out + off, d_h + off, m * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream_out));
+            if (d2h == 1) {
+                k_copy_out<<<2 * ctx->n_sm, 256, 0, ctx->stream_out>>>(reinterpret_cast<const uint32_t*>(d_h + off), h_out_dev + 9 * off, 9 * m);
+                ++ctx->launches;
+                if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "launch of k_copy_out failed: %s", cudaGetErrorString(e));
+            }
+            else {
+                CU(cudaMemcpyAsync(h_out + off, d_h + off, m * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream_out));
+            }
             off += m;
             ++c;
             m = std::min(2 * m, ctx->e2e_chunk);
         }
         CU(cudaStreamSynchronize(ctx->stream_out));
         CU(cudaStreamSynchronize(ctx->stream));
+        if (timed && h_out_dev && ctx->d2h_policy < 0) {
+            const double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t_begin).count() / (double)n;
+            double& est = ctx->d2h_ns_per_ray[d2h];
+            est = est == 0.0 ? ns : 0.5 * est + 0.5 * ns;
+            ++ctx->d2h_calls;
+        }
         return B2COL_OK;
     }
     CU(cudaMemcpyAsync(ctx->d_rays.p, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));

@@ -690,6 +690,36 @@ def test_counting_mode_matches_and_counts(CollisionSystem, emu):
     assert abs(visits - tv.value) <= 0.02 * tv.value, (visits, tv.value)
 
 
+@pytest.mark.parametrize("d2h_mode", ["ce", "sm", "auto"])
+def test_host_pipeline_d2h_modes(CollisionSystem, monkeypatch, d2h_mode):
+    """The chunked host-buffer pipeline returns the same bytes whether the results travel by the copy engine, by SM
+    stores into the page-locked buffer (k_copy_out), or by whichever of the two the context measured to be faster;
+    ray counts that are not multiples of the chunk / of four exercise the ragged tail of the copy kernel."""
+    monkeypatch.setenv("B2COL_D2H_MODE", d2h_mode)
+    s = synth.uniform_boxes(100_000, seed=97, extent=400)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    for R in (1_300_003, 262_145, 1 << 20):
+        rays = synth.random_rays(R, seed=98, extent=400)
+        h_rays = torch.from_numpy(rays).pin_memory()
+        h_out = torch.zeros(R * 36 + 64, dtype=torch.uint8).pin_memory()
+        d_rays = h_rays.cuda()
+        d_out = torch.empty(R * 36, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        cs.raycast_device(d_rays, R, d_out)
+        cs.sync()
+        want = d_out.cpu()
+        for rep in range(4 if d2h_mode == "auto" else 1):
+            h_out.fill_(0xAB)
+            cs.raycast_host_pinned(h_rays, R, h_out)
+            assert bool((h_out[: R * 36] == want).all()), (d2h_mode, R, rep)
+            assert bool((h_out[R * 36 :] == 0xAB).all()), "wrote past the end of the result buffer"
+    # pageable host memory takes the copy-engine path whatever the mode
+    rays = synth.random_rays(300_000, seed=99, extent=400)
+    assert (cs.get_raycasts(rays)["hit"].sum()) > 0
+
+
 def test_few_ray_calls_equal_batch(CollisionSystem):
     """GetRaycast is a batch of one: calls of 1..32 rays take the mapped-staging path (one launch, no copies); they must
     return exactly what the same rays return inside a large batch, across more calls than the counter pool has slots."""
