@@ -377,15 +377,29 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
     }
     __syncthreads();
     const MortonPlan plan = s_plan;
+    // A modest grid (4 blocks per SM: every block ends with up to 1024 atomics on the same 1024 global counters, and 8 blocks
+    // per SM spent 4 us more there) whose threads keep two records in flight.
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2u * stride) {
+        const uint32_t j = i + stride;
+        const bool two = j < n;
         const float4* bp = reinterpret_cast<const float4*>(world_rec + i);
-        const float4 b0 = bp[0], b1 = bp[1];
-        const float lo[3] = {b0.x, b0.y, b0.z}, hi[3] = {b0.w, b1.x, b1.y};
-        const uint64_t key = morton_key(lo, hi, plan);
-        keys[i] = key;
-        vals[i] = i;
-        for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+        const float4* cp = reinterpret_cast<const float4*>(world_rec + (two ? j : i));
+        const float4 b0 = bp[0], b1 = bp[1], c0 = cp[0], c1 = cp[1];
+        {
+            const float lo[3] = {b0.x, b0.y, b0.z}, hi[3] = {b0.w, b1.x, b1.y};
+            const uint64_t key = morton_key(lo, hi, plan);
+            keys[i] = key;
+            vals[i] = i;
+            for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+        }
+        if (two) {
+            const float lo[3] = {c0.x, c0.y, c0.z}, hi[3] = {c0.w, c1.x, c1.y};
+            const uint64_t key = morton_key(lo, hi, plan);
+            keys[j] = key;
+            vals[j] = j;
+            for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+        }
     }
     __syncthreads();
     for (int p = 0; p < passes; ++p) {
@@ -980,6 +994,7 @@ struct b2col_ctx {
     // processes sharing the host the SM stores win by 4 % (2130 vs 2044) — not worth a default that depends on the neighbours.
     int d2h_policy = 0;
     int n_sm = 148;
+    int morton_blocks_per_sm = 0;  // 0 = by collider count; B2COL_MORTON_BLOCKS_PER_SM overrides (tuning)
     uint64_t d2h_calls = 0;
     double d2h_ns_per_ray[2] = {0.0, 0.0};
     // rays per chunk of the host-buffer pipeline: largest, first (tools/tune_e2e.py on B200, 16M rays: 256K -> 1M: 12.55 ms;
@@ -1204,6 +1219,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
         if (const char* e = getenv("B2COL_D2H_MODE")) c->d2h_policy = !strcmp(e, "ce") ? 0 : (!strcmp(e, "sm") ? 1 : -1);
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
@@ -1488,7 +1504,10 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
     const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     uint32_t* ghist = scratch_ghist(ctx);
     {
-        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), 148u * 8u);
+        // 4 blocks per SM up to 2M colliders (fewer end-of-block atomics on the shared counters: -4 us at 1M), 8 beyond (the
+        // stream dominates: 125 -> 119 us at 10M)
+        const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
+        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), (uint32_t)(ctx->n_sm * per_sm));
         LAUNCH_FRAME(ctx, k_morton, grid, 256, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, ctx->T,
                ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
