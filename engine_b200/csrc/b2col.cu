@@ -292,7 +292,10 @@ k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, c
 // The same level, FUSED with the refit of the colliders that sit on this level's entities (b2col_update's normal
 // path): the world matrix is still in registers when transformBox needs it, so the refit's 64-byte re-read per
 // collider and one launch disappear.  col_of_entity[e] = index of e's collider or NO_COLLIDER.
-__global__ void __launch_bounds__(256)
+#ifndef B2_REFIT_MIN_BLOCKS
+#define B2_REFIT_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(256, B2_REFIT_MIN_BLOCKS)
 k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
                         const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
                         const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds)
