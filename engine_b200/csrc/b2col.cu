@@ -362,7 +362,7 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 // registers here anyway).  The bit allocation (make_morton_plan) depends on the centroid bounds the refit has
 // just reduced: thread 0 of every block derives it once and shares it.
 __global__ void __launch_bounds__(256)
-k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, float T, uint64_t* __restrict__ keys,
+k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, int packed, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
     pdl_wait();
@@ -392,15 +392,25 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
         {
             const float lo[3] = {b0.x, b0.y, b0.z}, hi[3] = {b0.w, b1.x, b1.y};
             const uint64_t key = morton_key(lo, hi, plan);
-            keys[i] = key;
-            vals[i] = i;
+            if (packed) {  // keys of at most 32 bits travel through the sort as key << 32 | index (k_onesweep MODE 1 / 2)
+                keys[i] = (key << 32) | i;
+            }
+            else {
+                keys[i] = key;
+                vals[i] = i;
+            }
             for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
         }
         if (two) {
             const float lo[3] = {c0.x, c0.y, c0.z}, hi[3] = {c0.w, c1.x, c1.y};
             const uint64_t key = morton_key(lo, hi, plan);
-            keys[j] = key;
-            vals[j] = j;
+            if (packed) {  // keys of at most 32 bits travel through the sort as key << 32 | index (k_onesweep MODE 1 / 2)
+                keys[j] = (key << 32) | j;
+            }
+            else {
+                keys[j] = key;
+                vals[j] = j;
+            }
             for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
         }
     }
@@ -997,6 +1007,7 @@ struct b2col_ctx {
     // processes sharing the host the SM stores win by 4 % (2130 vs 2044) — not worth a default that depends on the neighbours.
     int d2h_policy = 0;
     int n_sm = 148;
+    bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
     int morton_blocks_per_sm = 0;  // 0 = by collider count; B2COL_MORTON_BLOCKS_PER_SM overrides (tuning)
     uint64_t d2h_calls = 0;
     double d2h_ns_per_ray[2] = {0.0, 0.0};
@@ -1222,6 +1233,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
         if (const char* e = getenv("B2COL_D2H_MODE")) c->d2h_policy = !strcmp(e, "ce") ? 0 : (!strcmp(e, "sm") ? 1 : -1);
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
@@ -1506,20 +1518,28 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     uint32_t* ghist = scratch_ghist(ctx);
+    const bool packed = 3 * ctx->bits - ctx->drop <= 32 && !ctx->no_packed_sort;  // key << 32 | index in one word through the sort
     {
         // 4 blocks per SM up to 2M colliders (fewer end-of-block atomics on the shared counters: -4 us at 1M), 8 beyond (the
         // stream dominates: 125 -> 119 us at 10M)
         const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
         const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), (uint32_t)(ctx->n_sm * per_sm));
-        LAUNCH_FRAME(ctx, k_morton, grid, 256, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, ctx->T,
+        LAUNCH_FRAME(ctx, k_morton, grid, 256, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, (int)packed, ctx->T,
                ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
     PHASE(ctx);  // morton
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
-        LAUNCH_FRAME(ctx, k_onesweep, tiles, RS_THREADS, 0, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
-               ctx->d_keys[side ^ 1].as<uint64_t>(), ctx->d_vals[side ^ 1].as<uint32_t>(), n, tiles, p * RS_BITS, ghist + p * RS_RADIX,
-               scratch_lookback(ctx) + (size_t)p * lb_words_per_pass, scratch_tickets(ctx) + p);
+        const uint64_t* kin = ctx->d_keys[side].as<uint64_t>();
+        const uint32_t* vin = ctx->d_vals[side].as<uint32_t>();
+        uint64_t* kout = ctx->d_keys[side ^ 1].as<uint64_t>();
+        uint32_t* vout = ctx->d_vals[side ^ 1].as<uint32_t>();
+        const uint32_t* gh = ghist + p * RS_RADIX;
+        uint32_t* lb = scratch_lookback(ctx) + (size_t)p * lb_words_per_pass;
+        uint32_t* tk = scratch_tickets(ctx) + p;
+        if (!packed) LAUNCH_FRAME(ctx, k_onesweep<0>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, p * RS_BITS, gh, lb, tk);
+        else if (p + 1 < ctx->passes) LAUNCH_FRAME(ctx, k_onesweep<1>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, 32 + p * RS_BITS, gh, lb, tk);
+        else LAUNCH_FRAME(ctx, k_onesweep<2>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, 32 + p * RS_BITS, gh, lb, tk);
         side ^= 1;
         PHASE(ctx);  // radix pass p
     }

@@ -76,6 +76,13 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* wa
 // ever wait on tiles that already started (forward progress of the look-back).
 //   ghist    [256]  total count of each digit value in this pass (over all n keys)
 //   lookback [tiles + ceil(tiles / LB_GROUP)][256] zero-initialised status words for this pass
+//
+// MODE 0: 64-bit keys and 32-bit values in separate arrays (keys wider than 32 bits).
+// MODE 1, 2: the key is at most 32 bits wide and travels as ONE 64-bit word (key << 32 | value) — 8 instead of 12 bytes per
+//   pair and pass, one staging round and one scatter instead of two; `shift` then addresses the upper half (32 + 8 * pass).
+//   MODE 1 writes packed words again (vin / vout unused); MODE 2, the last pass, writes kout = key, vout = value, so that
+//   everything downstream reads the same arrays whatever the key width.
+template <int MODE>
 __global__ void __launch_bounds__(RS_THREADS)
 k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
            uint32_t n, uint32_t n_tiles, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
@@ -110,11 +117,11 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
         const uint32_t idx = wbase + (uint32_t)k * 32u;
         const bool ok = idx < valid;
         key[k] = ok ? kin[tile_base + idx] : ~0ull;
-        val[k] = ok ? vin[tile_base + idx] : 0u;
+        if (MODE == 0) val[k] = ok ? vin[tile_base + idx] : 0u;
     }
 
 #ifdef B2_SORT_TIMING
-    if (key[0] == 0x123456789abcdefull && val[RS_ITEMS - 1] == 77u) s_tile = 0;  // wait for the loads
+    if (key[0] == 0x123456789abcdefull && key[RS_ITEMS - 1] == 77ull) s_tile = 0;  // wait for the loads
 #endif
     RS_STAMP(1);
     // ---- rank within the warp: lanes with equal digits find each other with one ballot per digit bit
@@ -236,11 +243,21 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
             const uint64_t kk = skeys[j];
             const uint32_t d = (uint32_t)(kk >> shift) & (RS_RADIX - 1);
             dst[m] = gbase[d] + (j - sbase[d]);
-            kout[dst[m]] = kk;
+            if (MODE == 2) {
+                kout[dst[m]] = kk >> 32;
+                vout[dst[m]] = (uint32_t)kk;
+            }
+            else {
+                kout[dst[m]] = kk;
+            }
         }
     }
-    __syncthreads();
     RS_STAMP(4);
+    if (MODE != 0) {
+        RS_STAMP(5);
+        return;
+    }
+    __syncthreads();
     uint32_t* svals = reinterpret_cast<uint32_t*>(skeys);
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
