@@ -1500,7 +1500,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
     return B2COL_OK;
 }
 
-inline size_t lookback_words_per_pass(uint32_t tiles) { return ((size_t)tiles + (tiles + LB_GROUP - 1) / LB_GROUP) * RS_RADIX; }  // tile counts + group status
+inline size_t lookback_words_per_pass(uint32_t tiles) { return ((size_t)tiles + (tiles + LB_GROUP_SMALL - 1) / LB_GROUP_SMALL) * RS_RADIX; }  // tile counts + group status
 
 // The frame's kernels, nothing else (no allocation, no memset, no synchronisation): capturable.
 //   full:  [propagate+refit per level | propagate per level, refit] , Morton, radix passes, hierarchy
@@ -1537,9 +1537,20 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
         const uint32_t* gh = ghist + p * RS_RADIX;
         uint32_t* lb = scratch_lookback(ctx) + (size_t)p * lb_words_per_pass;
         uint32_t* tk = scratch_tickets(ctx) + p;
-        if (!packed) LAUNCH_FRAME(ctx, k_onesweep<0>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, p * RS_BITS, gh, lb, tk);
-        else if (p + 1 < ctx->passes) LAUNCH_FRAME(ctx, k_onesweep<1>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, 32 + p * RS_BITS, gh, lb, tk);
-        else LAUNCH_FRAME(ctx, k_onesweep<2>, tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, 32 + p * RS_BITS, gh, lb, tk);
+        const int sh = p * RS_BITS + (packed ? 32 : 0);
+        const int mode = !packed ? 0 : (p + 1 < ctx->passes ? 1 : 2);
+#define B2_SORT_PASS(M, G) LAUNCH_FRAME(ctx, (k_onesweep<M, G>), tiles, RS_THREADS, 0, kin, vin, kout, vout, n, tiles, sh, gh, lb, tk)
+        if (tiles >= 128u) {
+            if (mode == 0) B2_SORT_PASS(0, LB_GROUP_SMALL);
+            else if (mode == 1) B2_SORT_PASS(1, LB_GROUP_SMALL);
+            else B2_SORT_PASS(2, LB_GROUP_SMALL);
+        }
+        else {
+            if (mode == 0) B2_SORT_PASS(0, LB_GROUP_LARGE);
+            else if (mode == 1) B2_SORT_PASS(1, LB_GROUP_LARGE);
+            else B2_SORT_PASS(2, LB_GROUP_LARGE);
+        }
+#undef B2_SORT_PASS
         side ^= 1;
         PHASE(ctx);  // radix pass p
     }

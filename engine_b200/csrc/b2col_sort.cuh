@@ -31,11 +31,9 @@ enum : uint32_t {
 #define B2_LB_BATCH 8
 #endif
 constexpr int LB_BATCH = B2_LB_BATCH;
-#ifndef B2_LB_GROUP
-#define B2_LB_GROUP 16
-#endif
-constexpr uint32_t LB_GROUP = B2_LB_GROUP;  // tiles per look-back group
-
+// Tiles per look-back group, a template parameter of the pass: 8 from 128 tiles up (-2.8 us per update at 1M, -25 us at 10M),
+// 16 below (200k colliders: 70.8 vs 73.6 us with 8).  The status array is sized for the smaller group.
+constexpr uint32_t LB_GROUP_SMALL = 8, LB_GROUP_LARGE = 16;
 static_assert(RS_THREADS == RS_RADIX, "one thread per digit in the scan phases");
 
 #ifdef B2_SORT_TIMING  // dev builds only: per-tile phase timestamps (ns, %globaltimer) of the LAST pass launched
@@ -82,7 +80,7 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* wa
 //   pair and pass, one staging round and one scatter instead of two; `shift` then addresses the upper half (32 + 8 * pass).
 //   MODE 1 writes packed words again (vin / vout unused); MODE 2, the last pass, writes kout = key, vout = value, so that
 //   everything downstream reads the same arrays whatever the key width.
-template <int MODE>
+template <int MODE, uint32_t LB_GROUP>
 __global__ void __launch_bounds__(RS_THREADS)
 k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
            uint32_t n, uint32_t n_tiles, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
@@ -180,12 +178,12 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
         {
             uint32_t v[LB_GROUP - 1];
 #pragma unroll
-            for (int j = 0; j < LB_GROUP - 1; ++j) {
+            for (int j = 0; j < (int)LB_GROUP - 1; ++j) {
                 const uint32_t t = first + (uint32_t)j;
                 v[j] = t < tile ? ta[(size_t)t * RS_RADIX + tid] : LB_FLAG_AGG;
             }
 #pragma unroll
-            for (int j = 0; j < LB_GROUP - 1; ++j) {
+            for (int j = 0; j < (int)LB_GROUP - 1; ++j) {
                 const uint32_t t = first + (uint32_t)j;
                 uint32_t w = v[j];
                 while ((w >> 30) == 0u) w = ta[(size_t)t * RS_RADIX + tid];  // not posted yet: that tile is running (ticket order)
