@@ -444,7 +444,10 @@ __global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, fl
 // boundary splits: prefix-max(level)[p-1] > level[p] < suffix-max(level)[p+1].
 // (Measured and dropped, profiles/r1_d_experiments.txt: writing the leaf records from the last radix pass, where the
 // gathers are independent — the pass grew by 14 us, this kernel shrank by 4: here the gather hides under the climb.)
-constexpr int BUILD_BLOCK = 256;
+#ifndef B2_BUILD_BLOCK
+#define B2_BUILD_BLOCK 128
+#endif
+constexpr int BUILD_BLOCK = B2_BUILD_BLOCK;  // update at 1M: 64 -> 170.4 us, 96 -> 168.4, 128 -> 167.8, 256 -> 170.1, 512 -> 178.9, 1024 -> 204.0
 __global__ void __launch_bounds__(BUILD_BLOCK)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
 {
