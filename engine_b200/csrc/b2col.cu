@@ -235,7 +235,13 @@ __device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const flo
     }
 }
 
-// block reduction of the per-thread bounds: warp shuffles, then one atomic per block and word (256-thread blocks)
+#ifndef B2_REFIT_BLOCK
+#define B2_REFIT_BLOCK 128
+#endif
+// threads per block of the refit kernels; update at 1M / 10M: 64 -> 179 us, 96 -> 167 / 1612, 128 -> 162 / 1466 (with 8 blocks per SM
+// promised to the compiler), 160 -> 166 / 1514, 192 -> 167 / 1526, 256 -> 168 / 1534, 512 -> 182
+constexpr int REFIT_BLOCK = B2_REFIT_BLOCK;
+// block reduction of the per-thread bounds: warp shuffles, then one atomic per block and word
 __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t* bounds)
 {
 #pragma unroll
@@ -246,7 +252,7 @@ __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t
             cmax[k] = fmaxf(cmax[k], __shfl_xor_sync(0xffffffffu, cmax[k], o));
         }
     }
-    __shared__ float smin[8][6], smax[8][6];
+    __shared__ float smin[REFIT_BLOCK / 32][6], smax[REFIT_BLOCK / 32][6];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) {
 #pragma unroll
@@ -259,7 +265,7 @@ __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t
     if (threadIdx.x < 6) {
         const int k = threadIdx.x;
         float a = smin[0][k], b = smax[0][k];
-        for (int w = 1; w < 8; ++w) {
+        for (int w = 1; w < REFIT_BLOCK / 32; ++w) {
             a = fminf(a, smin[w][k]);
             b = fmaxf(b, smax[w][k]);
         }
@@ -293,9 +299,9 @@ k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, c
 // path): the world matrix is still in registers when transformBox needs it, so the refit's 64-byte re-read per
 // collider and one launch disappear.  col_of_entity[e] = index of e's collider or NO_COLLIDER.
 #ifndef B2_REFIT_MIN_BLOCKS
-#define B2_REFIT_MIN_BLOCKS 1
+#define B2_REFIT_MIN_BLOCKS 8
 #endif
-__global__ void __launch_bounds__(256, B2_REFIT_MIN_BLOCKS)
+__global__ void __launch_bounds__(REFIT_BLOCK, B2_REFIT_MIN_BLOCKS)
 k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
                         const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
                         const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds)
@@ -318,7 +324,7 @@ k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t co
 
 // Refit loop alone (reference src/system_collisions.cpp:123-132): world AABB = transformBox(local, world_matrix), for
 // callers that supply world matrices themselves or propagate separately.  Also reduces the scene bounds.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(REFIT_BLOCK)
 k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __restrict__ col_local, const float4* __restrict__ world,
         LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
@@ -1488,7 +1494,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
         for (size_t k = 0; k < n_levels; ++k) {
             const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
             if (!cnt) continue;
-            LAUNCH_FRAME(ctx, k_propagate_refit_level, cdiv(cnt, 256), 256, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
+            LAUNCH_FRAME(ctx, k_propagate_refit_level, cdiv(cnt, REFIT_BLOCK), REFIT_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
                    ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_of_entity.as<uint32_t>(),
                    ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
         }
@@ -1497,7 +1503,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
     }
     if (propagate) GUARD(enqueue_propagate(ctx));
     PHASE(ctx);
-    LAUNCH_FRAME(ctx, k_refit, cdiv(n, 256), 256, 0, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
+    LAUNCH_FRAME(ctx, k_refit, cdiv(n, REFIT_BLOCK), REFIT_BLOCK, 0, n, ctx->d_col_entity.as<uint32_t>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world.as<float4>(),
            ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
     PHASE(ctx);
     return B2COL_OK;
