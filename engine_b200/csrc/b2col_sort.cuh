@@ -80,8 +80,11 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* wa
 //   pair and pass, one staging round and one scatter instead of two; `shift` then addresses the upper half (32 + 8 * pass).
 //   MODE 1 writes packed words again (vin / vout unused); MODE 2, the last pass, writes kout = key, vout = value, so that
 //   everything downstream reads the same arrays whatever the key width.
+#ifndef B2_RS_MIN_BLOCKS
+#define B2_RS_MIN_BLOCKS 1
+#endif
 template <int MODE, uint32_t LB_GROUP>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, B2_RS_MIN_BLOCKS)
 k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout, uint32_t* __restrict__ vout,
            uint32_t n, uint32_t n_tiles, int shift, const uint32_t* __restrict__ ghist, uint32_t* lookback, uint32_t* ticket)
 {
