@@ -81,7 +81,7 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* wa
 //   MODE 1 writes packed words again (vin / vout unused); MODE 2, the last pass, writes kout = key, vout = value, so that
 //   everything downstream reads the same arrays whatever the key width.
 #ifndef B2_RS_MIN_BLOCKS
-#define B2_RS_MIN_BLOCKS 1
+#define B2_RS_MIN_BLOCKS 2  // 128 registers: with 1 the compiler takes ~170 and a 10M-pair pass slows from 111 to 162 us
 #endif
 template <int MODE, uint32_t LB_GROUP>
 __global__ void __launch_bounds__(RS_THREADS, B2_RS_MIN_BLOCKS)
