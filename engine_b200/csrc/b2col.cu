@@ -367,14 +367,19 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 // Morton keys + primitive indices + the digit histograms of every radix pass (the keys are in
 // registers here anyway).  The bit allocation (make_morton_plan) depends on the centroid bounds the refit has
 // just reduced: thread 0 of every block derives it once and shares it.
-__global__ void __launch_bounds__(256)
+#ifndef B2_MORTON_BLOCK
+#define B2_MORTON_BLOCK 256
+#endif
+constexpr int MORTON_BLOCK = B2_MORTON_BLOCK;
+__global__ void __launch_bounds__(MORTON_BLOCK)
 k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, int packed, float T, uint64_t* __restrict__ keys,
          uint32_t* __restrict__ vals, uint32_t* ghist)
 {
     pdl_wait();
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
     __shared__ MortonPlan s_plan;
-    for (int p = 0; p < passes; ++p) shist[p][threadIdx.x] = 0u;
+    for (int p = 0; p < passes; ++p)
+        for (int b = threadIdx.x; b < RS_RADIX; b += MORTON_BLOCK) shist[p][b] = 0u;
     if (threadIdx.x == 0) {
         float cmin[3], cmax[3];
 #pragma unroll
@@ -422,8 +427,10 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
     }
     __syncthreads();
     for (int p = 0; p < passes; ++p) {
-        const uint32_t c = shist[p][threadIdx.x];
-        if (c) atomicAdd(&ghist[p * RS_RADIX + threadIdx.x], c);
+        for (int b = threadIdx.x; b < RS_RADIX; b += MORTON_BLOCK) {
+            const uint32_t c = shist[p][b];
+            if (c) atomicAdd(&ghist[p * RS_RADIX + b], c);
+        }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, bounds, n, T);
 }
@@ -1532,8 +1539,8 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
         // 4 blocks per SM up to 2M colliders (fewer end-of-block atomics on the shared counters: -4 us at 1M), 8 beyond (the
         // stream dominates: 125 -> 119 us at 10M)
         const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
-        const uint32_t grid = std::min<uint32_t>(cdiv(n, 256), (uint32_t)(ctx->n_sm * per_sm));
-        LAUNCH_FRAME(ctx, k_morton, grid, 256, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, (int)packed, ctx->T,
+        const uint32_t grid = std::min<uint32_t>(cdiv(n, MORTON_BLOCK), (uint32_t)(ctx->n_sm * per_sm * 256 / MORTON_BLOCK));  // per_sm counts 256-thread blocks
+        LAUNCH_FRAME(ctx, k_morton, grid, MORTON_BLOCK, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, (int)packed, ctx->T,
                ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
     PHASE(ctx);  // morton
