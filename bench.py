@@ -192,6 +192,77 @@ def workload_config(args):
 
 
 # -------------------------------------------------------------------------------------------------
+class DevMem:
+    """device memory owned by the library (the gather window) as a torch tensor: torch.as_tensor(DevMem(addr, n), device=...)"""
+
+    def __init__(self, addr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (addr, False), "version": 2}
+
+
+def source_hash() -> str:
+    """identifies the build a committed ncu capture belongs to (roofline.traffic): sha256 over the CUDA sources"""
+    import hashlib
+
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "engine_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def measure_rebuild(cs, scene, args, torch):
+    """refit + rebuild per frame at N colliders (BASELINE.json metric, second half), three ways:
+      ms          every collider MOVES every frame: a device op perturbs all positions, the TRS arrays are handed over with
+                  b2col_set_trs_device (44 B/entity device-to-device, inside the timed region) and b2col_update rebuilds — median of 100
+      static_ms   the same TRS replayed (nothing moves, warmest caches): the round-1 figure, kept for continuity
+      refit_only_ms  b2col_refit on the moving scene (same tree shape, new boxes)"""
+    N = scene.n_colliders
+    peak, _ = measured_peak_gbs()
+    algo = 280.0 * N  # SURVEY.md 8(d): refit 140 B + build 140 B per collider
+    cs.set_scene(scene)
+    cs.on_update()
+    for _ in range(max(args.warmup, 3)):
+        cs.on_update(wait=False)
+    cs.sync()
+    K = max(args.steps, 10)
+    l0 = cs.stats()["kernel_launches"]
+    cs.event_record(0)
+    for _ in range(K):
+        cs.on_update(wait=False)
+    cs.event_record(1)
+    static_ms = cs.event_elapsed_ms(0, 1) / K
+    launches_per_update = (cs.stats()["kernel_launches"] - l0) // K
+    # moving scene: everything on the context's own stream (torch ops included), no host synchronisation inside the loop
+    ext = torch.cuda.ExternalStream(cs.stream)
+    d_pos, d_rot, d_scl = (torch.from_numpy(a).cuda() for a in (scene.pos, scene.rot, scene.scl))
+    g = torch.Generator(device="cuda").manual_seed(7)
+    frames = 100
+    delta = 0.05 * torch.randn((8, scene.pos.shape[0], 3), device="cuda", generator=g)  # 8 seeded per-frame displacement fields, cycled
+    torch.cuda.synchronize()
+    times = {}
+    with torch.cuda.stream(ext):
+        for mode in ("rebuild", "refit_only"):
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(frames + 5)]
+            for f in range(frames + 5):
+                evs[f][0].record(ext)
+                d_pos.add_(delta[f % 8])  # the frame's animation: every collider moves
+                cs.set_trs_device(d_pos, d_rot, d_scl)
+                (cs.on_update if mode == "rebuild" else cs.on_update_refit)(wait=False)
+                evs[f][1].record(ext)
+            cs.sync()
+            t = np.array([a.elapsed_time(b) for a, b in evs[5:]])
+            times[mode] = t
+    cs.set_scene(scene)
+    cs.on_update()  # leave the tree of the unperturbed scene for the traversal
+    ms = float(np.median(times["rebuild"]))
+    return {"ms": ms, "p99_ms": float(np.percentile(times["rebuild"], 99)), "frames": frames, "static_ms": static_ms, "colliders": N,
+            "launches_per_update": launches_per_update, "algorithmic_bytes": algo, "achieved_gbs": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak,
+            "static_frac": algo / (static_ms * 1e-3) / 1e9 / peak, "refit_only_ms": float(np.median(times["refit_only"])),
+            "what": f"every collider moves every frame (device-side perturbation of all positions + 44 B/entity device-to-device hand-over of the TRS arrays, both inside the "
+                    f"timed frame), then fused propagate+refit, Morton, {cs.stats()['sort_passes']}-pass radix sort, hierarchy/bounds as one CUDA-graph replay; median of {frames} "
+                    "frames, each bracketed by CUDA events on the context's stream; static_ms = the same TRS replayed back to back (round-1 definition)"}
+
+
 def run_ours(args):
     # This program's stdout is ONE JSON line, but NCCL writes its version banner to the process's stdout when the first
     # communicator comes up: park fd 1 on stderr until the line is printed.
@@ -202,7 +273,7 @@ def run_ours(args):
     import torch.distributed as dist
 
     from engine_b200 import build as b2build
-    from engine_b200.collision import CollisionSystem
+    from engine_b200.collision import CollisionSystem, shard_bounds
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -213,7 +284,7 @@ def run_ours(args):
         from engine_b200 import dist as b2dist_early
 
         numa = b2dist_early.bind_to_gpu_numa_node(local)  # before any pinned allocation
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))  # barriers / max-over-ranks / the unique id only
     if rank == 0:
         b2build.build()
     if world > 1:
@@ -234,50 +305,50 @@ def run_ours(args):
     cs = CollisionSystem(device=local, use_cuda_graph=True)  # b2col_update replays its kernel sequence as one CUDA graph
     scene = make_scene(args.colliders, args.workload)
     N = scene.n_colliders
+    R = args.rays
 
-    # ---- build on rank 0, replicate over NVLink ---------------------------------------------------
-    rebuild = None
-    bcast_ms = 0.0
-    if rank == 0:
-        cs.set_scene(scene)
-        cs.on_update()
-        for _ in range(max(args.warmup, 3)):
-            cs.on_update(wait=False)
-        cs.sync()
-        K = max(args.steps, 10)
-        l0 = cs.stats()["kernel_launches"]
-        cs.event_record(0)
-        for _ in range(K):
-            cs.on_update(wait=False)
-        cs.event_record(1)
-        ms = cs.event_elapsed_ms(0, 1) / K
-        l1 = cs.stats()["kernel_launches"]
-        peak, peak_src = measured_peak_gbs()
-        algo = 280.0 * N  # refit 140 B + build 140 B per collider
-        # refit-only frames (b2col_refit: same tree shape, new boxes; the reference's TODO, src/system_collisions.cpp:116-120)
-        for _ in range(3):
-            cs.on_update_refit(wait=False)
-        cs.event_record(4)
-        for _ in range(K):
-            cs.on_update_refit(wait=False)
-        cs.event_record(5)
-        refit_ms = cs.event_elapsed_ms(4, 5) / K
-        cs.on_update()  # leave a freshly built tree for the traversal below
-        rebuild = {"ms": ms, "colliders": N, "launches_per_update": (l1 - l0) // K, "algorithmic_bytes": algo,
-                   "achieved_gbs": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak, "refit_only_ms": refit_ms,
-                   "what": f"fused propagate+refit, Morton, {cs.stats()['sort_passes']}-pass radix sort, hierarchy/bounds; device-resident TRS, "
-                           "one CUDA graph replay per frame, back-to-back on one stream"}
+    # ---- build on rank 0 -------------------------------------------------------------------------------
+    rebuild = measure_rebuild(cs, scene, args, torch) if rank == 0 else None
+
+    # ---- replicate over NVLink: NCCL called from C++ inside libb2col.so (b2col_comm_*) --------------------
+    multi = None
     if world > 1:
-        from engine_b200 import dist as b2dist
-
+        ids = [CollisionSystem.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        cs.comm_init_rank(world, rank, ids[0])
         barrier()
         t0 = time.perf_counter()
-        b2dist.replicate_bvh(cs, src=0)  # one NCCL broadcast of the BVH blob over NVLink
+        cs.comm_replicate(0, N)  # cold: first collective of the communicator (connection set-up) + allocation of the replicas' blobs
+        cs.sync()
         barrier()
-        bcast_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        cold_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
 
-    # ---- this rank's ray shard ----------------------------------------------------------------------
-    R = args.rays
+        def timed_collective(fn, reps=10):
+            for _ in range(2):
+                fn()
+            cs.sync()
+            barrier()
+            cs.event_record(6)
+            for _ in range(reps):
+                fn()
+            cs.event_record(7)
+            cs.sync()
+            ms = max_over_ranks(cs.event_elapsed_ms(6, 7)) / reps
+            barrier()
+            return ms
+
+        blob_bytes = cs.bvh_blob()[1]
+        bcast_ms = timed_collective(lambda: cs.comm_replicate(0, N))
+        records_ms = timed_collective(lambda: cs.comm_replicate_records(0, N))  # 32 B/collider + Morton/sort/hierarchy on every replica
+        cs.comm_replicate(0, N)
+        cs.sync()
+        barrier()
+        multi = {"bvh_blob_bytes": blob_bytes, "bvh_broadcast_ms": bcast_ms, "bvh_broadcast_gbs": blob_bytes / (bcast_ms * 1e-3) / 1e9, "bvh_broadcast_cold_ms": cold_ms,
+                 "records_broadcast_plus_rebuild_ms": records_ms, "records_bytes": 32 * N,
+                 "how": "warm, 10 back-to-back repeats, CUDA events on every rank's stream, max over ranks: ncclBroadcast straight out of / into the BVH allocations "
+                        "(b2col_comm_replicate) vs ncclBroadcast of the 32-byte world records + Morton/sort/hierarchy on every replica (b2col_comm_replicate_records)"}
+
+    # ---- this rank's ray shard (weak scaling: R rays per GPU, the batch is the concatenation in rank order) ----------
     rays_np = make_rays(R, rank, args.workload)
     h_rays = torch.from_numpy(rays_np).pin_memory()
     h_out = torch.empty(R * 36, dtype=torch.uint8).pin_memory()
@@ -316,6 +387,80 @@ def run_ours(args):
     value = world * R / (step_ms * 1e-3) / 1e6
     hits = int((d_out.view(R, 36)[:, 32] != 0).sum().item())
 
+    # ---- multi-GPU: the same step with the hits gathered on rank 0 INSIDE the timed region ----------------------------
+    if world > 1:
+        def gather_run(d_shard, n_total, steps):
+            for _ in range(2):
+                cs.comm_raycast_gather(d_shard, n_total, 0)
+            cs.sync()
+            barrier()
+            cs.event_record(8)
+            for _ in range(steps):
+                addr = cs.comm_raycast_gather(d_shard, n_total, 0)
+            cs.event_record(9)
+            cs.sync()
+            ms = max_over_ranks(cs.event_elapsed_ms(8, 9)) / steps
+            barrier()
+            return ms, addr
+
+        # weak: world * R rays, slice r = rank r's rays
+        g_ms, addr = gather_run(d_rays, world * R, args.steps)
+        multi["value_with_gather"] = world * R / (g_ms * 1e-3) / 1e6
+        multi["ms_per_step_with_gather"] = g_ms
+        multi["gather_bytes_per_step"] = (world - 1) * R * 36
+        # every rank's FULL slice, bitwise, against a 1-GPU trace of the same rays (rank 0 regenerates each rank's rays)
+        verified = None
+        if rank == 0:
+            win = torch.as_tensor(DevMem(addr, world * R * 36), device=f"cuda:{local}")
+            verified = True
+            tmp_out = torch.empty(R * 36, dtype=torch.uint8, device="cuda")
+            for r in range(world):
+                d_r = d_rays if r == 0 else torch.from_numpy(make_rays(R, r, args.workload)).cuda()
+                cs.raycast_device(d_r, R, tmp_out)
+                cs.sync()
+                verified = verified and bool(torch.equal(tmp_out, win[r * R * 36 : (r + 1) * R * 36]))
+                del d_r
+            del tmp_out, win
+        multi["all_ranks_bitwise_equal_to_1gpu_trace"] = verified
+        # strong: BASELINE configs[2] as written — 16M rays in total, R/N per rank, gathered on rank 0
+        S = 16 * 1024 * 1024
+        batch = make_rays(S, 0, args.workload)  # the same batch on every rank; a rank uploads its slice only
+        lo, hi = shard_bounds(S, world, rank)
+        d_slice = torch.from_numpy(batch[lo:hi]).cuda()
+        s_ms, addr = gather_run(d_slice, S, max(args.steps, 10))
+        strong = {"rays_total": S, "rays_per_gpu": S // world, "ms_per_step_with_gather": s_ms, "value_with_gather": S / (s_ms * 1e-3) / 1e6}
+        for _ in range(2):
+            cs.raycast_device(d_slice, hi - lo, d_out)
+        cs.sync()
+        barrier()
+        cs.event_record(8)
+        for _ in range(max(args.steps, 10)):
+            cs.raycast_device(d_slice, hi - lo, d_out)
+        cs.event_record(9)
+        cs.sync()
+        ms_nog = max_over_ranks(cs.event_elapsed_ms(8, 9)) / max(args.steps, 10)
+        barrier()
+        strong["ms_per_step"] = ms_nog
+        strong["value"] = S / (ms_nog * 1e-3) / 1e6
+        if rank == 0:
+            cs.comm_raycast_gather(d_slice, S, 0)
+        else:
+            cs.comm_raycast_gather(d_slice, S, 0)
+        cs.sync()
+        barrier()
+        if rank == 0:
+            win = torch.as_tensor(DevMem(addr, S * 36), device=f"cuda:{local}")
+            d_all = torch.from_numpy(batch).cuda()
+            one = torch.empty(S * 36, dtype=torch.uint8, device="cuda")
+            cs.raycast_device(d_all, S, one)
+            cs.sync()
+            strong["bitwise_equal_to_1gpu_trace"] = bool(torch.equal(one, win))
+            del win, d_all, one
+        multi["strong"] = strong
+        multi["comm"] = cs.comm_info()
+        del d_slice, batch
+        barrier()
+
     # ---- e2e: the public call with HOST buffers (pinned): H2D + trace + D2H inside the timed region ---
     for _ in range(min(args.warmup, 2)):
         cs.raycast_host_pinned(h_rays, R, h_out)
@@ -327,41 +472,32 @@ def run_ours(args):
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
     barrier()
     e2e_value = world * R / (e2e_ms * 1e-3) / 1e6
-    same = bool((h_out.view(R, 36)[:: max(R // 4096, 1)] == d_out.view(R, 36)[:: max(R // 4096, 1)].cpu()).all().item())
-
-    # ---- hits gathered back to rank 0 over NVLink (NCCL gather), reported separately ------------
-    gather_ms = None
-    if world > 1:
-        from engine_b200 import dist as b2dist
-
-        into = torch.empty(world * d_out.numel(), dtype=torch.uint8, device="cuda") if rank == 0 else None
-        b2dist.gather_hits_device(d_out, dst=0, into=into)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(3):
-            b2dist.gather_hits_device(d_out, dst=0, into=into)
-        barrier()
-        gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / 3
-        if rank == 0:
-            assert bool((into.view(world, -1)[0][: 36 * 4096] == d_out[: 36 * 4096]).all().item())
-        del into
+    cs.raycast_device(d_rays, R, d_out)
+    cs.sync()
+    same = bool(torch.equal(h_out, d_out.cpu()))  # the whole batch, byte for byte
 
     if rank != 0:
         if world > 1:
+            cs.comm_finalize()
             dist.destroy_process_group()
         return
 
     peak, peak_src = measured_peak_gbs()
     algo_bytes = 60.0 * R + 64.0 * (N - 1)  # 24 B ray in + 36 B Raycast out, node set once
     achieved = algo_bytes / (step_ms * 1e-3) / 1e9
-    traffic = None  # dram__bytes_read + dram__bytes_write of one launch of this kernel on this workload, from the committed ncu capture
+    # dram__bytes_read + dram__bytes_write of ONE launch of this kernel on this workload, from the committed ncu capture of THIS
+    # build (tools/capture_traffic.sh writes the file with the hash of the CUDA sources); null when the sources have changed since
+    traffic, traffic_note = None, "no ncu capture of this build committed"
     try:
-        tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_d_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         if (tr["workload"], tr["colliders"], tr["rays"]) == (args.workload, N, R):
-            traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+            if tr.get("source_hash") == source_hash():
+                traffic, traffic_note = tr["dram_bytes_read"] + tr["dram_bytes_write"], f"ncu --set full capture of this build ({tr['source_hash']}), profiles/{tr.get('report', 'r2_traffic.json')}"
+            else:
+                traffic_note = f"the committed capture belongs to build {tr.get('source_hash')}, this is {source_hash()}: dropped"
     except (OSError, KeyError, ValueError):
         pass
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
                 "algorithmic_bytes": algo_bytes,
                 "kernel": "k_trace_lbvh", "peak_source": peak_src,
                 "note": "primary figure = compulsory stream bytes only; traversal at 1M AABBs is L2/latency-bound, not HBM-bound (SURVEY.md 8(d))"}
@@ -384,6 +520,14 @@ def run_ours(args):
                            "l2_to_sm_gbs": visits * 32.0 / (step_ms * 1e-3) / 1e9,
                            "peak_source": "measured gather rate of an L2-resident table, tools/micro/gather_bench.cu (0.99); stack and ray traffic in shared memory share the pipe"}
 
+    extras = {}
+    if world == 1 and not args.no_extras:
+        del d_rays, d_out, h_rays, h_out
+        torch.cuda.empty_cache()
+        from tools import bench_extras
+
+        extras = bench_extras.run_all(cs, args, torch)
+
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         arm = CpuArm(scene)
@@ -401,15 +545,22 @@ def run_ours(args):
 
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
-    print(json.dumps({
+    line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": R * 24, "d2h_bytes_per_step": R * 36, "ms_per_step": e2e_ms,
-                "matches_device_path": same},
+                "matches_device_path": same, "checked": "every byte of the batch"},
         "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks,
-        "rebuild": rebuild, "bvh_broadcast_ms": bcast_ms, "hits_gather_ms": gather_ms, "numa_cpulist_rank0": numa, "hit_fraction": hits / R, "wall_ms_timed_region": wall_ms,
-    }))
+        "rebuild": rebuild, "numa_cpulist_rank0": numa, "hit_fraction": hits / R, "wall_ms_timed_region": wall_ms,
+    }
+    if multi:
+        line["multi_gpu"] = multi
+        line["value_with_gather"] = multi["value_with_gather"]
+        line["bvh_broadcast_ms"] = multi["bvh_broadcast_ms"]
+    line.update(extras)
+    print(json.dumps(line))
     if world > 1:
+        cs.comm_finalize()
         dist.destroy_process_group()
 
 
@@ -422,6 +573,7 @@ def main():
     ap.add_argument("--colliders", type=int, default=1_000_000)
     ap.add_argument("--rays", type=int, default=16 * 1024 * 1024, help="rays per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra 1-GPU records (config 4 dynamic frames, config 5 aimed rays, update through the drop-in)")
     ap.add_argument("--workload", default="config3", choices=["config3", "config5"], help="config3: uniform 1M (the headline); config5: clustered (use --colliders 10000000)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -10,7 +10,9 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B2COL_LIB") or os.path.join(HERE, "libb2col.so")  # B2COL_LIB: dev override (kernel variants)
 
-OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_OVERFLOW = range(7)
+OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_OVERFLOW, ERR_COMM = range(8)
+COMM_ID_BYTES = 128
+GATHER_NONE, GATHER_PEER_WINDOW, GATHER_PEER_WINDOW_IPC, GATHER_NCCL_SENDRECV = range(4)
 MODE_LBVH, MODE_REFTOPO, MODE_LBVH_COUNT = 0, 1, 2
 
 # PODs — byte-identical to the reference's (include/system_collisions.h:13-24,40-48)
@@ -38,13 +40,21 @@ class Stats(C.Structure):
     ]
 
 
+class CommInfo(C.Structure):
+    _fields_ = [("n_ranks", C.c_int), ("rank", C.c_int), ("single_process", C.c_int), ("gather_mode", C.c_int), ("nccl_version", C.c_int),
+                ("window_bytes", C.c_uint64), ("gathers", C.c_uint64), ("replications", C.c_uint64)]
+
+
 # every symbol include/b2col.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "b2col_abi_version", "b2col_create", "b2col_destroy", "b2col_last_error", "b2col_sync", "b2col_stream",
     "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_set_world_matrices", "b2col_set_colliders",
     "b2col_update", "b2col_propagate", "b2col_refit", "b2col_raycast_batch", "b2col_raycast_device", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
-    "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats", "b2col_get_trace_counters",
+    "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats", "b2col_get_trace_counters", "b2col_read_device",
     "b2col_bvh_blob", "b2col_bvh_export_blob", "b2col_bvh_import_blob", "b2col_event_record", "b2col_event_elapsed_ms",
+    "b2col_shard_bounds", "b2col_comm_get_unique_id", "b2col_comm_init_rank", "b2col_comm_init_all", "b2col_comm_finalize",
+    "b2col_comm_replicate", "b2col_comm_replicate_all", "b2col_comm_replicate_records", "b2col_comm_raycast_gather",
+    "b2col_comm_raycast_gather_all", "b2col_mgpu_raycast_batch", "b2col_comm_info",
 ]
 
 
@@ -91,10 +101,24 @@ def load() -> C.CDLL:
     lib.b2col_get_world_aabbs.argtypes = [vp, vp]
     lib.b2col_get_leaf_order.argtypes = [vp, vp]
     lib.b2col_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    lib.b2col_read_device.argtypes = [vp, vp, sz, vp]
     lib.b2col_get_trace_counters.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b2col_bvh_blob.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     lib.b2col_bvh_import_blob.argtypes = [vp, vp, sz]
     lib.b2col_bvh_export_blob.argtypes = [vp, vp, sz]
+    lib.b2col_shard_bounds.argtypes = [sz, C.c_int, C.c_int, C.POINTER(sz), C.POINTER(sz)]
+    lib.b2col_shard_bounds.restype = None
+    lib.b2col_comm_get_unique_id.argtypes = [vp]
+    lib.b2col_comm_init_rank.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.b2col_comm_init_all.argtypes = [C.POINTER(vp), C.c_int]
+    lib.b2col_comm_finalize.argtypes = [vp]
+    lib.b2col_comm_replicate.argtypes = [vp, C.c_int, u32]
+    lib.b2col_comm_replicate_all.argtypes = [C.POINTER(vp), C.c_int, C.c_int]
+    lib.b2col_comm_replicate_records.argtypes = [vp, C.c_int, u32]
+    lib.b2col_comm_raycast_gather.argtypes = [vp, vp, sz, C.c_int, C.POINTER(vp)]
+    lib.b2col_comm_raycast_gather_all.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), sz, C.c_int, C.POINTER(vp)]
+    lib.b2col_mgpu_raycast_batch.argtypes = [C.POINTER(vp), C.c_int, vp, sz, vp, C.c_int]
+    lib.b2col_comm_info.argtypes = [vp, C.POINTER(CommInfo)]
     lib.b2col_event_record.argtypes = [vp, C.c_int]
     lib.b2col_event_elapsed_ms.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
     _lib = lib

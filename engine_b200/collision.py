@@ -162,6 +162,12 @@ class CollisionSystem:
         self._ck(self.lib.b2col_get_world_aabbs(self.h, ptr(out)))
         return out
 
+    def read_raycasts(self, d_addr: int, n: int) -> np.ndarray:
+        """n Raycasts from device memory of this context (e.g. the gathered array of comm_raycast_gather), after everything enqueued"""
+        out = np.empty(n, RAYCAST_DTYPE)
+        self._ck(self.lib.b2col_read_device(self.h, C.c_void_p(d_addr), n * RAYCAST_DTYPE.itemsize, ptr(out)))
+        return out
+
     def leaf_order(self) -> np.ndarray:
         out = np.empty(self.n_colliders, np.uint32)
         self._ck(self.lib.b2col_get_leaf_order(self.h, ptr(out)))
@@ -180,7 +186,44 @@ class CollisionSystem:
         self._ck(self.lib.b2col_get_trace_counters(self.h, C.byref(v), C.byref(r)))
         return {"node_visits": int(v.value), "rays": int(r.value)}
 
-    # -- multi-GPU -----------------------------------------------------------------------------
+    # -- multi-GPU (include/b2col.h "multi-GPU"; NCCL is called from C++ inside libb2col.so) ------
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """ncclGetUniqueId (rank 0 calls it; distribute the 128 bytes by any means)"""
+        lib = capi.load()
+        buf = C.create_string_buffer(capi.COMM_ID_BYTES)
+        st = lib.b2col_comm_get_unique_id(buf)
+        if st != capi.OK:
+            raise B2ColError(st, (lib.b2col_last_error(None) or b"").decode())
+        return buf.raw
+
+    def comm_init_rank(self, n_ranks: int, rank: int, unique_id: bytes) -> None:
+        assert len(unique_id) == capi.COMM_ID_BYTES
+        self._ck(self.lib.b2col_comm_init_rank(self.h, n_ranks, rank, C.c_char_p(unique_id)))
+
+    def comm_finalize(self) -> None:
+        self._ck(self.lib.b2col_comm_finalize(self.h))
+
+    def comm_replicate(self, src_rank: int, n_colliders: int) -> None:
+        """collective: one ncclBroadcast of rank src's BVH blob into every rank's blob allocation (enqueued)"""
+        self._ck(self.lib.b2col_comm_replicate(self.h, src_rank, n_colliders))
+
+    def comm_replicate_records(self, src_rank: int, n_colliders: int) -> None:
+        """collective: broadcast the 32-byte world records instead and build the (identical) tree on every rank"""
+        self._ck(self.lib.b2col_comm_replicate_records(self.h, src_rank, n_colliders))
+
+    def comm_raycast_gather(self, d_rays_shard, n_total: int, dst_rank: int = 0) -> int:
+        """collective: trace this rank's slice of an n_total-ray batch; the Raycasts of the whole batch land in batch order on
+        dst_rank.  Returns the device address of the gathered array on dst_rank, 0 elsewhere.  Enqueued."""
+        out = C.c_void_p()
+        self._ck(self.lib.b2col_comm_raycast_gather(self.h, ptr(d_rays_shard), n_total, dst_rank, C.byref(out)))
+        return int(out.value or 0)
+
+    def comm_info(self) -> dict:
+        ci = capi.CommInfo()
+        self._ck(self.lib.b2col_comm_info(self.h, C.byref(ci)))
+        return {k: getattr(ci, k) for k, _ in capi.CommInfo._fields_}
+
     def bvh_blob(self) -> tuple[int, int]:
         p, n = C.c_void_p(), C.c_size_t()
         self._ck(self.lib.b2col_bvh_blob(self.h, C.byref(p), C.byref(n)))
@@ -200,3 +243,52 @@ class CollisionSystem:
         ms = C.c_float()
         self._ck(self.lib.b2col_event_elapsed_ms(self.h, a, b, C.byref(ms)))
         return float(ms.value)
+
+
+def shard_bounds(n: int, n_ranks: int, rank: int) -> tuple[int, int]:
+    """b2col_shard_bounds: rank's contiguous slice [lo, hi) of an n-element batch"""
+    lo, hi = C.c_size_t(), C.c_size_t()
+    capi.load().b2col_shard_bounds(n, n_ranks, rank, C.byref(lo), C.byref(hi))
+    return int(lo.value), int(hi.value)
+
+
+class MultiGpu:
+    """Several GPUs driven by ONE process (how a game engine would use the backend; engine_b200/shim does the same in
+    C++): context 0 owns the scene and builds, the others hold replicas.  b2col_comm_init_all / _replicate_all /
+    _raycast_gather_all / b2col_mgpu_raycast_batch."""
+
+    def __init__(self, devices, **kw):
+        self.systems = [CollisionSystem(device=d, **kw) for d in devices]
+        self.lib = self.systems[0].lib
+        self._arr = (C.c_void_p * len(self.systems))(*[cs.h for cs in self.systems])
+        self.primary._ck(self.lib.b2col_comm_init_all(self._arr, len(self.systems)))
+
+    @property
+    def primary(self) -> CollisionSystem:
+        return self.systems[0]
+
+    def replicate(self, src: int = 0) -> None:
+        self.primary._ck(self.lib.b2col_comm_replicate_all(self._arr, len(self.systems), src))
+
+    def raycast_gather(self, d_rays_shards, n_total: int, dst: int = 0) -> int:
+        """d_rays_shards[i]: device tensor / address of rank i's slice (on device i). Returns the device address (on dst) of the
+        gathered Raycasts; enqueued — sync the dst system before reading."""
+        shards = (C.c_void_p * len(self.systems))(*[ptr(t) for t in d_rays_shards])
+        out = C.c_void_p()
+        self.primary._ck(self.lib.b2col_comm_raycast_gather_all(self._arr, len(self.systems), shards, n_total, dst, C.byref(out)))
+        return int(out.value or 0)
+
+    def get_raycasts(self, rays, out: np.ndarray | None = None) -> np.ndarray:
+        rays = _rays(rays)
+        n = rays.shape[0]
+        if out is None:
+            out = np.empty(n, RAYCAST_DTYPE)
+        self.primary._ck(self.lib.b2col_mgpu_raycast_batch(self._arr, len(self.systems), ptr(rays), n, ptr(out), MODE_LBVH))
+        return out
+
+    def raycast_host_pinned(self, h_rays, n: int, h_out) -> None:
+        self.primary._ck(self.lib.b2col_mgpu_raycast_batch(self._arr, len(self.systems), ptr(h_rays), n, ptr(h_out), MODE_LBVH))
+
+    def close(self) -> None:
+        for cs in self.systems:
+            cs.close()

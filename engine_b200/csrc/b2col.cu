@@ -145,7 +145,8 @@ struct BlobHeader {
     Grid grid;                   // quantisation grid of the traversal nodes (written by k_morton)
     uint32_t trace_root;         // where k_trace_lbvh starts: `root`, or the compact copy of the root (k_top_layout)
     uint32_t top_count;          // nodes in the compact copy of the top levels behind the leaf records (0: none)
-    uint32_t reserved[37];
+    uint32_t has_wild;           // 1: some leaf box cannot be bounded on the grid (NaN / inf / > 1e37: WILD_BIT slots in the tree)
+    uint32_t reserved[36];
 };
 static_assert(sizeof(BlobHeader) == 256, "blob header");
 constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
@@ -220,15 +221,15 @@ __device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const flo
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float ctr = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
-        if (isfinite(ctr)) {
+        if (grid_coord_ok(ctr)) {  // NaN, +-inf and |x| > 1e37 stay out of the grids (such boxes become wild leaves)
             cmin[k] = ctr;
             cmax[k] = ctr;
         }
-        if (isfinite(b.lo[k])) {
+        if (grid_coord_ok(b.lo[k])) {
             cmin[3 + k] = b.lo[k];
             cmax[3 + k] = b.lo[k];
         }
-        if (isfinite(b.hi[k])) {
+        if (grid_coord_ok(b.hi[k])) {
             cmin[3 + k] = fminf(cmin[3 + k], b.hi[k]);
             cmax[3 + k] = fmaxf(cmax[3 + k], b.hi[k]);
         }
@@ -435,6 +436,20 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
     if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, bounds, n, T);
 }
 
+// b2col_comm_replicate_records: the scene bounds a replica needs for its Morton / quantisation grids arrive inside the
+// source rank's blob header; this puts them where k_morton reads them.
+__global__ void k_bounds_from_header(const BlobHeader* hdr, uint32_t* bounds)
+{
+    pdl_wait();
+    const int k = threadIdx.x;
+    if (k < 3) {
+        bounds[k] = hdr->bounds_min_inv[k];
+        bounds[3 + k] = hdr->bounds_max[k];
+        bounds[6 + k] = hdr->box_min_inv[k];
+        bounds[9 + k] = hdr->box_max[k];
+    }
+}
+
 // Refit-only frames (b2col_refit) skip k_morton: this fills the header fields k_morton would have written,
 // from the bounds k_refit has just reduced.
 __global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T)
@@ -483,10 +498,12 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     box.w[0] = box.w[1] = box.w[2] = 0u;
     uint64_t key = 0ull;
     uint32_t lev_l = LEVEL_END;
+    bool wild = false;  // this subtree holds a leaf the grid cannot bound (b2col_bvh.cuh, WILD_BIT)
     if (valid) {
         const LeafRec rec = DevOps::load_leaf(&world_rec[sorted_prim[i]]);  // one 256-bit load: the world record IS the leaf record
         DevOps::store_leaf(&leaves[i], rec);
         box = quantise_box(rec.lo, rec.hi, grid);
+        wild = box_is_wild(rec.lo, rec.hi);
         key = keys[i];
         if (i > 0u) lev_l = split_level(keys[i - 1u], key, i - 1u);
     }
@@ -495,12 +512,13 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
             QNode nd;
 #pragma unroll
             for (int k = 0; k < 3; ++k) nd.w[k] = nd.w[3 + k] = box.w[k];
-            nd.w[6] = LEAF_BIT | 0u;
-            nd.w[7] = LEAF_BIT | 0u;
+            nd.w[6] = LEAF_BIT | (wild ? WILD_BIT : 0u) | 0u;
+            nd.w[7] = nd.w[6];
             DevOps::store_qnode(&qnodes[0], nd);
             hdr->root = 0u;
             hdr->trace_root = 0u;
             hdr->top_count = 0u;
+            hdr->has_wild = wild ? 1u : 0u;
         }
         return;
     }
@@ -551,8 +569,9 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         const bool local = j <= (uint32_t)BUILD_BLOCK && s_local[j] != 0;
         QBox sib;
         uint32_t bound, level;
-        DevOps::store_ref(&qnodes[p], is_left ? 0 : 1, ref);
-        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r);
+        bool sib_wild;
+        DevOps::store_ref(&qnodes[p], is_left ? 0 : 1, ref | (wild ? WILD_BIT : 0u));
+        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r, wild);
         Xch got;
         if (local) {  // same 128-bit exchange, in shared memory (ATOMS.EXCH.128): the message is the atomic's operand, no fences
             got = DevOps::exchange_shared(&s_xch[j], mine);
@@ -563,7 +582,8 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
             if (got.w[3] == UNVISITED) return;
             *reinterpret_cast<uint4*>(&xch[p]) = make_uint4(0u, 0u, 0u, UNVISITED);  // self-cleaning: ready for the next frame
         }
-        xch_unpack(got, sib, bound, level);
+        xch_unpack(got, sib, bound, level, sib_wild);
+        wild = wild || sib_wild;
         DevOps::store_qboxes(&qnodes[p], is_left ? box.w : sib.w, is_left ? sib.w : box.w);
         if (is_left) {
             r = bound;
@@ -580,6 +600,7 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
             hdr->root = p;
             hdr->trace_root = p;  // k_top_layout, when it runs, redirects the traversal to its compact copy
             hdr->top_count = 0u;
+            hdr->has_wild = wild ? 1u : 0u;
             return;
         }
     }
@@ -665,13 +686,13 @@ k_top_layout(BlobHeader* hdr, const QNode* qnodes, QNode* top, uint32_t top_base
                 if (first + j < count) {
                     if (!last) {
                         if (!(nd[j].w[6] & LEAF_BIT)) {
-                            next_f[pre] = nd[j].w[6];
-                            nd[j].w[6] = top_base + next + pre;
+                            next_f[pre] = nd[j].w[6] & REF_INDEX_MASK;
+                            nd[j].w[6] = (nd[j].w[6] & WILD_BIT) | (top_base + next + pre);
                             ++pre;
                         }
                         if (!(nd[j].w[7] & LEAF_BIT)) {
-                            next_f[pre] = nd[j].w[7];
-                            nd[j].w[7] = top_base + next + pre;
+                            next_f[pre] = nd[j].w[7] & REF_INDEX_MASK;
+                            nd[j].w[7] = (nd[j].w[7] & WILD_BIT) | (top_base + next + pre);
                             ++pre;
                         }
                     }
@@ -732,11 +753,23 @@ static_assert(TRACE_SMEM_STACK % 2 == 0 && TRACE_SMEM_STACK >= 4, "spill granula
 
 // Shared memory of one trace block.  Everything is laid out [row][thread], so lane l always hits bank
 // l whatever row it addresses: every access is one conflict-free wavefront.
+#ifndef B2_STAGE_RAYS
+#define B2_STAGE_RAYS 12
+#endif
+constexpr int STAGE_RAYS = B2_STAGE_RAYS;  // finished Raycasts a warp stages per round on their way out (flush_finished)
+constexpr int STAGE_WORDS = 11;            // per staged ray: the nine words of the Raycast + its 64-bit index in the batch
 struct TraceSmem {
     uint32_t node[TRACE_SMEM_STACK][TRACE_BLOCK];  // deferred far children ...
     float t[TRACE_SMEM_STACK][TRACE_BLOCK];        // ... and their entry tmin
     float ray[9][TRACE_BLOCK];                     // the lane's exact ray: origin, normalised direction, reciprocals
+    uint32_t stage[TRACE_BLOCK / 32][STAGE_RAYS * STAGE_WORDS];
 };
+// 10 blocks per SM must fit the 196 KB shared-memory carve-out (10 x (18 912 + 1 024 reserved) = 199 360 <= 200 704): with the
+// 228 KB carve-out only 28 KB of L1 remain for the node gathers and the kernel loses 30 % (measured, profiles/r2_experiments.txt:
+// 32 staged rays per warp, 21.5 KB per block: 1867 -> 1300 Mrays/s)
+#ifndef B2_ALLOW_BIG_SMEM  // dev variants only
+static_assert((sizeof(TraceSmem) + 1024) * B2_TRACE_MIN_BLOCKS <= 196 * 1024, "trace blocks per SM no longer fit the 196 KB shared-memory carve-out");
+#endif
 
 // Overflow of the shared-memory stack (a lane more than TRACE_SMEM_STACK deferred children deep — rare):
 // the older half moves to a local-memory array and comes back when the shared part runs empty.  Total depth
@@ -762,6 +795,53 @@ __device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t*
     return lsp;  // sp = TRACE_SPILL in the caller
 }
 
+// Epilogue of the lanes whose ray has finished (`pending`), warp-cooperative.  A Raycast is 36 bytes at a 36-byte
+// stride: written by its own lane it costs nine 4-byte stores per lane, each instruction touching one sector per ray —
+// 7 % of the kernel's L1 wavefronts (ncu, profiles/r1_e) and, when `out` is a peer GPU's memory (b2col_comm_raycast_gather),
+// nine NVLink write packets of 4 bytes per ray.  Instead every finished lane packs its nine words into the warp's staging
+// rows, ray after ray (stride 9 words: conflict-free), and the warp writes the staged words out 32 at a time — each
+// instruction covers ~3.5 whole Raycasts, contiguous 36-byte runs in global memory.  The staging area holds STAGE_RAYS rays
+// per warp (shared memory is what limits the kernel's occupancy); more finished lanes than that take another round.
+__device__ __forceinline__ void flush_finished(TraceSmem& sm, int warp, int lane, uint32_t lt_mask, bool pending, const uint32_t* w9, unsigned long long my,
+                                               b2col_raycast* __restrict__ out)
+{
+#ifdef B2_NO_STAGE  // dev variant (A/B timing): every lane writes its own Raycast, nine 4-byte stores at a 36-byte stride
+    if (pending) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) reinterpret_cast<uint32_t*>(out)[9ull * my + k] = w9[k];
+    }
+    return;
+#endif
+    unsigned pend = __ballot_sync(0xffffffffu, pending);
+    if (pend == 0u) return;
+    uint32_t* st = sm.stage[warp];
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(out);
+    int j = pending ? __popc(pend & lt_mask) : -1;  // this lane's place among the finished rays
+    int left = __popc(pend);
+    for (;;) {  // rounds of at most STAGE_RAYS rays (usually one: 7-12 lanes finish per fetch)
+        const int round = min(left, STAGE_RAYS);
+        if (j >= 0 && j < round) {  // 11 words per ray: the Raycast and where it goes (stride 11: conflict-free)
+            uint32_t* p = st + STAGE_WORDS * j;
+#pragma unroll
+            for (int k = 0; k < 9; ++k) p[k] = w9[k];
+            p[9] = (uint32_t)my;
+            p[10] = (uint32_t)(my >> 32);
+        }
+        __syncwarp();
+        const int total = 9 * round;
+        for (int e = lane; e < total; e += 32) {
+            const int r = (e * 7282) >> 16;  // e / 9 for e < 288
+            const uint32_t* p = st + STAGE_WORDS * r;
+            const unsigned long long m = (unsigned long long)p[9] | ((unsigned long long)p[10] << 32);
+            o32[9ull * m + (unsigned)(e - 9 * r)] = p[e - 9 * r];
+        }
+        __syncwarp();  // the staging rows are reused by the next round / flush
+        left -= round;
+        if (left <= 0) break;
+        j -= round;
+    }
+}
+
 // GetRaycast (reference src/system_collisions.cpp:160-199) over a batch, production tree.
 //
 // Persistent warps with dynamic ray fetch: incoherent rays finish after wildly different numbers of
@@ -781,15 +861,16 @@ __device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t*
 // the exact leaf tests and the epilogue.
 // COUNT (B2COL_MODE_LBVH_COUNT, a diagnostic instantiation): also adds the number of node visits to counter[1] — what
 // bench.py turns into the L1 wavefront rate, the resource that actually binds this kernel.
-template <bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
-k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
-             const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
-             unsigned long long* counter, int fetch_threshold)
+// WILD: the tree holds leaves the grid cannot bound (hdr->has_wild; b2col_bvh.cuh WILD_BIT): flagged slots are always
+// entered and no ray is dismissed by its distance from the grid.  Chosen once per kernel, so that sane scenes run the
+// instantiation that never looks at the bit.
+template <bool COUNT, bool WILD>
+__device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
+                                           const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
+                                           unsigned long long* counter, int fetch_threshold)
 {
-    __shared__ TraceSmem sm;
     const int tid = threadIdx.x;
-    const int lane = tid & 31;
+    const int lane = tid & 31, warp = tid >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t root = hdr->trace_root;
     const Grid grid = hdr->grid;
@@ -821,8 +902,10 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
     for (;;) {
         // Epilogues are deferred to this point so that the lanes that finished since the last fetch
         // run them together instead of one at a time inside the traversal loop.
-        if (pending) {
-            finish_raycast<DevOps>(reinterpret_cast<uint32_t*>(out + my), exact_ray(), best, leaves);
+        {
+            uint32_t w9[9];
+            if (pending) finish_raycast<DevOps>(w9, exact_ray(), best, leaves);
+            flush_finished(sm, warp, lane, lt_mask, pending, w9, my, out);
             pending = false;
         }
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -836,7 +919,7 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
                 my = base + (unsigned long long)__popc(need & lt_mask);
                 if (my < n_rays) {
                     const RayPre r = load_ray(rays, my);
-                    if (rayq_prepare(r, grid, q)) {
+                    if (rayq_prepare(r, grid, q) || WILD) {
 #pragma unroll
                         for (int k = 0; k < 3; ++k) {
                             sm.ray[k][tid] = r.o[k];
@@ -879,7 +962,7 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
                 if (cur != REF_EMPTY) {
                     if (COUNT) ++visits;
                     const QNode nd = DevOps::load_qnode(&qnodes[cur]);
-                    const VisitOut v = visit_node<DevOps>(best, lim, q, nd, leaves, T, exact_ray);
+                    const VisitOut v = visit_node<DevOps, WILD>(best, lim, q, nd, leaves, T, exact_ray);
                     if (v.push) {
                         sm.node[sp][tid] = v.far;
                         sm.t[sp][tid] = v.tfar;
@@ -904,6 +987,17 @@ k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2co
         for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
         if (lane == 0 && visits) atomicAdd(counter + 1, visits);
     }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
+k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
+             const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
+             unsigned long long* counter, int fetch_threshold)
+{
+    __shared__ TraceSmem sm;
+    if (hdr->has_wild) trace_body<COUNT, true>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
+    else trace_body<COUNT, false>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
 }
 
 // Same query, walking an uploaded reference-format tree with the reference's exact semantics.
@@ -960,8 +1054,18 @@ thread_local std::string g_create_error;
 
 }  // namespace
 
+struct b2col_comm_state;  // b2col_comm.inl
+
 struct b2col_ctx {
     int device = 0;
+    b2col_comm_state* comm = nullptr;  // multi-GPU: communicator, gather window (b2col_comm_*)
+    // a host-buffer batch whose work is enqueued but not yet waited for (raycast_batch_begin / _end)
+    struct PendingBatch {
+        bool active = false, pipeline = false, timed = false, has_dev_out = false;
+        int d2h = 0, mode = 0;
+        size_t n = 0;
+        std::chrono::steady_clock::time_point t_begin;
+    } pending;
     cudaStream_t stream = nullptr;
     b2col_config cfg{};
     float T = 1000.0f;
@@ -1046,6 +1150,9 @@ struct b2col_ctx {
     bool no_small_path = false;  // dev: B2COL_NO_SMALL=1 sends few-ray calls through the copy path (A/B timing)
     bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
     bool phase_timing = false;
+    void* h_import_hdr = nullptr;  // page-locked copy of the header of the last imported blob, checked by b2col_sync
+    bool import_check_pending = false;
+    uint32_t import_check_leaves = 0;
     cudaEvent_t phase_ev[16] = {};
     int n_phase = 0;
 };
@@ -1136,6 +1243,7 @@ size_t blob_size_for(uint32_t n_leaves)
     return sizeof(BlobHeader) + n_nodes * sizeof(QNode) + (size_t)n_leaves * sizeof(LeafRec) + top_cap_for(n_leaves) * sizeof(QNode);
 }
 inline BlobHeader* blob_hdr(const b2col_ctx* c) { return c->d_blob.as<BlobHeader>(); }
+inline BlobHeader* blob_hdr_n(const b2col_ctx* c) { return c->d_blob.as<BlobHeader>(); }
 inline QNode* blob_qnodes(const b2col_ctx* c) { return reinterpret_cast<QNode*>(static_cast<char*>(c->d_blob.p) + sizeof(BlobHeader)); }
 inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
 {
@@ -1267,6 +1375,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
 void b2col_destroy(b2col_ctx* ctx)
 {
     if (!ctx) return;
+    b2col_comm_finalize(ctx);
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
@@ -1276,6 +1385,7 @@ void b2col_destroy(b2col_ctx* ctx)
     for (auto& g : ctx->graphs)
         if (g.exec) cudaGraphExecDestroy(g.exec);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    if (ctx->h_import_hdr) cudaFreeHost(ctx->h_import_hdr);
     release(ctx->d_small_counters);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
@@ -1293,6 +1403,15 @@ b2col_status b2col_sync(b2col_ctx* ctx)
     if (!ctx) return B2COL_ERR_INVALID;
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->import_check_pending) {  // header of the last imported blob (b2col_bvh_import_blob), now on the host
+        ctx->import_check_pending = false;
+        const BlobHeader* h = static_cast<const BlobHeader*>(ctx->h_import_hdr);
+        const bool empty = h->magic == 0u && h->n_leaves == 0u && ctx->import_check_leaves == 0u;
+        if (!empty && (h->magic != BLOB_MAGIC || h->n_leaves != ctx->import_check_leaves)) {
+            ctx->have_tree = false;
+            return fail(ctx, B2COL_ERR_INVALID, "imported blob rejected: magic %08x, %u leaves in the header, %u by its size", h->magic, h->n_leaves, ctx->import_check_leaves);
+        }
+    }
     return B2COL_OK;
 }
 
@@ -1383,7 +1502,7 @@ b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const
 b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_entity, const b2col_aabb* h_local)
 {
     if (!ctx || (n && (!h_entity || !h_local))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
-    if (n >= 0x7fffffffu) return fail(ctx, B2COL_ERR_INVALID, "too many colliders");
+    if (n >= (1u << 29)) return fail(ctx, B2COL_ERR_INVALID, "too many colliders (child refs hold 30-bit indices)");
     CU(cudaSetDevice(ctx->device));
     uint32_t max_e = 0;
     for (uint32_t i = 0; i < n; ++i) {
@@ -1521,10 +1640,13 @@ inline size_t lookback_words_per_pass(uint32_t tiles) { return ((size_t)tiles + 
 // The frame's kernels, nothing else (no allocation, no memset, no synchronisation): capturable.
 //   full:  [propagate+refit per level | propagate per level, refit] , Morton, radix passes, hierarchy
 //   !full: [ ... same transform/refit ... ], header, hierarchy on the sorted keys of the last full build
-b2col_status enqueue_frame(b2col_ctx* ctx, bool full)
+b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
 {
-    const uint32_t n = ctx->n_colliders;
-    GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
+    // n_records != 0: the world records (and the scene bounds, in the blob header) were received from another rank
+    // (b2col_comm_replicate_records): Morton + sort + hierarchy only
+    const uint32_t n = n_records ? n_records : ctx->n_colliders;
+    if (n_records) LAUNCH_FRAME(ctx, k_bounds_from_header, 1, 32, 0, (const BlobHeader*)blob_hdr_n(ctx), scratch_bounds(ctx));
+    else GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
     if (!full) {
         LAUNCH_FRAME(ctx, k_header, 1, 1, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
         GUARD(launch_build(ctx, n, ctx->sorted_side));
@@ -1623,32 +1745,9 @@ b2col_status run_frame(b2col_ctx* ctx, bool full)
 
 }  // namespace
 
-b2col_status b2col_update(b2col_ctx* ctx)
+// buffers, key width and scratch of a full build of n colliders (everything but the blob, which the callers size first)
+static b2col_status prepare_build_inner(b2col_ctx* ctx, uint32_t n)
 {
-    if (!ctx) return B2COL_ERR_INVALID;
-    if (!ctx->have_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_set_colliders has not been called");
-    if (!ctx->world_external && !(ctx->have_hierarchy && ctx->have_trs))
-        return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
-    CU(cudaSetDevice(ctx->device));
-    const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
-    ctx->n_phase = 0;
-    PHASE(ctx);  // 0: start
-
-    // ---- allocate the frame's buffers -----------------------------------------------------------
-    const size_t blob_bytes = blob_size_for(n);
-    GUARD(ensure(ctx, ctx->d_blob, blob_bytes));
-    ctx->blob_bytes = blob_bytes;
-    ctx->tree_leaves = n;
-    ctx->topology_valid = false;
-    if (n == 0) {
-        if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));  // world matrices are still the caller's to read back
-        CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
-        ctx->have_tree = true;  // empty tree: header says n_leaves = 0, every query misses
-        ctx->topology_valid = true;
-        return B2COL_OK;
-    }
-    if (ctx->max_col_entity > E)
-        return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, E);
     GUARD(ensure(ctx, ctx->d_world_aabb, (size_t)n * sizeof(LeafRec)));  // 32-byte records {world AABB, entity, collider index}
     GUARD(ensure(ctx, ctx->d_keys[0], (size_t)n * 8));
     GUARD(ensure(ctx, ctx->d_keys[1], (size_t)n * 8));
@@ -1659,7 +1758,6 @@ b2col_status b2col_update(b2col_ctx* ctx)
         CU(cudaMemsetAsync(ctx->d_xch.p, 0xFF, ctx->d_xch.cap, ctx->stream));
         ctx->xch_ready = ctx->d_xch.p;
     }
-    ctx->exact_nodes_valid = false;
     // Morton key width: the radix sort costs one pass per 8 key bits, and at ~1M colliders each pass is
     // latency-bound (~20 us), so the key is only as wide as the collider count needs: 32 bits (11,11,10 per
     // axis, 4.3e9 cells) up to 2M colliders, 40 bits up to 32M, 48 beyond; an explicit
@@ -1677,10 +1775,72 @@ b2col_status b2col_update(b2col_ctx* ctx)
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     GUARD(prepare_scratch(ctx, (SCRATCH_BOUNDS_WORDS + (size_t)RS_MAX_PASSES * RS_RADIX + 16 + (size_t)ctx->passes * lb_words_per_pass) * 4));
+    return B2COL_OK;
+}
+static b2col_status prepare_build(b2col_ctx* ctx, uint32_t n)
+{
+    const void* before[3] = {ctx->d_world_aabb.p, ctx->d_keys[0].p, ctx->d_vals[0].p};
+    const void* before2[2] = {ctx->d_keys[1].p, ctx->d_vals[1].p};
+    const b2col_status st = prepare_build_inner(ctx, n);
+    if (before[0] != ctx->d_world_aabb.p || before[1] != ctx->d_keys[0].p || before[2] != ctx->d_vals[0].p || before2[0] != ctx->d_keys[1].p ||
+        before2[1] != ctx->d_vals[1].p) {  // the sorted keys / world records of the last build are gone: no refit, no export of the old tree
+        ctx->topology_valid = false;
+        ctx->exact_nodes_valid = false;
+    }
+    return st;
+}
+
+b2col_status b2col_update(b2col_ctx* ctx)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (!ctx->have_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_set_colliders has not been called");
+    if (!ctx->world_external && !(ctx->have_hierarchy && ctx->have_trs))
+        return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs, or b2col_set_world_matrices");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t E = ctx->n_entities, n = ctx->n_colliders;
+    ctx->n_phase = 0;
+    PHASE(ctx);  // 0: start
+
+    // ---- validate, then allocate the frame's buffers.  Nothing that describes the CURRENT tree (have_tree, tree_leaves,
+    // blob_bytes, topology_valid) changes before the new frame is enqueued, except where an allocation has already
+    // destroyed the old tree: a failed update leaves the previous tree answering queries, or none at all — never a
+    // half-described one.
+    if (n != 0 && ctx->max_col_entity > E)
+        return fail(ctx, B2COL_ERR_INVALID, "a collider refers to entity %u but only %u entities have transforms", ctx->max_col_entity, E);
+    const size_t blob_bytes = blob_size_for(n);
+    {
+        const void* before = ctx->d_blob.p;
+        const b2col_status st = ensure(ctx, ctx->d_blob, blob_bytes);
+        if (ctx->d_blob.p != before || st != B2COL_OK) {  // the old blob is gone (ensure frees before it allocates)
+            ctx->have_tree = false;
+            ctx->topology_valid = false;
+            ctx->exact_nodes_valid = false;
+            ctx->tree_leaves = 0;
+        }
+        GUARD(st);
+    }
+    if (n == 0) {
+        if (!ctx->world_external && !ctx->world_fresh) GUARD(enqueue_propagate(ctx));  // world matrices are still the caller's to read back
+        ctx->have_tree = false;
+        CU(cudaMemsetAsync(ctx->d_blob.p, 0, sizeof(BlobHeader), ctx->stream));
+        ctx->blob_bytes = blob_bytes;
+        ctx->tree_leaves = 0;
+        ctx->have_tree = true;  // empty tree: header says n_leaves = 0, every query misses
+        ctx->topology_valid = true;
+        ctx->exact_nodes_valid = false;
+        return B2COL_OK;
+    }
+    GUARD(prepare_build(ctx, n));
     if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
     if (!ctx->world_external) GUARD(ensure(ctx, ctx->d_world, ((size_t)E + 1) * 64));
     PHASE(ctx);  // 1: set-up
+    // from here on the blob is being overwritten: until the frame is enqueued in full there is no tree
+    ctx->have_tree = false;
+    ctx->topology_valid = false;
+    ctx->exact_nodes_valid = false;
     GUARD(run_frame(ctx, true));
+    ctx->blob_bytes = blob_bytes;
+    ctx->tree_leaves = n;
     ctx->have_tree = true;
     ctx->topology_valid = true;
     ++ctx->full_builds;
@@ -1711,7 +1871,14 @@ b2col_status b2col_refit(b2col_ctx* ctx)
     ctx->exact_nodes_valid = false;
     if (!ctx->world_external) GUARD(ensure(ctx, ctx->d_world, ((size_t)ctx->n_entities + 1) * 64));
     PHASE(ctx);
-    GUARD(run_frame(ctx, false));
+    {
+        const b2col_status st = run_frame(ctx, false);
+        if (st != B2COL_OK) {  // the blob may be half re-bounded
+            ctx->have_tree = false;
+            ctx->topology_valid = false;
+            return st;
+        }
+    }
     ++ctx->refits;
     return B2COL_OK;
 }
@@ -1723,9 +1890,12 @@ b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_
     return enqueue_trace(ctx, d_rays, n, d_out, mode);
 }
 
-b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode)
+// b2col_raycast_batch in two halves, so that one host thread can keep the pipelines of several GPUs in flight
+// (b2col_mgpu_raycast_batch): _begin enqueues every copy and kernel of the batch, _end waits for them.
+static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode)
 {
     if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    ctx->pending = b2col_ctx::PendingBatch();
     if (n == 0) return B2COL_OK;
     CU(cudaSetDevice(ctx->device));
     if (mode == B2COL_MODE_LBVH && n <= b2col_ctx::SMALL_MAX && ctx->have_tree && ctx->tree_leaves > 0 && !ctx->no_small_path) {
@@ -1819,27 +1989,58 @@ b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t
             ++c;
             m = std::min(2 * m, ctx->e2e_chunk);
         }
-        CU(cudaStreamSynchronize(ctx->stream_out));
-        CU(cudaStreamSynchronize(ctx->stream));
-        if (timed && h_out_dev && ctx->d2h_policy < 0) {
-            const double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - t_begin).count() / (double)n;
-            double& est = ctx->d2h_ns_per_ray[d2h];
-            est = est == 0.0 ? ns : 0.5 * est + 0.5 * ns;
-            ++ctx->d2h_calls;
-        }
+        ctx->pending.active = true;
+        ctx->pending.pipeline = true;
+        ctx->pending.timed = timed;
+        ctx->pending.has_dev_out = h_out_dev != nullptr;
+        ctx->pending.d2h = d2h;
+        ctx->pending.n = n;
+        ctx->pending.t_begin = t_begin;
         return B2COL_OK;
     }
     CU(cudaMemcpyAsync(ctx->d_rays.p, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));
     GUARD(enqueue_trace(ctx, ctx->d_rays.as<b2col_ray>(), n, ctx->d_hits.as<b2col_raycast>(), mode));
     CU(cudaMemcpyAsync(h_out, ctx->d_hits.p, n * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->pending.active = true;
+    ctx->pending.mode = mode;
+    ctx->pending.n = n;
+    return B2COL_OK;
+}
+
+static b2col_status raycast_batch_end(b2col_ctx* ctx)
+{
+    if (!ctx->pending.active) return B2COL_OK;
+    const b2col_ctx::PendingBatch pb = ctx->pending;
+    ctx->pending.active = false;
+    CU(cudaSetDevice(ctx->device));
+    if (pb.pipeline) {
+        CU(cudaStreamSynchronize(ctx->stream_out));
+        CU(cudaStreamSynchronize(ctx->stream));
+        if (pb.timed && pb.has_dev_out && ctx->d2h_policy < 0) {
+            const double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - pb.t_begin).count() / (double)pb.n;
+            double& est = ctx->d2h_ns_per_ray[pb.d2h];
+            est = est == 0.0 ? ns : 0.5 * est + 0.5 * ns;
+            ++ctx->d2h_calls;
+        }
+        return B2COL_OK;
+    }
     CU(cudaStreamSynchronize(ctx->stream));
-    if (mode == B2COL_MODE_REFTOPO) {
+    if (pb.mode == B2COL_MODE_REFTOPO) {
         uint32_t flag = 0;
         CU(cudaMemcpy(&flag, ctx->d_flag.p, 4, cudaMemcpyDeviceToHost));
         if (flag) return fail(ctx, B2COL_ERR_OVERFLOW, "reference-topology traversal stack overflow (tree deeper than %d)", REFTOPO_STACK);
     }
     return B2COL_OK;
 }
+
+b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode)
+{
+    if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n == 0) return B2COL_OK;
+    GUARD(raycast_batch_begin(ctx, h_rays, n, h_out, mode));
+    return raycast_batch_end(ctx);
+}
+
 
 b2col_status b2col_upload_ref_bvh(b2col_ctx* ctx, const b2col_bitreenode* h_nodes, size_t n_nodes)
 {
@@ -1852,6 +2053,26 @@ b2col_status b2col_upload_ref_bvh(b2col_ctx* ctx, const b2col_bitreenode* h_node
         if (nd.type1 > 2 || nd.type2 > 2) return fail(ctx, B2COL_ERR_INVALID, "node %zu has an invalid type", i);
         if ((nd.type1 == B2COL_NODE_BOUNDING_VOLUME && nd.index1 >= n_nodes) || (nd.type2 == B2COL_NODE_BOUNDING_VOLUME && nd.index2 >= n_nodes))
             return fail(ctx, B2COL_ERR_INVALID, "node %zu refers to a child outside the array", i);
+    }
+    // ... and that it is a TREE below its root (the last node): a node reachable twice means a cycle or a shared subtree, and a
+    // cycle would keep k_trace_reftopo descending forever
+    if (n_nodes) {
+        std::vector<uint8_t> seen(n_nodes, 0);
+        std::vector<uint32_t> todo;
+        todo.push_back((uint32_t)(n_nodes - 1));
+        seen[n_nodes - 1] = 1;
+        while (!todo.empty()) {
+            const b2col_bitreenode& nd = h_nodes[todo.back()];
+            todo.pop_back();
+            const uint32_t child[2] = {nd.index1, nd.index2};
+            const uint8_t type[2] = {nd.type1, nd.type2};
+            for (int k = 0; k < 2; ++k) {
+                if (type[k] != B2COL_NODE_BOUNDING_VOLUME) continue;
+                if (seen[child[k]]) return fail(ctx, B2COL_ERR_INVALID, "node %u is reachable twice from the root: not a tree", child[k]);
+                seen[child[k]] = 1;
+                todo.push_back(child[k]);
+            }
+        }
     }
     GUARD(ensure(ctx, ctx->d_ref_nodes, n_nodes * 60 + 4));
     if (n_nodes) {
@@ -1867,8 +2088,8 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
     if (!ctx || !n_out) return fail(ctx, B2COL_ERR_INVALID, "null argument");
     *n_out = 0;
     if (!ctx->have_tree || ctx->tree_leaves == 0) return B2COL_OK;  // empty bvh_
-    if (ctx->tree_leaves != ctx->n_colliders || !ctx->d_world_aabb.p)
-        return fail(ctx, B2COL_ERR_STATE, "export needs a tree built by b2col_update on this ctx");
+    if (!ctx->topology_valid || ctx->tree_leaves != ctx->n_colliders || !ctx->d_world_aabb.p)
+        return fail(ctx, B2COL_ERR_STATE, "export needs a tree built by b2col_update on this ctx (an imported tree has no keys / world records here)");
     CU(cudaSetDevice(ctx->device));
     const uint32_t n = ctx->tree_leaves;
     if (n == 1) {
@@ -1944,10 +2165,21 @@ b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out)
     return B2COL_OK;
 }
 
+b2col_status b2col_read_device(b2col_ctx* ctx, const void* d_src, size_t bytes, void* h_dst)
+{
+    if (!ctx || (bytes && (!d_src || !h_dst))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!bytes) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return B2COL_OK;
+}
+
 b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out)
 {
     if (!ctx || (ctx->n_colliders && !h_out)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
-    if (!ctx->have_tree || ctx->tree_leaves != ctx->n_colliders) return fail(ctx, B2COL_ERR_STATE, "b2col_update has not run");
+    if (!ctx->have_tree || !ctx->topology_valid || ctx->tree_leaves != ctx->n_colliders)
+        return fail(ctx, B2COL_ERR_STATE, "b2col_update has not run on this ctx for the tree it holds");
     if (!ctx->n_colliders) return B2COL_OK;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMemcpyAsync(h_out, ctx->d_vals[ctx->sorted_side].p, (size_t)ctx->n_colliders * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -2010,21 +2242,44 @@ b2col_status b2col_bvh_export_blob(b2col_ctx* ctx, void* d_dst, size_t bytes)
     return B2COL_OK;
 }
 
+// leaf count of a blob of `bytes` bytes (blob_size_for is strictly increasing); false if no count matches
+static bool leaves_from_blob_size(size_t bytes, uint32_t* n_out)
+{
+    uint32_t lo = 0, hi = (1u << 29);
+    while (lo < hi) {
+        const uint32_t mid = lo + (hi - lo) / 2;
+        if (blob_size_for(mid) < bytes) lo = mid + 1;
+        else hi = mid;
+    }
+    *n_out = lo;
+    return blob_size_for(lo) == bytes;
+}
+
 b2col_status b2col_bvh_import_blob(b2col_ctx* ctx, const void* d_src, size_t bytes)
 {
     if (!ctx || !d_src || bytes < sizeof(BlobHeader)) return fail(ctx, B2COL_ERR_INVALID, "bad blob");
+    uint32_t n_leaves = 0;
+    if (!leaves_from_blob_size(bytes, &n_leaves)) return fail(ctx, B2COL_ERR_INVALID, "%zu bytes is not the size of a BVH blob", bytes);
     CU(cudaSetDevice(ctx->device));
-    BlobHeader h;
-    CU(cudaStreamSynchronize(ctx->stream));
-    CU(cudaMemcpy(&h, d_src, sizeof h, cudaMemcpyDeviceToHost));
-    if (h.magic != BLOB_MAGIC && !(h.magic == 0 && h.n_leaves == 0)) return fail(ctx, B2COL_ERR_INVALID, "blob magic mismatch");
-    if (blob_size_for(h.n_leaves) != bytes) return fail(ctx, B2COL_ERR_INVALID, "blob size %zu does not match its header (%u leaves)", bytes, h.n_leaves);
-    GUARD(ensure(ctx, ctx->d_blob, bytes));
+    // No host round trip on this path: the leaf count follows from the size, and the header (magic, leaf count) is copied
+    // to page-locked memory behind the import and checked by the next b2col_sync.
+    if (!ctx->h_import_hdr) CU(cudaHostAlloc(&ctx->h_import_hdr, sizeof(BlobHeader), cudaHostAllocDefault));
+    {
+        const void* before = ctx->d_blob.p;
+        const b2col_status st = ensure(ctx, ctx->d_blob, bytes);
+        if (ctx->d_blob.p != before || st != B2COL_OK) ctx->have_tree = false;
+        GUARD(st);
+    }
+    ctx->have_tree = false;
     if (ctx->d_blob.p != d_src) CU(cudaMemcpyAsync(ctx->d_blob.p, d_src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_import_hdr, ctx->d_blob.p, sizeof(BlobHeader), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->import_check_leaves = n_leaves;
+    ctx->import_check_pending = true;
     ctx->blob_bytes = bytes;
-    ctx->tree_leaves = h.n_leaves;
+    ctx->tree_leaves = n_leaves;
     ctx->have_tree = true;
     ctx->topology_valid = false;  // a foreign tree: its sorted keys are not on this ctx
+    ctx->exact_nodes_valid = false;
     return B2COL_OK;
 }
 
@@ -2064,3 +2319,5 @@ b2col_status b2col_event_elapsed_ms(b2col_ctx* ctx, int a, int b, float* ms)
 }
 
 }  // extern "C"
+
+#include "b2col_comm.inl"

@@ -15,6 +15,23 @@ struct Aabb24 {  // engine::AABB, 24 bytes (reference include/component_collider
 
 constexpr uint32_t UNVISITED = 0xFFFFFFFFu;
 
+// ---- colliders the grid cannot bound ("wild") --------------------------------------------------
+// The reference's transformBox / slab test have defined behaviour for NaN and +-inf coordinates (fminf / fmaxf drop NaN,
+// src/system_collisions.cpp:21-38,65-83): a world AABB with a NaN plane ignores that plane, one with an infinite plane is
+// open on that side.  Such a box has no conservative image on a finite grid, so its child slot — and the slot of every
+// ancestor — carries WILD_BIT: the slot is ALWAYS entered, whatever the grid test says, and the exact leaf test decides
+// as it does for every other leaf.  Sane scenes have no wild leaf and run the instantiation of the traversal that does
+// not look at the bit (hdr->has_wild, decided once per kernel); a scene with some pays ~tree depth extra visits per ray
+// and wild leaf.  Coordinates beyond 1e37 count as non-finite so that the grid extent itself stays finite.
+constexpr uint32_t WILD_BIT = 0x40000000u;
+constexpr uint32_t REF_INDEX_MASK = 0x3FFFFFFFu;  // leaf position / node index of a child ref (n < 2^30)
+constexpr float GRID_COORD_MAX = 1.0e37f;
+B2_HD bool grid_coord_ok(float x) { return fabsf(x) <= GRID_COORD_MAX; }  // false for NaN, +-inf and |x| > 1e37
+B2_HD bool box_is_wild(const float* lo, const float* hi)
+{
+    return !(grid_coord_ok(lo[0]) && grid_coord_ok(lo[1]) && grid_coord_ok(lo[2]) && grid_coord_ok(hi[0]) && grid_coord_ok(hi[1]) && grid_coord_ok(hi[2]));
+}
+
 // ---- traversal structure: 32-byte quantised nodes + 32-byte exact leaf records -------------------
 // The production traversal is bound first by L1 wavefronts (one per lane per 32-byte sector: incoherent
 // rays never share a line) and then by instruction issue, so a node visit must cost ONE sector and as
@@ -229,7 +246,8 @@ B2_HD void build_from_leaf(uint32_t i, uint32_t n, const Key* keys, const uint32
 // retires, the second receives it as the exchange's return value.  No data is published through ordinary
 // memory, hence no fences.  The message holds
 //     the child's grid box            6 x 15 bits   (the always-set bit 15 of each plane is reused as payload)
-//     the far bound of its range      31 bits
+//     the far bound of its range      30 bits
+//     whether it holds a wild leaf     1 bit   (WILD_BIT above)
 //     the split LEVEL beyond that bound  7 bits
 // where level(i) = 64 + msb(key[i] ^ key[i+1]), or msb(i ^ (i+1)) for duplicate keys, 127 = array end, is the
 // delta of Karras' tree reduced to what the climb compares: in any state the climb reaches, all splits
@@ -266,28 +284,31 @@ B2_HD uint32_t split_level(uint64_t ka, uint64_t kb, uint32_t i)
     return x ? 64u + msb64(x) : msb32(i ^ (i + 1u));
 }
 
-B2_HD Xch xch_pack(const QBox& box, uint32_t bound, uint32_t level)
+// w[3] = far bound (30 bits) | wild << 30 | level bit 6 << 31.  bound <= n - 1 < 2^30 - 1, so w[3] is never UNVISITED.
+B2_HD Xch xch_pack(const QBox& box, uint32_t bound, uint32_t level, bool wild)
 {
     Xch m;
     m.w[0] = (box.w[0] & 0x7FFF7FFFu) | ((level & 1u) << 15) | ((level & 2u) << 30);
     m.w[1] = (box.w[1] & 0x7FFF7FFFu) | ((level & 4u) << 13) | ((level & 8u) << 28);
     m.w[2] = (box.w[2] & 0x7FFF7FFFu) | ((level & 16u) << 11) | ((level & 32u) << 26);
-    m.w[3] = bound | ((level & 64u) << 25);
+    m.w[3] = bound | (wild ? WILD_BIT : 0u) | ((level & 64u) << 25);
     return m;
 }
-B2_HD void xch_unpack(const Xch& m, QBox& box, uint32_t& bound, uint32_t& level)
+B2_HD void xch_unpack(const Xch& m, QBox& box, uint32_t& bound, uint32_t& level, bool& wild)
 {
     level = ((m.w[0] >> 15) & 1u) | ((m.w[0] >> 30) & 2u) | ((m.w[1] >> 13) & 4u) | ((m.w[1] >> 28) & 8u) | ((m.w[2] >> 11) & 16u) |
             ((m.w[2] >> 26) & 32u) | ((m.w[3] >> 25) & 64u);
     box.w[0] = m.w[0] | 0x80008000u;
     box.w[1] = m.w[1] | 0x80008000u;
     box.w[2] = m.w[2] | 0x80008000u;
-    bound = m.w[3] & 0x7FFFFFFFu;
+    bound = m.w[3] & REF_INDEX_MASK;
+    wild = (m.w[3] & WILD_BIT) != 0u;
 }
 
 template <class Ops, class Key>
 B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint32_t* sorted_prim, const Aabb24* world_aabb,
-                             const uint32_t* col_entity, Xch* xch, const Grid& grid, QNode* qnodes, LeafRec* leaves, uint32_t* root_out)
+                             const uint32_t* col_entity, Xch* xch, const Grid& grid, QNode* qnodes, LeafRec* leaves, uint32_t* root_out,
+                             uint32_t* has_wild_out)
 {
     const uint32_t prim = sorted_prim[i];
     LeafRec rec;
@@ -300,14 +321,16 @@ B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint
     rec.prim = prim;
     Ops::store_leaf(&leaves[i], rec);
     QBox box = quantise_box(rec.lo, rec.hi, grid);
+    bool wild = box_is_wild(rec.lo, rec.hi);
     if (n == 1) {  // a lone leaf still gets a node; both slots = the leaf (an empty slot has no grid encoding)
         QNode nd;
 #pragma unroll
         for (int k = 0; k < 3; ++k) nd.w[k] = nd.w[3 + k] = box.w[k];
-        nd.w[6] = LEAF_BIT | 0u;
-        nd.w[7] = LEAF_BIT | 0u;
+        nd.w[6] = LEAF_BIT | (wild ? WILD_BIT : 0u) | 0u;
+        nd.w[7] = nd.w[6];
         Ops::store_qnode(&qnodes[0], nd);
         *root_out = 0u;
+        *has_wild_out = wild ? 1u : 0u;
         return;
     }
     const uint64_t key = (uint64_t)keys[i];
@@ -318,13 +341,15 @@ B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint
     for (;;) {
         const bool is_left = lev_r < lev_l;  // join the neighbour beyond the LOWER split; array ends never win
         const uint32_t p = is_left ? r : l - 1u;
-        Ops::store_ref(&qnodes[p], is_left ? 0 : 1, ref);
-        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r);
+        Ops::store_ref(&qnodes[p], is_left ? 0 : 1, ref | (wild ? WILD_BIT : 0u));
+        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r, wild);
         const Xch got = Ops::exchange(&xch[p], mine);
         if (got.w[3] == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
         QBox sib;
         uint32_t bound, level;
-        xch_unpack(got, sib, bound, level);
+        bool sib_wild;
+        xch_unpack(got, sib, bound, level, sib_wild);
+        wild = wild || sib_wild;
         Ops::store_qboxes(&qnodes[p], is_left ? box.w : sib.w, is_left ? sib.w : box.w);
         if (is_left) {
             r = bound;
@@ -339,6 +364,7 @@ B2_HD void build_from_leaf_q(uint32_t i, uint32_t n, const Key* keys, const uint
         ref = p;
         if (lev_l == LEVEL_END && lev_r == LEVEL_END) {  // the range is the whole array
             *root_out = p;
+            *has_wild_out = wild ? 1u : 0u;
             return;
         }
     }
@@ -480,18 +506,22 @@ struct RayQ {
     uint32_t sel_near[3], sel_far[3];
 };
 
-// false => the origin is non-finite or more than 2^22 cells from the grid: every box is then more
-// than 16 T away (make_grid), so the reference's slab test (tmin < T) rejects them all: a miss.
+// false => the origin is more than 2^22 cells from the grid (or infinite): every box on the grid is then more than
+// 16 T away (make_grid), so the reference's slab test (tmin < T) rejects them all: a miss — unless the tree holds wild
+// leaves, which the caller must then still visit.  A NaN origin coordinate or reciprocal is NOT a miss: the reference's
+// fminf / fmaxf drop the NaN slab values of that axis (src/system_collisions.cpp:67-83) and the other axes decide; here
+// c (and n) become NaN, the axis' near / far values become NaN and max3f / min3f drop them likewise.
 B2_HD bool rayq_prepare(const RayPre& r, const Grid& g, RayQ& q)
 {
     bool ok = true;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float og = (r.o[k] - g.gmin[k]) * g.inv_cell[k];
-        ok = ok && (fabsf(og) < 4194304.0f);
+        ok = ok && !(fabsf(og) >= 4194304.0f);
         const float on = 1.0f + og * (1.0f / GRID_CELLS);
         float n = r.ninv[k] * (g.cell[k] * GRID_CELLS);
-        n = fminf(fmaxf(n, -1.099511627776e12f), 1.099511627776e12f);  // +-2^40 (NaN -> -2^40: harmless, exact tests decide)
+        const float nc = fminf(fmaxf(n, -1.099511627776e12f), 1.099511627776e12f);  // +-2^40
+        n = (n == n) ? nc : n;                                                         // NaN stays NaN: the axis drops out
         q.n[k] = n;
         q.c[k] = -(on * n);
         const bool neg = n < 0.0f;
@@ -573,20 +603,36 @@ struct VisitOut {
     bool push;
 };
 
-template <class Ops, class RayFn>
+// WILD: the tree holds wild leaves (see WILD_BIT): a flagged slot is entered whatever its grid box says, as early as possible.
+template <class Ops, bool WILD, class RayFn>
 B2_HD VisitOut visit_node(Hit& best, float& lim, const RayQ& q, const QNode& nd, const LeafRec* leaves, float T, RayFn exact_ray)
 {
     float ta, tb;
     bool ha = qslab(q, nd.w[0], nd.w[1], nd.w[2], lim, ta);
     bool hb = qslab(q, nd.w[3], nd.w[4], nd.w[5], lim, tb);
-    const uint32_t ra = nd.w[6], rb = nd.w[7];
+    uint32_t ra = nd.w[6], rb = nd.w[7];
+    if (WILD) {
+        if (ra & WILD_BIT) {
+            ha = true;
+            ta = -B2_INF;
+        }
+        if (rb & WILD_BIT) {
+            hb = true;
+            tb = -B2_INF;
+        }
+        ra &= ~WILD_BIT;
+        rb &= ~WILD_BIT;
+    }
     const bool la = ha && (ra & LEAF_BIT), lb = hb && (rb & LEAF_BIT);
     if (la || lb) {
         const RayPre r = exact_ray();
         bool better = false;
         if (la) better = leaf_candidate(best, r, Ops::load_leaf(&leaves[ra & ~LEAF_BIT]), ra, T);
         if (lb) better = leaf_candidate(best, r, Ops::load_leaf(&leaves[rb & ~LEAF_BIT]), rb, T) || better;
-        if (better) lim = best.t;
+        // Not below -2^26: an exact tmin of -inf (every axis either dropped as NaN or entered with an infinite reciprocal from
+        // inside the slab) has a FINITE image in grid space, where |n| is clamped to 2^40 — at most -2^-14 * 2^40, the
+        // origin being at least the 2-cell margin inside the grid box — and a later leaf tying at -inf must still be reached.
+        if (better) lim = fmaxf(best.t, -67108864.0f);
         ha = ha && !la && (ta <= lim);
         hb = hb && !lb && (tb <= lim);
     }
@@ -616,14 +662,14 @@ B2_HD void finish_raycast(uint32_t* out9, const RayPre& r, const Hit& best, cons
 // Whole-ray form with a plain array stack (host emulation; the device kernel, k_trace_lbvh in b2col.cu,
 // runs the same visit_node per step with a shared-memory stack and interleaves ray fetching).  A
 // deferred child whose entry tmin has meanwhile fallen behind the best hit is dropped when popped.
-template <class Ops>
+template <class Ops, bool WILD>
 B2_HD Hit trace_lbvh(const RayPre& r, const Grid& grid, const QNode* qnodes, const LeafRec* leaves, uint32_t root, float T)
 {
     Hit best;
     best.t = B2_INF;
     best.leaf = -1;
     RayQ q;
-    if (!rayq_prepare(r, grid, q)) return best;
+    if (!rayq_prepare(r, grid, q) && !WILD) return best;
     float lim = float_pred(T);
     uint32_t s_node[LBVH_STACK];
     float s_t[LBVH_STACK];
@@ -637,7 +683,7 @@ B2_HD Hit trace_lbvh(const RayPre& r, const Grid& grid, const QNode* qnodes, con
             cur = s_node[sp];
         }
         const QNode nd = Ops::load_qnode(&qnodes[cur]);
-        const VisitOut v = visit_node<Ops>(best, lim, q, nd, leaves, T, [&]() { return r; });
+        const VisitOut v = visit_node<Ops, WILD>(best, lim, q, nd, leaves, T, [&]() { return r; });
         if (v.push) {
             s_node[sp] = v.far;
             s_t[sp] = v.tfar;

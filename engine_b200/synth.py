@@ -305,3 +305,98 @@ def game_inputs(n_frames: int, seed: int = 10) -> np.ndarray:
         f += seg
     out[:, 5] = (rng.random(n_frames) < 0.02).astype(np.float32)
     return out
+
+
+def degenerate_scene(n: int = 5000, seed: int = 90, extent: float = 60.0, with_nan: bool = True) -> Scene:
+    """A sane uniform scene with degenerate colliders mixed in (the reference's transformBox, src/system_collisions.cpp:14-41,
+    and slab test, :62-100, have DEFINED behaviour for them through fminf / fmaxf): infinite and huge positions and scales, zero scale,
+    a local box whose min exceeds its max, an infinite local box — and, with_nan, NaN positions / quaternions / box coordinates.
+    Every 97th collider starting at 11 is degenerate, cycling through the kinds; the kinds are returned in `scene.degenerate_kind`
+    (0 = sane)."""
+    rng = np.random.default_rng(seed)
+    s = uniform_boxes(n, seed=seed, extent=extent, hmin=0.4, hmax=2.5)
+    s.rot[1:] = random_unit_quats(rng, n)  # rotated boxes: the refit matters
+    kind = np.zeros(n, np.int32)
+    kinds = ["pos_inf", "pos_huge", "scale_zero", "scale_zero_axis", "scale_huge", "scale_inf", "box_inverted", "box_inf", "scale_negative", "pos_1e30"]
+    if with_nan:
+        kinds += ["pos_nan", "quat_nan", "box_nan_one", "quat_zero"]
+    inf, nan = np.float32(np.inf), np.float32(np.nan)
+    for j, c in enumerate(range(11, n, 97)):
+        k = kinds[j % len(kinds)]
+        kind[c] = 1 + j % len(kinds)
+        e = c + 1  # entity ID of collider c
+        if k == "pos_inf":
+            s.pos[e, j % 3] = inf if j % 2 else -inf
+        elif k == "pos_huge":
+            s.pos[e, j % 3] = np.float32(3.0e38)
+        elif k == "pos_1e30":
+            s.pos[e] = np.float32(1.0e30)
+        elif k == "scale_zero":
+            s.scl[e] = 0.0
+        elif k == "scale_zero_axis":
+            s.scl[e, j % 3] = 0.0
+        elif k == "scale_huge":
+            s.scl[e] = np.float32(1.0e30)
+        elif k == "scale_inf":
+            s.scl[e, j % 3] = inf
+        elif k == "scale_negative":
+            s.scl[e] = (-1.5, 2.0, -0.5)
+        elif k == "box_inverted":
+            s.collider_aabb[c] = (1.0, 2.0, 0.5, -1.0, -2.0, -0.5)
+        elif k == "box_inf":
+            s.rot[e] = (0.0, 0.0, 0.0, 1.0)
+            s.collider_aabb[c, 3 + j % 3] = inf
+        elif k == "pos_nan":
+            s.pos[e, j % 3] = nan
+        elif k == "quat_nan":
+            s.rot[e, j % 4] = nan
+        elif k == "quat_zero":
+            s.rot[e] = 0.0
+        elif k == "box_nan_one":
+            s.rot[e] = (0.0, 0.0, 0.0, 1.0)
+            s.collider_aabb[c, j % 6] = nan
+    s.degenerate_kind = kind
+    return s
+
+
+def degenerate_rays(n: int, seed: int = 91, extent: float = 70.0) -> np.ndarray:
+    """Random rays with the degenerate cases of the reference's ray arithmetic mixed in (GetRaycast normalises, :162; the slab test
+    divides by the direction, :65): zero / denormal / infinite / NaN direction components, axis-parallel directions with signed
+    zeros, NaN and infinite origin coordinates (a NaN coordinate makes the reference IGNORE that axis), origins far outside the scene."""
+    rng = np.random.default_rng(seed)
+    rays = random_rays(n, seed=seed, extent=extent, normalised=False)
+    inf, nan = np.float32(np.inf), np.float32(np.nan)
+    for j, i in enumerate(range(3, n, 13)):
+        k = j % 14
+        if k == 0:
+            rays[i, 3:] = 0.0
+        elif k == 1:
+            rays[i, 3 + j % 3] = inf
+        elif k == 2:
+            rays[i, j % 3] = nan
+        elif k == 3:
+            rays[i, 3:] = (0.0, -0.0, 1.0)
+        elif k == 4:
+            rays[i, 3:] = (1e-30, 1e-30, 1e-30)
+        elif k == 5:
+            rays[i, j % 3] = inf
+        elif k == 6:
+            rays[i, 3 + j % 3] = nan
+        elif k == 7:
+            rays[i, 0:3] = (nan, nan, 0.5)
+        elif k == 8:
+            rays[i, 0:3] *= np.float32(1.0e6)
+        elif k == 9:
+            rays[i, 3:] = (-0.0, 1.0, 0.0)
+        elif k == 10:
+            rays[i, 0:3] = np.float32(1.0e30)
+            rays[i, 3:] = (-1.0, -1.0, -1.0)
+        elif k == 11:
+            rays[i, 3:] = (1.0, 0.0, 0.0)
+            rays[i, 0] = -np.float32(3.0e38)
+        elif k == 12:
+            rays[i, 3 + j % 3] = -inf
+        elif k == 13:
+            rays[i, 0:3] = rng.uniform(-extent, extent, 3).astype(np.float32)
+            rays[i, 3:] = (0.0, 0.0, -1.0)
+    return rays

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B2COL_ABI_VERSION 1
+#define B2COL_ABI_VERSION 2
 
 typedef struct b2col_ctx b2col_ctx;
 
@@ -47,7 +47,8 @@ typedef enum b2col_status {
     B2COL_ERR_NO_DEVICE = 3,   /* no usable CUDA device: this library has no CPU path */
     B2COL_ERR_STATE = 4,       /* call sequence error (e.g. update before set_*) */
     B2COL_ERR_UNSUPPORTED = 5, /* e.g. a parent whose ID is not smaller than its child's */
-    B2COL_ERR_OVERFLOW = 6     /* traversal stack overflow in reference-topology mode */
+    B2COL_ERR_OVERFLOW = 6,    /* traversal stack overflow in reference-topology mode */
+    B2COL_ERR_COMM = 7         /* NCCL could not be loaded, or an NCCL call failed; see b2col_last_error */
 } b2col_status;
 
 /* engine::Ray — reference include/system_collisions.h:13-16 (24 bytes) */
@@ -188,15 +189,77 @@ b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out);
  * depth-first leaf order of the tree, the order that decides tie winners */
 b2col_status b2col_get_leaf_order(b2col_ctx* ctx, uint32_t* h_out);
 b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out);
+/* copy `bytes` of device memory owned by this ctx (e.g. the gathered Raycasts of b2col_comm_raycast_gather) to the host, ordered
+ * after everything enqueued on the ctx stream; returns when h_dst is complete */
+b2col_status b2col_read_device(b2col_ctx* ctx, const void* d_src, size_t bytes, void* h_dst);
 /* totals over all B2COL_MODE_LBVH_COUNT calls on this ctx: BVH nodes fetched (one 32-byte sector each — the
  * unit the traversal's binding resource, L1 wavefronts, is counted in) and rays traced */
 b2col_status b2col_get_trace_counters(b2col_ctx* ctx, uint64_t* node_visits, uint64_t* rays);
 
-/* ---- multi-GPU replication ------------------------------------------------------------------- */
-/* The traversal structure lives in ONE contiguous device allocation so that it can be replicated
- * with a single broadcast (NCCL over NVLink; the host side does the collective).  export returns the
- * device pointer and size of the source rank's blob; import copies a received blob of identical
- * size into this ctx and makes it the current tree. */
+/* ---- multi-GPU: rays shard across the GPUs of one box, the BVH is replicated, hits are gathered back ------------
+ * replaces: nothing in the reference, which is single-threaded on one CPU core (src/application.cpp:390); this is the
+ * scale-out of CollisionSystem::GetRaycast (include/system_collisions.h:36, src/system_collisions.cpp:160-199) that
+ * BASELINE.json's north_star asks for.  Rays are independent and the tree is read-only during
+ * queries, so a batch is cut into contiguous slices — b2col_shard_bounds — one per rank, the results land in the same
+ * slices and the gathered output is bit-identical to a 1-GPU trace of the whole batch.
+ *
+ * A "rank" is one context on one GPU.  Two deployments:
+ *   - one process per GPU (torchrun): rank 0 calls b2col_comm_get_unique_id, the application distributes the 128 bytes
+ *     (any transport), every rank calls b2col_comm_init_rank; afterwards b2col_comm_replicate / _raycast_gather are
+ *     collectives: every rank calls them with the same arguments, in the same order.
+ *   - one process driving n GPUs (a game engine: engine_b200/shim): b2col_comm_init_all over n contexts, then the
+ *     *_all entry points (one NCCL group per call) and b2col_mgpu_raycast_batch for host buffers.
+ * NCCL (libnccl.so.2) is loaded on first use; without it these calls fail with B2COL_ERR_COMM and nothing else is
+ * affected. */
+#define B2COL_COMM_ID_BYTES 128 /* sizeof(ncclUniqueId) */
+/* rank's slice [*lo, *hi) of an n-element batch: lo = n*rank/n_ranks, hi = n*(rank+1)/n_ranks (pure function) */
+void b2col_shard_bounds(size_t n, int n_ranks, int rank, size_t* lo, size_t* hi);
+b2col_status b2col_comm_get_unique_id(void* id128);
+b2col_status b2col_comm_init_rank(b2col_ctx* ctx, int n_ranks, int rank, const void* id128);
+/* n contexts of this process, each on its own device; context i becomes rank i.  Enables peer access between them. */
+b2col_status b2col_comm_init_all(b2col_ctx* const* ctxs, int n);
+/* releases the communicator and the gather window (b2col_destroy does it too) */
+b2col_status b2col_comm_finalize(b2col_ctx* ctx);
+
+/* Replicate the tree of src_rank (built by b2col_update there) on every rank: ONE ncclBroadcast over NVLink straight
+ * out of the source's BVH allocation into the other ranks' — no staging copy, no size exchange, no host round trip;
+ * every rank passes the collider count (it sizes the allocation).  Enqueued on the ctx stream.  Receiving ranks can
+ * trace the tree but not export / refit it (the sorted keys stay on src_rank). */
+b2col_status b2col_comm_replicate(b2col_ctx* ctx, int src_rank, uint32_t n_colliders);
+b2col_status b2col_comm_replicate_all(b2col_ctx* const* ctxs, int n, int src_rank);
+/* The alternative SURVEY.md 8(e) asks to measure against it: broadcast the 32-byte world records (half the bytes of the
+ * tree) and run Morton + sort + hierarchy on every rank; the build is deterministic, so the trees are identical. */
+b2col_status b2col_comm_replicate_records(b2col_ctx* ctx, int src_rank, uint32_t n_colliders);
+
+/* Sharded GetRaycast with the gather fused into the traversal: d_rays_shard holds THIS rank's slice of an n_total-ray
+ * batch (device memory); the nearest hits of the whole batch end up in batch order in device memory on dst_rank,
+ * *d_out_all (set on dst_rank only; owned by the context, valid until its next gather with a larger batch or
+ * b2col_comm_finalize).  The trace kernel of every rank writes its Raycasts straight into dst_rank's buffer over
+ * NVLink (peer mapping), so nothing is sent after the traversal; the call ends with the completion step of the
+ * collective on the ctx stream.  Enqueued; b2col_sync on dst_rank (after the other ranks enqueued theirs) waits for
+ * the whole batch. */
+b2col_status b2col_comm_raycast_gather(b2col_ctx* ctx, const b2col_ray* d_rays_shard, size_t n_total, int dst_rank, const b2col_raycast** d_out_all);
+b2col_status b2col_comm_raycast_gather_all(b2col_ctx* const* ctxs, int n, const b2col_ray* const* d_rays_shards, size_t n_total, int dst_rank,
+                                           const b2col_raycast** d_out_all);
+/* replaces: CollisionSystem::GetRaycast over a batch in HOST memory, on several GPUs of this process: slice i is
+ * uploaded, traced and downloaded by context i, straight from / into the caller's buffers (nothing to gather).
+ * Contexts need not have a communicator, only equal trees (b2col_comm_replicate_all, or the same b2col_update). */
+b2col_status b2col_mgpu_raycast_batch(b2col_ctx* const* ctxs, int n, const b2col_ray* h_rays, size_t n_rays, b2col_raycast* h_out, int mode);
+
+enum { B2COL_GATHER_NONE = 0, B2COL_GATHER_PEER_WINDOW = 1, B2COL_GATHER_PEER_WINDOW_IPC = 2, B2COL_GATHER_NCCL_SENDRECV = 3 };
+typedef struct b2col_comm_info_t {
+    int n_ranks, rank;
+    int single_process;   /* 1: created by b2col_comm_init_all */
+    int gather_mode;      /* B2COL_GATHER_*: how b2col_comm_raycast_gather moves the hits (3 = fallback: IPC mapping unavailable) */
+    int nccl_version;
+    uint64_t window_bytes, gathers, replications;
+} b2col_comm_info_t;
+b2col_status b2col_comm_info(b2col_ctx* ctx, b2col_comm_info_t* out);
+
+/* ---- single-allocation BVH blob (tools, tests; the collectives above use it directly) --------------------------- */
+/* The traversal structure lives in ONE contiguous device allocation.  b2col_bvh_blob returns its device pointer and
+ * size; export copies it into caller-owned device memory; import copies a blob of matching size into this ctx and
+ * makes it the current tree (the leaf count follows from the size; the header is checked at the next b2col_sync). */
 b2col_status b2col_bvh_blob(b2col_ctx* ctx, void** d_ptr, size_t* bytes);
 /* copy the blob into caller-owned device memory (e.g. the tensor a collective will send); enqueued */
 b2col_status b2col_bvh_export_blob(b2col_ctx* ctx, void* d_dst, size_t bytes);

@@ -43,13 +43,14 @@ def load_golden(name):
 SCENE_FIXTURES = ["game600", "hier1500", "grid512", "city2000", "single", "pair", "triple"]
 
 
-def assert_raycast_equal(got, want, what="", ignore_entity_on=None, rel_tol=0.0):
+def assert_raycast_equal(got, want, what="", ignore_entity_on=None, rel_tol=0.0, nan_equal=False):
     """Parity bar (BASELINE.json north_star): hit flag and hit_entity bit-exact; distance, location,
     normal within 1e-5 relative.  We hold the floats to the stricter numeric equality by default
     (rel_tol=0): == treats +0 and -0 as equal, the one thing that legitimately differs — the
     reference's fminf/fmaxf return an operand-order-dependent zero sign (libm call with
     compiler-chosen argument order), so the sign of a zero distance is not defined by its source.
-    ignore_entity_on: boolean mask of rays (exact tmin ties) whose hit_entity may differ."""
+    ignore_entity_on: boolean mask of rays (exact tmin ties) whose hit_entity may differ.
+    nan_equal: degenerate inputs only — a NaN matches a NaN (a NaN ray origin gives a NaN location on both sides)."""
     assert got.shape == want.shape, (what, got.shape, want.shape)
     bad = np.nonzero(got["hit"] != want["hit"])[0]
     assert bad.size == 0, f"{what}: hit flag differs on {bad.size} rays, first {bad[:5]}"
@@ -64,6 +65,8 @@ def assert_raycast_equal(got, want, what="", ignore_entity_on=None, rel_tol=0.0)
             ok = a == b
         else:
             ok = np.abs(a - b) <= rel_tol * np.maximum(np.abs(a), np.abs(b))
+        if nan_equal:
+            ok |= np.isnan(a) & np.isnan(b)
         if ignore_entity_on is not None and f == "normal":
             ok |= ignore_entity_on.reshape((-1,) + (1,) * (ok.ndim - 1))
         assert ok.all(), f"{what}: {f} differs on {int((~ok).sum())} values, first ray {np.nonzero(~ok)[0][:5]}"

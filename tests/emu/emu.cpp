@@ -72,7 +72,7 @@ void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, 
 // `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
 // that the result does not depend on thread scheduling.
 void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, int drop, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
-               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order, int* mismatch)
+               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order, int* mismatch, uint32_t* has_wild)
 {
     if (n == 0) return;
     float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -81,12 +81,12 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
         for (int k = 0; k < 3; ++k) {
             const float lo = world_aabb[i].lo[k], hi = world_aabb[i].hi[k];
             const float c = (lo + hi) * 0.5f;
-            if (std::isfinite(c)) {
+            if (grid_coord_ok(c)) {
                 smin[k] = fminf(smin[k], c);
                 smax[k] = fmaxf(smax[k], c);
             }
-            if (std::isfinite(lo)) { bmin[k] = fminf(bmin[k], lo); bmax[k] = fmaxf(bmax[k], lo); }
-            if (std::isfinite(hi)) { bmin[k] = fminf(bmin[k], hi); bmax[k] = fmaxf(bmax[k], hi); }
+            if (grid_coord_ok(lo)) { bmin[k] = fminf(bmin[k], lo); bmax[k] = fmaxf(bmax[k], lo); }
+            if (grid_coord_ok(hi)) { bmin[k] = fminf(bmin[k], hi); bmax[k] = fmaxf(bmax[k], hi); }
         }
     const MortonPlan plan = make_morton_plan(smin, smax, 3 * bits - drop);
     const Grid grid = make_grid(bmin, bmax, T);
@@ -107,23 +107,23 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
         build_from_leaf<HostOps>(order ? order[t] : t, n, sorted_keys, sorted_prim, world_aabb, col_entity, nodes, other.data(), grid, q_exact.data(),
                                  (LeafRec*)nullptr, root);
     // ... and the traversal structure by the production builder (grid-space merge, visited in reverse order to
-    // vary which child arrives first); the two must agree on NaN-free input
+    // vary which child arrives first); the two must agree when no leaf is wild (the exact builder does not flag them)
     Xch none;
     none.w[0] = none.w[1] = none.w[2] = 0u;
     none.w[3] = UNVISITED;
     std::vector<Xch> xch(n, none);
     uint32_t root_q = 0;
     for (uint32_t t = 0; t < n; ++t)
-        build_from_leaf_q<HostOps>(order ? order[n - 1 - t] : n - 1 - t, n, sorted_keys, sorted_prim, world_aabb, col_entity, xch.data(), grid, qnodes, leaves, &root_q);
+        build_from_leaf_q<HostOps>(order ? order[n - 1 - t] : n - 1 - t, n, sorted_keys, sorted_prim, world_aabb, col_entity, xch.data(), grid, qnodes, leaves, &root_q, has_wild);
     *mismatch = (root_q != *root) ? 1 : 0;
-    bool nan_free = true;
-    for (uint32_t i = 0; i < n && nan_free; ++i)
-        for (int k = 0; k < 3; ++k) nan_free = nan_free && world_aabb[i].lo[k] == world_aabb[i].lo[k] && world_aabb[i].hi[k] == world_aabb[i].hi[k];
-    if (nan_free && std::memcmp(q_exact.data(), qnodes, q_exact.size() * sizeof(QNode)) != 0) *mismatch |= 2;
+    bool any_wild = false;
+    for (uint32_t i = 0; i < n && !any_wild; ++i) any_wild = box_is_wild(world_aabb[i].lo, world_aabb[i].hi);
+    if (any_wild != (*has_wild != 0u)) *mismatch |= 4;
+    if (!any_wild && std::memcmp(q_exact.data(), qnodes, q_exact.size() * sizeof(QNode)) != 0) *mismatch |= 2;
 }
 
 void emu_trace_lbvh(const QNode* qnodes, const LeafRec* leaves, const Grid* grid, uint32_t root, uint32_t n_leaves, const float* rays6, size_t n_rays,
-                    uint32_t* out9, float T)
+                    uint32_t* out9, float T, uint32_t has_wild)
 {
     for (size_t i = 0; i < n_rays; ++i) {
         const RayPre r = ray_prepare(rays6 + 6 * i, rays6 + 6 * i + 3);
@@ -131,7 +131,7 @@ void emu_trace_lbvh(const QNode* qnodes, const LeafRec* leaves, const Grid* grid
             write_raycast(out9 + 9 * i, r, false, 0.0f, 0, 0u);
             continue;
         }
-        const Hit h = trace_lbvh<HostOps>(r, *grid, qnodes, leaves, root, T);
+        const Hit h = has_wild ? trace_lbvh<HostOps, true>(r, *grid, qnodes, leaves, root, T) : trace_lbvh<HostOps, false>(r, *grid, qnodes, leaves, root, T);
         finish_raycast<HostOps>(out9 + 9 * i, r, h, leaves);
     }
 }

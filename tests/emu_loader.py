@@ -68,13 +68,14 @@ class Emu:
         sorted_keys = np.zeros(n, np.uint64)
         root = C.c_uint32(0)
         mismatch = C.c_int(0)
+        has_wild = C.c_uint32(0)
         if order is not None:
             order = np.ascontiguousarray(order, np.uint32)
         self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_int(drop), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
-                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order), C.byref(mismatch))
+                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order), C.byref(mismatch), C.byref(has_wild))
         assert mismatch.value == 0, f"grid-space builder disagrees with the exact builder (flags {mismatch.value})"
         return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
-                    sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb)
+                    sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb, has_wild=int(has_wild.value))
 
     def morton(self, centroids, cmin, cmax, key_bits):
         """(plan dict, keys) of engine_b200/csrc/b2col_math.cuh make_morton_plan / morton_key"""
@@ -92,7 +93,7 @@ class Emu:
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
         out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
         self.lib.emu_trace_lbvh(_p(tree["qnodes"]), _p(tree["leaves"]), _p(tree["grid"]), C.c_uint32(tree["root"]), C.c_uint32(tree["n"]), _p(rays),
-                                C.c_size_t(rays.shape[0]), _p(out), C.c_float(T))
+                                C.c_size_t(rays.shape[0]), _p(out), C.c_float(T), C.c_uint32(tree.get("has_wild", 0)))
         return out
 
     def trace_reftopo(self, nodes60, rays, T=1000.0):

@@ -273,3 +273,46 @@ def test_morton_plan_flat_world_example(emu):
     c = np.array([[0, 0, 0], [1000, 1000, 50]], np.float32)
     plan, _ = emu.morton(c, c.min(0), c.max(0), 32)
     assert plan["c"] == 2 and plan["d2"] == 4 and plan["nc"] == 8 and plan["drop"] == 0 and plan["shift_a"] == 0  # x, y: 12 bits, z: 8
+
+
+@pytest.mark.parametrize("with_nan", [False, True])
+def test_emu_degenerate_colliders_and_rays(emu, port, with_nan):
+    """NaN / inf / huge / zero-scale / inverted colliders; the kernel bodies must return what the reference's own
+    arithmetic returns leaf by leaf (brute force with its slab test) — wild leaves are always entered (b2col_bvh.cuh WILD_BIT) —
+    for sane and for degenerate rays, including the rays whose NaN origin coordinate makes the reference ignore an axis."""
+    s = synth.degenerate_scene(5000, with_nan=with_nan)
+    world = emu.propagate(s.parent, s.pos, s.rot, s.scl)
+    assert (bits(world) == bits(port.transform_update(s.parent, s.pos, s.rot, s.scl))).all()
+    boxes = emu.refit(s.collider_entity, s.collider_aabb, world)
+    assert (bits(boxes) == bits(port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6))).all()
+    assert (~np.isfinite(boxes)).any(axis=1).sum() >= 10
+    tree = emu.build(boxes, s.collider_entity)
+    assert tree["has_wild"] == 1
+    rays = np.concatenate([synth.degenerate_rays(4000), synth.random_rays(4000, seed=5, extent=70)])
+    got = emu.trace_lbvh(tree, rays)
+    brute = port.raycast_brute(tree["leaf_entity"], boxes[tree["sorted_prim"]], rays, nthreads=8)
+    assert_raycast_equal(got, brute, "degenerate scene vs brute force", nan_equal=True)
+    # without the boxes that swallow every ray (huge on all three axes: infinite / 1e30 scale) the other kinds decide
+    with np.errstate(invalid="ignore"):
+        keep = ~((boxes[:, 3:] - boxes[:, :3]) > 1e6).all(axis=1)
+    tree2 = emu.build(boxes[keep], s.collider_entity[keep])
+    got2 = emu.trace_lbvh(tree2, rays)
+    brute2 = port.raycast_brute(tree2["leaf_entity"], boxes[keep][tree2["sorted_prim"]], rays, nthreads=8)
+    assert_raycast_equal(got2, brute2, "degenerate scene without the all-swallowing boxes vs brute force", nan_equal=True)
+    if not with_nan:
+        assert 100 < got2["hit"].sum() < rays.shape[0] - 100  # no NaN plane: unions are exact, so the reference's own walk of the exported tree agrees too
+        assert_raycast_equal(got2, port.raycast_tree(emu.export(tree2), rays, nthreads=8), "exported", nan_equal=True)
+
+
+def test_shard_bounds_match_python():
+    from engine_b200 import collision, dist
+
+    for n in (0, 1, 7, 1000, 1001, 16 * 1024 * 1024, (1 << 40) + 12345):
+        for world in (1, 2, 3, 8):
+            cover = 0
+            for r in range(world):
+                lo, hi = collision.shard_bounds(n, world, r)
+                assert (lo, hi) == dist.shard_bounds(n, world, r)
+                assert lo == cover
+                cover = hi
+            assert cover == n

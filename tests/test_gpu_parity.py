@@ -3,6 +3,8 @@ against the oracle: golden vectors from the real reference, the oracle port, the
 oracle/_ref/libref_engine.so travelled with the snapshot, and size-independent properties at
 BASELINE.json's full sizes.  Parity bar: hit flag + hit_entity bit-exact; distance / location /
 normal held to exact float equality (stricter than the 1e-5 relative tolerance of north_star)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -31,6 +33,23 @@ def CollisionSystem():
 @pytest.fixture(scope="module")
 def emu():
     return Emu()
+
+
+_REF_WALKER = None
+
+
+def reference_walk(exported, rays, port):
+    """GetRaycast of the LIVE reference (oracle/_ref/libref_engine.so, unmodified src/system_collisions.cpp:160-199,379-540) over
+    `rays`, walking `exported` assigned to its public bvh_ member, on all host threads — every ray, no sampling.  The pinned C port
+    (second opinion, and the checker where the reference library did not travel) takes over when the library is absent."""
+    global _REF_WALKER
+    threads = os.cpu_count() or 8
+    if RefEngine.available():
+        if _REF_WALKER is None:
+            _REF_WALKER = RefEngine()
+        _REF_WALKER.set_bvh(exported)
+        return _REF_WALKER.raycast(rays, nthreads=threads)
+    return port.raycast_tree(exported, rays, nthreads=threads)
 
 
 def read_blob(cs, n):
@@ -156,6 +175,108 @@ def test_degenerate_inputs(CollisionSystem, port):
     assert (got["hit"] == want["hit"]).all() and (got["hit_entity"] == want["hit_entity"]).all()
 
 
+def nan_eq_bits(a, b):
+    """bitwise equality of float arrays except that any NaN matches any NaN (x86 and the GPU produce different NaN payloads)"""
+    a, b = np.ascontiguousarray(a, np.float32), np.ascontiguousarray(b, np.float32)
+    return (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+
+
+@pytest.mark.parametrize("with_nan", [False, True])
+def test_degenerate_colliders(CollisionSystem, port, emu, with_nan):
+    """NaN / +-inf positions, zero / 1e30 / infinite / negative scales, NaN and zero quaternions, a local box whose min exceeds its
+    max, an infinite local box — mixed into a 5k scene (reference transformBox src/system_collisions.cpp:14-41 and
+    slab test :62-100, whose fminf / fmaxf give these inputs defined results).  World matrices and world AABBs equal the oracle's
+    bit for bit (any NaN == any NaN); the tree equals the host restatement incl. its WILD_BIT slots; every ray — sane and degenerate
+    ones — gets the reference's leaf-level answer (brute force with the reference's slab test), and, where no NaN plane makes the
+    reference's own node unions order-dependent, the answer of the LIVE reference walking the exported tree."""
+    s = synth.degenerate_scene(5000, with_nan=with_nan)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+    assert nan_eq_bits(cs.world_matrices(), world[1:]).all(), "world matrices"
+    want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+    boxes = cs.world_aabbs()
+    assert nan_eq_bits(boxes, want_boxes).all(), "world AABBs"
+    assert (~np.isfinite(boxes)).any(axis=1).sum() >= 10
+    tree = emu.build(boxes, s.collider_entity)
+    assert tree["has_wild"] == 1
+    order = cs.leaf_order()
+    assert np.array_equal(order, tree["sorted_prim"])
+    qnodes, leaves = read_blob(cs, s.n_colliders)
+    assert np.array_equal(qnodes, tree["qnodes"]["w"]), "quantised nodes (incl. WILD_BIT flags) differ from the host restatement"
+    assert (qnodes[:, 6:8] & 0x40000000).any()
+    rays = np.concatenate([synth.degenerate_rays(6000), synth.random_rays(20000, seed=5, extent=70), synth.axis_rays(2000, seed=6, extent=60)])
+    got = cs.get_raycasts(rays)
+    brute = port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8)
+    assert_raycast_equal(got, brute, "degenerate colliders vs brute force", nan_equal=True)
+    # the same scene without the boxes that swallow every ray at t = -inf (infinite / 1e30 scale), so that the other kinds decide
+    with np.errstate(invalid="ignore"):
+        keep = ~((boxes[:, 3:] - boxes[:, :3]) > 1e6).all(axis=1)
+    cs2 = CollisionSystem()
+    cs2.set_hierarchy(s.parent)
+    cs2.set_trs(s.pos, s.rot, s.scl)
+    cs2.set_colliders(s.collider_entity[keep], s.collider_aabb[keep])
+    cs2.on_update()
+    order2, boxes2 = cs2.leaf_order(), cs2.world_aabbs()
+    got2 = cs2.get_raycasts(rays)
+    assert_raycast_equal(got2, port.raycast_brute(s.collider_entity[keep][order2], boxes2[order2], rays, nthreads=8), "degenerate colliders (2) vs brute force", nan_equal=True)
+    if not with_nan:
+        assert 100 < got2["hit"].sum() < rays.shape[0] - 100
+        assert_raycast_equal(got2, reference_walk(cs2.bvh, rays, port), "degenerate colliders vs the reference's GetRaycast on the exported tree", nan_equal=True)
+        assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), "degenerate colliders (all) vs the reference's GetRaycast on the exported tree", nan_equal=True)
+    # refit-only frame keeps the flags
+    cs.on_update_refit()
+    assert_raycast_equal(cs.get_raycasts(rays), got, "refit frame", nan_equal=True)
+
+
+def test_degenerate_rays_vs_live_reference(CollisionSystem, port):
+    """Degenerate RAYS on a sane scene, every one against the reference: zero / denormal / infinite / NaN directions, NaN origin
+    coordinates (the reference's fminf / fmaxf then IGNORE that axis and the ray can hit), infinite and far-away origins."""
+    s = synth.uniform_boxes(3000, seed=51, extent=40, hmin=0.5, hmax=3.0)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    rays = synth.degenerate_rays(20000, seed=93, extent=45)
+    got = cs.get_raycasts(rays)
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    assert_raycast_equal(got, port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8), "degenerate rays vs brute force", nan_equal=True)
+    assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), "degenerate rays vs the reference's GetRaycast on the exported tree", nan_equal=True)
+    nan_origin = np.isnan(rays[:, :3]).any(axis=1) & ~np.isnan(rays[:, :3]).all(axis=1) & np.isfinite(rays[:, 3:]).all(axis=1)
+    assert got["hit"][nan_origin].sum() > 10, "rays with one NaN origin coordinate hit in the reference (that axis drops out)"
+
+
+def test_failed_update_keeps_a_consistent_tree(CollisionSystem, port):
+    """b2col_update must not leave a half-described tree behind when it fails.  Good update, then a collider set that
+    refers to an entity without a transform: the update fails with B2COL_ERR_INVALID and queries keep answering from the old tree."""
+    s = synth.uniform_boxes(20000, seed=77, extent=80)
+    rays = synth.random_rays(5000, seed=78, extent=90)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    before = cs.get_raycasts(rays)
+    assert before["hit"].sum() > 100
+    bad_entity = np.concatenate([s.collider_entity, np.array([s.n_entities + 5], np.uint32)])
+    cs.set_colliders(bad_entity, np.concatenate([s.collider_aabb, s.collider_aabb[:1]]))
+    with pytest.raises(capi.B2ColError) as ei:
+        cs.on_update()
+    assert ei.value.status == capi.ERR_INVALID
+    assert (cs.get_raycasts(rays).view(np.uint8) == before.view(np.uint8)).all(), "the previous tree must keep answering"
+    with pytest.raises(capi.B2ColError):
+        cs.on_update_refit()  # the collider set changed: no topology to refit
+    with pytest.raises(capi.B2ColError):
+        cs.bvh  # export needs a tree of the CURRENT collider set
+    cs.set_colliders(s.collider_entity, s.collider_aabb)
+    cs.on_update()
+    assert (cs.get_raycasts(rays).view(np.uint8) == before.view(np.uint8)).all()
+    # a malformed reference tree with a cycle is rejected instead of hanging k_trace_reftopo
+    bad = np.zeros(3, capi.NODE_DTYPE)
+    bad["index1"] = [1, 2, 0]  # 2 -> 0 -> 1 -> 2
+    bad["type2"] = 2
+    with pytest.raises(capi.B2ColError):
+        cs.upload_ref_bvh(bad)
+
+
 # ---------------------------------------------------------------------------------------------
 # radix sort and hierarchy at scale, duplicates
 # ---------------------------------------------------------------------------------------------
@@ -237,9 +358,8 @@ def test_config2_100k_camera_rays(CollisionSystem, port):
     cs.on_update()
     got = cs.get_raycasts(rays)
     exported = cs.bvh
-    # reference traversal (restated) of the exported tree on every 8th ray
-    sel = np.arange(0, rays.shape[0], 8)
-    assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), "config 2 vs reference traversal")
+    # the live reference's GetRaycast on the exported tree: every ray
+    assert_raycast_equal(got, reference_walk(exported, rays, port), "config 2 vs the reference's GetRaycast on the exported tree")
     # brute force on a sample
     order, boxes = cs.leaf_order(), cs.world_aabbs()
     sel = np.arange(0, rays.shape[0], 997)
@@ -266,8 +386,7 @@ def test_config3_1m_incoherent(CollisionSystem, port):
     assert (parts.view(np.uint8) == got.view(np.uint8)).all()
     # (3) reference traversal of the exported tree on a sample, (4) brute force on a smaller sample
     exported = cs.bvh
-    sel = np.arange(0, n_rays, 64)
-    assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), "config 3 vs reference traversal")
+    assert_raycast_equal(got, reference_walk(exported, rays, port), "config 3 vs the reference's GetRaycast on the exported tree (all rays)")
     order, boxes = cs.leaf_order(), cs.world_aabbs()
     sel = np.arange(0, n_rays, 8192)
     assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), "config 3 vs brute force")
@@ -305,8 +424,7 @@ def test_config5_clustered_skewed(CollisionSystem, port):
         parts = np.concatenate([cs.get_raycasts(rays[lo : lo + n_rays // 4]) for lo in range(0, n_rays, n_rays // 4)])
         assert (parts.view(np.uint8) == got.view(np.uint8)).all()
         exported = cs.bvh
-        sel = np.arange(0, n_rays, 64)
-        assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), f"config 5 ({bits_per_axis}) vs reference traversal")
+        assert_raycast_equal(got, reference_walk(exported, rays, port), f"config 5 ({bits_per_axis}) vs the reference's GetRaycast on the exported tree (all rays)")
         order, boxes = cs.leaf_order(), cs.world_aabbs()
         sel = np.arange(0, n_rays, 4096)
         assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), f"config 5 ({bits_per_axis}) vs brute force")
@@ -348,8 +466,7 @@ def test_config5_full_size_10m(CollisionSystem, port):
     order, boxes = cs.leaf_order(), cs.world_aabbs()
     sel = np.arange(0, 2 * m, 2 * m // 192)
     assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=16), "10M vs brute force")
-    sel = np.arange(0, 2 * m, 16)
-    assert_raycast_equal(got[sel], port.raycast_tree(cs.bvh, rays[sel], nthreads=16), "10M vs reference traversal of the exported tree")
+    assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), "10M vs the reference's GetRaycast on the exported tree (all rays)")
 
 
 def test_compact_top_levels(CollisionSystem, port, monkeypatch):
@@ -432,8 +549,7 @@ def test_config4_dynamic_frames(CollisionSystem, port, emu):
         boxes = cs.world_aabbs()
         assert (bits(boxes) == bits(want_boxes)).all(), f"frame {frame}: world AABBs"
         got = cs.get_raycasts(rays)
-        sel = np.arange(0, rays.shape[0], 10)
-        assert_raycast_equal(got[sel], port.raycast_tree(cs.bvh, rays[sel], nthreads=8), f"frame {frame}")
+        assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), f"frame {frame} vs the reference's GetRaycast on the exported tree (all rays)")
 
 
 def test_refit_only_frames(CollisionSystem, port):
@@ -464,8 +580,7 @@ def test_refit_only_frames(CollisionSystem, port):
         assert (cs.leaf_order() == order0).all(), "refit must not reorder leaves"
         got = cs.get_raycasts(rays)
         exported = cs.bvh
-        sel = np.arange(0, rays.shape[0], 8)
-        assert_raycast_equal(got[sel], port.raycast_tree(exported, rays[sel], nthreads=8), f"refit frame {frame} vs reference traversal")
+        assert_raycast_equal(got, reference_walk(exported, rays, port), f"refit frame {frame} vs the reference's GetRaycast on the exported tree (all rays)")
         bsel = np.arange(0, rays.shape[0], 200)
         brute = port.raycast_brute(s.collider_entity[order0], boxes[order0], rays[bsel], nthreads=8)
         assert_raycast_equal(got[bsel], brute, f"refit frame {frame} vs brute force")
@@ -742,3 +857,77 @@ def test_few_ray_calls_equal_batch(CollisionSystem):
     assert cs.stats()["kernel_launches"] - launches == k
     one = cs.get_raycast(rays[0, :3], rays[0, 3:])
     assert one.tobytes() == want[0].tobytes()
+
+
+# ---------------------------------------------------------------------------------------------
+# multi-GPU data plane (include/b2col.h "multi-GPU"): needs >= 2 visible GPUs (gpurun --gpus 2)
+# ---------------------------------------------------------------------------------------------
+needs_2_gpus = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 visible GPUs (gpurun --gpus N)")
+
+
+@needs_2_gpus
+def test_multi_gpu_one_process(port):
+    """One process driving every visible GPU (what engine_b200/shim does): b2col_comm_init_all, replicate the tree with one grouped
+    ncclBroadcast, sharded raycast with the gather fused into the trace kernels (peer stores into the destination's window), and
+    the host-buffer batch split across the GPUs.  EVERY rank's full slice is compared bitwise with a 1-GPU trace of the same rays."""
+    from engine_b200.collision import MultiGpu, shard_bounds
+
+    n_dev = min(torch.cuda.device_count(), 8)
+    s = synth.uniform_boxes(400_000, seed=31, extent=500.0)
+    n_rays = 3_000_007
+    rays = synth.random_rays(n_rays, seed=32, extent=520.0)
+    mg = MultiGpu(range(n_dev), use_cuda_graph=True)
+    mg.primary.set_scene(s)
+    mg.primary.on_update()
+    want = mg.primary.get_raycasts(rays)  # 1 GPU, whole batch
+    assert want["hit"].sum() > 1000
+    mg.replicate(0)
+    shards = []
+    for r in range(n_dev):
+        lo, hi = shard_bounds(n_rays, n_dev, r)
+        shards.append(torch.from_numpy(rays[lo:hi]).to(f"cuda:{r}"))
+    torch.cuda.synchronize()
+    for dst in (0, n_dev - 1):
+        addr = mg.raycast_gather(shards, n_rays, dst)
+        got = mg.systems[dst].read_raycasts(addr, n_rays)
+        assert (got.view(np.uint8) == want.view(np.uint8)).all(), f"gathered on rank {dst}: differs from the 1-GPU trace"
+    info = mg.primary.comm_info()
+    assert info["n_ranks"] == n_dev and info["single_process"] == 1 and info["gathers"] == 2
+    # every replica answers on its own too (the broadcast tree is complete)
+    for r in range(1, n_dev):
+        lo, hi = shard_bounds(n_rays, n_dev, r)
+        assert (mg.systems[r].get_raycasts(rays[lo:hi]).view(np.uint8) == want[lo:hi].view(np.uint8)).all()
+    # host buffers: slices uploaded / traced / downloaded by their own GPU, straight into the caller's array
+    got = mg.get_raycasts(rays)
+    assert (got.view(np.uint8) == want.view(np.uint8)).all()
+    small = mg.get_raycasts(rays[:1000])  # too small to split: one GPU
+    assert (small.view(np.uint8) == want[:1000].view(np.uint8)).all()
+    # a new frame on the primary, replicated again
+    s.pos[1:] += np.float32(0.5)
+    mg.primary.set_trs(s.pos, s.rot, s.scl)
+    mg.primary.on_update()
+    want2 = mg.primary.get_raycasts(rays)
+    mg.replicate(0)
+    addr = mg.raycast_gather(shards, n_rays, 0)
+    assert (mg.primary.read_raycasts(addr, n_rays).view(np.uint8) == want2.view(np.uint8)).all()
+    mg.close()
+
+
+@needs_2_gpus
+def test_multi_gpu_one_process_per_gpu():
+    """One process per GPU (torchrun, the way bench.py runs): tests/mp_comm_worker.py on every visible GPU — unique id over gloo,
+    b2col_comm_init_rank, the blob broadcast and the records-broadcast + local rebuild, the fused gather onto rank 0 and onto the last
+    rank, each compared bitwise with a 1-GPU trace."""
+    import socket
+    import subprocess
+    import sys
+
+    n_dev = min(torch.cuda.device_count(), 8)
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port_no = sk.getsockname()[1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n_dev}", "--master-addr", "127.0.0.1", "--master-port", str(port_no),
+           os.path.join(root, "tests", "mp_comm_worker.py"), "300000", "2000003"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MP_COMM_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
