@@ -754,7 +754,7 @@ static_assert(TRACE_SMEM_STACK % 2 == 0 && TRACE_SMEM_STACK >= 4, "spill granula
 // Shared memory of one trace block.  Everything is laid out [row][thread], so lane l always hits bank
 // l whatever row it addresses: every access is one conflict-free wavefront.
 #ifndef B2_STAGE_RAYS
-#define B2_STAGE_RAYS 12
+#define B2_STAGE_RAYS 11
 #endif
 constexpr int STAGE_RAYS = B2_STAGE_RAYS;  // finished Raycasts a warp stages per round on their way out (flush_finished)
 constexpr int STAGE_WORDS = 11;            // per staged ray: the nine words of the Raycast + its 64-bit index in the batch
@@ -795,23 +795,26 @@ __device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t*
     return lsp;  // sp = TRACE_SPILL in the caller
 }
 
-// Epilogue of the lanes whose ray has finished (`pending`), warp-cooperative.  A Raycast is 36 bytes at a 36-byte
-// stride: written by its own lane it costs nine 4-byte stores per lane, each instruction touching one sector per ray —
-// 7 % of the kernel's L1 wavefronts (ncu, profiles/r1_e) and, when `out` is a peer GPU's memory (b2col_comm_raycast_gather),
-// nine NVLink write packets of 4 bytes per ray.  Instead every finished lane packs its nine words into the warp's staging
+// Epilogue of the lanes whose ray has finished (`pending`).  A Raycast is 36 bytes at a 36-byte stride: written by its own
+// lane it costs nine 4-byte stores per lane, each instruction touching one sector per ray — 7 % of the kernel's L1
+// wavefronts (ncu, profiles/r1_e).  Into LOCAL memory that is nevertheless the fastest form (measured, profiles/r2_experiments.txt:
+// the warp-cooperative transposition below costs 2.5 % more in instructions than the wavefronts it saves: 1800 vs 1846 Mrays/s),
+// so STAGED is only chosen when `out` is a peer GPU's memory (b2col_comm_raycast_gather), where per-lane stores would become
+// nine NVLink write packets of 4 bytes per ray: every finished lane packs its nine words into the warp's staging
 // rows, ray after ray (stride 9 words: conflict-free), and the warp writes the staged words out 32 at a time — each
 // instruction covers ~3.5 whole Raycasts, contiguous 36-byte runs in global memory.  The staging area holds STAGE_RAYS rays
 // per warp (shared memory is what limits the kernel's occupancy); more finished lanes than that take another round.
+template <bool STAGED>
 __device__ __forceinline__ void flush_finished(TraceSmem& sm, int warp, int lane, uint32_t lt_mask, bool pending, const uint32_t* w9, unsigned long long my,
                                                b2col_raycast* __restrict__ out)
 {
-#ifdef B2_NO_STAGE  // dev variant (A/B timing): every lane writes its own Raycast, nine 4-byte stores at a 36-byte stride
-    if (pending) {
+    if (!STAGED) {  // local memory: every lane writes its own Raycast, nine 4-byte stores at a 36-byte stride
+        if (pending) {
 #pragma unroll
-        for (int k = 0; k < 9; ++k) reinterpret_cast<uint32_t*>(out)[9ull * my + k] = w9[k];
+            for (int k = 0; k < 9; ++k) reinterpret_cast<uint32_t*>(out)[9ull * my + k] = w9[k];
+        }
+        return;
     }
-    return;
-#endif
     unsigned pend = __ballot_sync(0xffffffffu, pending);
     if (pend == 0u) return;
     uint32_t* st = sm.stage[warp];
@@ -864,7 +867,7 @@ __device__ __forceinline__ void flush_finished(TraceSmem& sm, int warp, int lane
 // WILD: the tree holds leaves the grid cannot bound (hdr->has_wild; b2col_bvh.cuh WILD_BIT): flagged slots are always
 // entered and no ray is dismissed by its distance from the grid.  Chosen once per kernel, so that sane scenes run the
 // instantiation that never looks at the bit.
-template <bool COUNT, bool WILD>
+template <bool COUNT, bool WILD, bool STAGED>
 __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
                                            const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
                                            unsigned long long* counter, int fetch_threshold)
@@ -905,7 +908,7 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
         {
             uint32_t w9[9];
             if (pending) finish_raycast<DevOps>(w9, exact_ray(), best, leaves);
-            flush_finished(sm, warp, lane, lt_mask, pending, w9, my, out);
+            flush_finished<STAGED>(sm, warp, lane, lt_mask, pending, w9, my, out);
             pending = false;
         }
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -989,15 +992,15 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
     }
 }
 
-template <bool COUNT>
+template <bool COUNT, bool STAGED>
 __global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
 k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
              const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
              unsigned long long* counter, int fetch_threshold)
 {
     __shared__ TraceSmem sm;
-    if (hdr->has_wild) trace_body<COUNT, true>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
-    else trace_body<COUNT, false>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
+    if (hdr->has_wild) trace_body<COUNT, true, STAGED>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
+    else trace_body<COUNT, false, STAGED>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
 }
 
 // Same query, walking an uploaded reference-format tree with the reference's exact semantics.
@@ -1262,7 +1265,7 @@ inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
         if (s_ != B2COL_OK) return s_;      \
     } while (0)
 
-b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode)
+b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode, bool remote_out = false)
 {
     if (n == 0) return B2COL_OK;
     const bool count = mode == B2COL_MODE_LBVH_COUNT;
@@ -1280,7 +1283,7 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
         CU(cudaMemsetAsync(ctx->d_counter.p, 0, 16, ctx->stream));
         const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
         if (count) {
-            LAUNCH(ctx, k_trace_lbvh<true>, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+            LAUNCH(ctx, (k_trace_lbvh<true, false>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
                    blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
             unsigned long long v = 0;
             CU(cudaMemcpyAsync(&v, ctx->d_counter.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1289,8 +1292,12 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
             ctx->counted_rays += n;
         }
         else {
-            LAUNCH(ctx, k_trace_lbvh<false>, grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
-                   blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+            if (remote_out)
+                LAUNCH(ctx, (k_trace_lbvh<false, true>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                       blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+            else
+                LAUNCH(ctx, (k_trace_lbvh<false, false>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                       blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
         }
     }
     else if (mode == B2COL_MODE_REFTOPO) {
@@ -1346,7 +1353,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         int sms = 148, per_sm = 8;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         c->n_sm = sms;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh<false>, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_lbvh<false, false>, TRACE_BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 8;
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_E2E_FIRST_CHUNK")) c->e2e_first_chunk = std::max<size_t>(1024, (size_t)atoll(e));
@@ -1913,7 +1920,7 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
         const b2col_ray* dr = static_cast<const b2col_ray*>(ctx->d_small);
         b2col_raycast* dout = reinterpret_cast<b2col_raycast*>(const_cast<b2col_ray*>(dr) + b2col_ctx::SMALL_MAX);
         memcpy(hr, h_rays, n * sizeof(b2col_ray));
-        LAUNCH(ctx, k_trace_lbvh<false>, 1, TRACE_BLOCK, dr, (unsigned long long)n, dout, blob_hdr(ctx), blob_qnodes(ctx), blob_leaves(ctx, ctx->tree_leaves), ctx->T,
+        LAUNCH(ctx, (k_trace_lbvh<false, false>), 1, TRACE_BLOCK, dr, (unsigned long long)n, dout, blob_hdr(ctx), blob_qnodes(ctx), blob_leaves(ctx, ctx->tree_leaves), ctx->T,
                ctx->d_small_counters.as<unsigned long long>() + ctx->small_next++, ctx->fetch_threshold);
         CU(cudaStreamSynchronize(ctx->stream));
         memcpy(h_out, ho, n * sizeof(b2col_raycast));

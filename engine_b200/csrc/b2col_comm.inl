@@ -116,6 +116,7 @@ struct b2col_comm_state {
     bool win_fallback = false;   // the window could not be mapped somewhere: every rank sends its slice with NCCL instead
     void* d_word = nullptr;      // 64 bytes of device scratch: completion word, IPC handle exchange
     cudaEvent_t done = nullptr;  // single-process completion
+    bool stage_remote = true;    // B2COL_REMOTE_STAGE=0: plain per-lane stores into the peer window too (A/B timing)
     uint64_t gathers = 0, replications = 0;
 };
 
@@ -155,6 +156,7 @@ b2col_status comm_attach(b2col_ctx* ctx, b2_ncclComm_t comm, int n_ranks, int ra
     CU(cudaMemsetAsync(c->d_word, 0, 64, ctx->stream));
     CU(cudaEventCreateWithFlags(&c->done, cudaEventDisableTiming));
     if (const char* e = getenv("B2COL_GATHER")) c->win_fallback = !strcmp(e, "nccl");  // A/B: force the send / recv gather
+    if (const char* e = getenv("B2COL_REMOTE_STAGE")) c->stage_remote = atoi(e) != 0;
     return B2COL_OK;
 }
 
@@ -168,11 +170,12 @@ b2col_status comm_ensure_window(b2col_ctx* ctx, size_t bytes, int dst)
     const size_t want = bytes + bytes / 8 + 4096;
     if (!c->peers.empty()) {  // one process: the first context to get here allocates on dst's device, the others read the pointer
         b2col_ctx* owner = c->peers[(size_t)dst];
+        if (!owner || !owner->comm) return fail(ctx, B2COL_ERR_STATE, "the destination rank's context has been destroyed");
         b2col_comm_state* oc = owner->comm;
         if (!(oc->win && oc->win_dst == dst && oc->win_bytes >= bytes)) {
             comm_release_window(owner);
             for (b2col_ctx* p : c->peers)
-                if (p != owner && p->comm->win) {  // stale views of the old window
+                if (p && p != owner && p->comm && p->comm->win) {  // stale views of the old window
                     cudaSetDevice(p->device);
                     cudaStreamSynchronize(p->stream);
                     p->comm->win = nullptr;
@@ -255,7 +258,8 @@ b2col_status comm_enqueue_shard(b2col_ctx* ctx, const b2col_ray* d_rays_shard, s
         GUARD(ensure(ctx, ctx->d_hits, (hi - lo) * sizeof(b2col_raycast)));
         return enqueue_trace(ctx, d_rays_shard, hi - lo, ctx->d_hits.as<b2col_raycast>(), B2COL_MODE_LBVH);
     }
-    return enqueue_trace(ctx, d_rays_shard, hi - lo, static_cast<b2col_raycast*>(c->win) + lo, B2COL_MODE_LBVH);
+    // the window is another GPU's memory on every rank but dst: there the kernel writes whole staged Raycasts (see flush_finished)
+    return enqueue_trace(ctx, d_rays_shard, hi - lo, static_cast<b2col_raycast*>(c->win) + lo, B2COL_MODE_LBVH, c->rank != dst && c->stage_remote);
 }
 
 // fallback gather: slices travel as NCCL point-to-point messages after the trace (caller wraps this in a group when one
@@ -386,7 +390,7 @@ b2col_status b2col_comm_finalize(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     if (!c->peers.empty() && c->win && c->rank == c->win_dst) {  // single process: the other ranks hold plain copies of this pointer
         for (b2col_ctx* p : c->peers)
-            if (p != ctx && p->comm && p->comm->win == c->win) {
+            if (p && p != ctx && p->comm && p->comm->win == c->win) {
                 cudaSetDevice(p->device);
                 cudaStreamSynchronize(p->stream);
                 p->comm->win = nullptr;
@@ -396,7 +400,7 @@ b2col_status b2col_comm_finalize(b2col_ctx* ctx)
     }
     if (c->peers.empty() || c->rank == c->win_dst) comm_release_window(ctx);
     for (b2col_ctx* p : c->peers)
-        if (p != ctx && p->comm) {
+        if (p && p != ctx && p->comm) {
             auto& v = p->comm->peers;
             for (auto& q : v)
                 if (q == ctx) q = nullptr;
