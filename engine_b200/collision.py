@@ -78,6 +78,25 @@ class CollisionSystem:
         scl = np.ascontiguousarray(scl, dtype=np.float32).reshape(n + 1, 3)
         self._ck(self.lib.b2col_set_trs(self.h, n, ptr(pos), ptr(rot), ptr(scl)))
 
+    def update_trs_rows(self, entity, pos, rot_xyzw, scl) -> None:
+        """sparse update: rows entity[i] of the device TRS arrays take pos / rot / scl [i] (b2col_update_trs_rows)"""
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        k = entity.shape[0]
+        pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(k, 3)
+        rot = np.ascontiguousarray(rot_xyzw, dtype=np.float32).reshape(k, 4)
+        scl = np.ascontiguousarray(scl, dtype=np.float32).reshape(k, 3)
+        self._ck(self.lib.b2col_update_trs_rows(self.h, k, ptr(entity), ptr(pos), ptr(rot), ptr(scl)))
+
+    def world_rows(self, entity) -> np.ndarray:
+        """world matrices of the given entities, gathered on the device (b2col_fetch_world_rows)"""
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        out = C.c_void_p()
+        self._ck(self.lib.b2col_fetch_world_rows(self.h, entity.shape[0], ptr(entity), C.byref(out)))
+        if entity.shape[0] == 0:
+            return np.zeros((0, 16), np.float32)
+        buf = (C.c_float * (16 * entity.shape[0])).from_address(out.value)
+        return np.frombuffer(buf, dtype=np.float32).reshape(-1, 16).copy()
+
     def set_trs_device(self, d_pos, d_rot_xyzw, d_scl) -> None:
         """torch CUDA tensors (float32, contiguous, (E+1,3)/(E+1,4)/(E+1,3)); enqueued, not waited for."""
         self._ck(self.lib.b2col_set_trs_device(self.h, self.n_entities, ptr(d_pos), ptr(d_rot_xyzw), ptr(d_scl)))

@@ -346,6 +346,31 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
     bounds_reduce(cmin, cmax, bounds);
 }
 
+// Sparse TRS update (b2col_commit_trs_rows): rows ids[i] of the entity-indexed SoA take the packed values i.  One thread per row.
+__global__ void __launch_bounds__(256)
+k_scatter_trs(uint32_t n, const uint32_t* __restrict__ ids, const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3,
+              float* d_pos, float4* d_rot, float* d_scl)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t e = ids[i];
+    d_rot[e] = rot4[i];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        d_pos[3 * e + k] = pos3[3 * (size_t)i + k];
+        d_scl[3 * e + k] = scl3[3 * (size_t)i + k];
+    }
+}
+
+// world_matrix write-back of the rows that can have moved (b2col_fetch_world_rows): packed[i] = world[ids[i]].  Four threads per row.
+__global__ void __launch_bounds__(256)
+k_gather_world(uint32_t n, const uint32_t* __restrict__ ids, const float4* __restrict__ world, float4* __restrict__ packed)
+{
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 4 * (size_t)n) return;
+    packed[t] = world[4 * (size_t)ids[t >> 2] + (t & 3)];
+}
+
 // Header fields every build needs besides the bounds: leaf / node counts and the quantisation grid of the
 // traversal nodes, derived from the box bounds k_refit reduced into the header.  One thread.
 __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t n, float T)
@@ -1153,6 +1178,12 @@ struct b2col_ctx {
     bool no_small_path = false;  // dev: B2COL_NO_SMALL=1 sends few-ray calls through the copy path (A/B timing)
     bool no_fuse = false;  // dev: B2COL_NO_FUSE=1 keeps propagate and refit as separate kernels (A/B timing)
     bool phase_timing = false;
+    // sparse TRS rows / world-matrix rows (the drop-in TransformSystem): page-locked host staging + device staging
+    void* h_rows = nullptr;
+    size_t h_rows_cap = 0;
+    DevBuf d_rows;
+    cudaEvent_t rows_ev = nullptr;  // the last copy out of / into h_rows has completed
+    uint32_t rows_staged = 0;
     void* h_import_hdr = nullptr;  // page-locked copy of the header of the last imported blob, checked by b2col_sync
     bool import_check_pending = false;
     uint32_t import_check_leaves = 0;
@@ -1393,6 +1424,9 @@ void b2col_destroy(b2col_ctx* ctx)
         if (g.exec) cudaGraphExecDestroy(g.exec);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_import_hdr) cudaFreeHost(ctx->h_import_hdr);
+    if (ctx->h_rows) cudaFreeHost(ctx->h_rows);
+    if (ctx->rows_ev) cudaEventDestroy(ctx->rows_ev);
+    release(ctx->d_rows);
     release(ctx->d_small_counters);
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
@@ -1491,6 +1525,99 @@ b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_p
 b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3)
 {
     return set_trs_common(ctx, n_entities, d_pos3, d_rot_xyzw, d_scl3, cudaMemcpyDeviceToDevice);
+}
+
+// page-locked staging of at least `bytes`, safe to overwrite (the copies that last used it have completed)
+static b2col_status rows_staging(b2col_ctx* ctx, size_t bytes)
+{
+    if (!ctx->rows_ev) CU(cudaEventCreateWithFlags(&ctx->rows_ev, cudaEventDisableTiming));
+    else CU(cudaEventSynchronize(ctx->rows_ev));
+    if (bytes > ctx->h_rows_cap) {
+        if (ctx->h_rows) CU(cudaFreeHost(ctx->h_rows));
+        ctx->h_rows = nullptr;
+        ctx->h_rows_cap = 0;
+        const size_t want = bytes + bytes / 4 + 4096;
+        CU(cudaHostAlloc(&ctx->h_rows, want, cudaHostAllocDefault));
+        ctx->h_rows_cap = want;
+    }
+    return ensure(ctx, ctx->d_rows, bytes);
+}
+// layout of a staged batch of n rows: [ids u32 x n | pad to 16 | rot float4 x n | pos float3 x n | scl float3 x n]
+static inline size_t rows_off_rot(uint32_t n) { return ((size_t)n * 4 + 15) & ~(size_t)15; }
+static inline size_t rows_bytes(uint32_t n) { return rows_off_rot(n) + (size_t)n * 40; }
+
+b2col_status b2col_stage_trs_rows(b2col_ctx* ctx, uint32_t n_rows, uint32_t** h_entity, float** h_pos3, float** h_rot_xyzw, float** h_scl3)
+{
+    if (!ctx || !h_entity || !h_pos3 || !h_rot_xyzw || !h_scl3) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_trs) return fail(ctx, B2COL_ERR_STATE, "b2col_set_trs must have uploaded the full arrays once");
+    CU(cudaSetDevice(ctx->device));
+    GUARD(rows_staging(ctx, rows_bytes(n_rows)));
+    char* base = static_cast<char*>(ctx->h_rows);
+    *h_entity = reinterpret_cast<uint32_t*>(base);
+    *h_rot_xyzw = reinterpret_cast<float*>(base + rows_off_rot(n_rows));
+    *h_pos3 = *h_rot_xyzw + 4 * (size_t)n_rows;
+    *h_scl3 = *h_pos3 + 3 * (size_t)n_rows;
+    ctx->rows_staged = n_rows;
+    return B2COL_OK;
+}
+
+b2col_status b2col_commit_trs_rows(b2col_ctx* ctx, uint32_t n_rows)
+{
+    if (!ctx) return B2COL_ERR_INVALID;
+    if (n_rows > ctx->rows_staged) return fail(ctx, B2COL_ERR_STATE, "%u rows committed, %u staged", n_rows, ctx->rows_staged);
+    const uint32_t staged = ctx->rows_staged;
+    ctx->rows_staged = 0;
+    if (n_rows == 0) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t* ids = static_cast<const uint32_t*>(ctx->h_rows);
+    for (uint32_t i = 0; i < n_rows; ++i)
+        if (ids[i] == 0u || ids[i] > ctx->n_entities) return fail(ctx, B2COL_ERR_INVALID, "row %u names entity %u of %u", i, ids[i], ctx->n_entities);
+    CU(cudaMemcpyAsync(ctx->d_rows.p, ctx->h_rows, rows_bytes(staged), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaEventRecord(ctx->rows_ev, ctx->stream));
+    const char* d = static_cast<const char*>(ctx->d_rows.p);
+    const float4* rot = reinterpret_cast<const float4*>(d + rows_off_rot(staged));
+    const float* pos = reinterpret_cast<const float*>(rot + staged);
+    const float* scl = pos + 3 * (size_t)staged;
+    LAUNCH(ctx, k_scatter_trs, cdiv(n_rows, 256), 256, n_rows, reinterpret_cast<const uint32_t*>(d), pos, rot, scl, ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(),
+           ctx->d_scl.as<float>());
+    ctx->world_external = false;
+    ctx->world_fresh = false;
+    return B2COL_OK;
+}
+
+b2col_status b2col_update_trs_rows(b2col_ctx* ctx, uint32_t n_rows, const uint32_t* h_entity, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3)
+{
+    if (!ctx || (n_rows && (!h_entity || !h_pos3 || !h_rot_xyzw || !h_scl3))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    uint32_t* e;
+    float *p, *r, *s;
+    GUARD(b2col_stage_trs_rows(ctx, n_rows, &e, &p, &r, &s));
+    memcpy(e, h_entity, (size_t)n_rows * 4);
+    memcpy(p, h_pos3, (size_t)n_rows * 12);
+    memcpy(r, h_rot_xyzw, (size_t)n_rows * 16);
+    memcpy(s, h_scl3, (size_t)n_rows * 12);
+    return b2col_commit_trs_rows(ctx, n_rows);
+}
+
+b2col_status b2col_fetch_world_rows(b2col_ctx* ctx, uint32_t n_rows, const uint32_t* h_entity, const float** h_rows16)
+{
+    if (!ctx || !h_rows16 || (n_rows && !h_entity)) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    *h_rows16 = nullptr;
+    if (n_rows == 0) return B2COL_OK;
+    if (!ctx->d_world.p) return fail(ctx, B2COL_ERR_STATE, "no world matrices on the device: call b2col_propagate / b2col_update first");
+    for (uint32_t i = 0; i < n_rows; ++i)
+        if (h_entity[i] > ctx->n_entities) return fail(ctx, B2COL_ERR_INVALID, "row %u names entity %u of %u", i, h_entity[i], ctx->n_entities);
+    CU(cudaSetDevice(ctx->device));
+    const size_t ids_bytes = ((size_t)n_rows * 4 + 63) & ~(size_t)63;
+    GUARD(rows_staging(ctx, ids_bytes + (size_t)n_rows * 64));
+    memcpy(ctx->h_rows, h_entity, (size_t)n_rows * 4);
+    char* d = static_cast<char*>(ctx->d_rows.p);
+    CU(cudaMemcpyAsync(d, ctx->h_rows, (size_t)n_rows * 4, cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_gather_world, cdiv(4 * (size_t)n_rows, 256), 256, n_rows, reinterpret_cast<const uint32_t*>(d), ctx->d_world.as<float4>(), reinterpret_cast<float4*>(d + ids_bytes));
+    CU(cudaMemcpyAsync(static_cast<char*>(ctx->h_rows) + ids_bytes, d + ids_bytes, (size_t)n_rows * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaEventRecord(ctx->rows_ev, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    *h_rows16 = reinterpret_cast<const float*>(static_cast<char*>(ctx->h_rows) + ids_bytes);
+    return B2COL_OK;
 }
 
 b2col_status b2col_set_world_matrices(b2col_ctx* ctx, uint32_t n_entities, const float* h_world16)

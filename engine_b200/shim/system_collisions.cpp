@@ -38,44 +38,70 @@ void CollisionSystem::onComponentInsert(Entity entity)
     ++colliders_inserted_;
 }
 
+// Did any collider's local AABB change since it was uploaded?  ColliderComponent has no dirty flag and the reference re-reads
+// every box every frame (src/system_collisions.cpp:125-127), so the check is exact — but it runs as memcmp over RUNS of
+// consecutive entity IDs (the component array is dense in entity ID, include/ecs.h:28-49, and device_boxes_ is in the same
+// order), not as a per-entity component lookup: ~2 ms per million colliders instead of ~100.
+bool CollisionSystem::BoxesUnchanged(const ColliderComponent* base) const
+{
+    static_assert(sizeof(ColliderComponent) == sizeof(AABB), "ColliderComponent is its AABB: runs of entities are runs of boxes");
+    const std::size_t n = device_entities_.size();
+    std::size_t i = 0;
+    while (i < n) {
+        std::size_t j = i + 1;
+        while (j < n && device_entities_[j] == device_entities_[j - 1] + 1u) ++j;
+        if (std::memcmp(&base[device_entities_[i]], &device_boxes_[i], (j - i) * sizeof(AABB)) != 0) return false;
+        i = j;
+    }
+    return true;
+}
+
 void CollisionSystem::onUpdate(float ts)
 {
     (void)ts;
     // world matrices of every entity, indexed by entity ID (row 0 unused) — what TransformSystem just wrote
     const uint32_t n_entities = m_scene->next_entity_id_ - 1u;
-    gather_entities_.clear();
-    gather_boxes_.clear();
-    for (Entity entity : m_entities) {  // ascending IDs (std::set), the reference's own iteration order
-        const auto* c = m_scene->GetComponent<ColliderComponent>(entity);
-        gather_entities_.push_back(entity);
-        gather_boxes_.push_back(c->aabb);
+    const ColliderComponent* cbase = nullptr;
+    if (!m_entities.empty()) {
+        const Entity first = *m_entities.begin();
+        cbase = m_scene->GetComponent<ColliderComponent>(first) - first;  // one lookup: the array is a dense vector indexed by entity ID
+    }
+    // the collider set only ever grows (the reference has no component removal, include/ecs.h:41-44), and only through
+    // onComponentInsert: the sorted entity list is rebuilt when that fired, the boxes are compared every
+    // collider_check_interval-th frame
+    bool same_set = have_build_ && seen_inserts_ == colliders_inserted_ && device_entities_.size() == m_entities.size();
+    if (same_set && cbase && collider_check_interval != 0 && ++frames_since_check_ >= collider_check_interval) {
+        frames_since_check_ = 0;
+        same_set = BoxesUnchanged(cbase);
+    }
+    if (!same_set) {
+        device_entities_.assign(m_entities.begin(), m_entities.end());  // ascending IDs (std::set), the reference's own iteration order
+        device_boxes_.resize(device_entities_.size());
+        for (std::size_t i = 0; i < device_entities_.size(); ++i) device_boxes_[i] = cbase[device_entities_[i]].aabb;
+        seen_inserts_ = colliders_inserted_;
+        frames_since_check_ = 0;
     }
     if (shared_->transforms_on_device && shared_->n_entities == n_entities) {
         // the drop-in TransformSystem of this Scene has already put this frame's world matrices on the device
     }
-    else {
+    else if (!m_entities.empty()) {
         // reference TransformSystem on the CPU: upload TransformComponent::world_matrix.  Only collider entities'
         // matrices are read by the refit, so only those rows are filled.
         gather_world_.resize(16u * (static_cast<std::size_t>(n_entities) + 1u));
-        for (Entity entity : gather_entities_) {
-            const auto* t = m_scene->GetComponent<TransformComponent>(entity);
-            std::memcpy(&gather_world_[16u * entity], &t->world_matrix, 64);
-        }
+        const Entity first = device_entities_.front();
+        const TransformComponent* tbase = m_scene->GetComponent<TransformComponent>(first) - first;
+        for (Entity entity : device_entities_) std::memcpy(&gather_world_[16u * entity], &tbase[entity].world_matrix, 64);
         Check(b2col_set_world_matrices(ctx_, n_entities, gather_world_.data()), "b2col_set_world_matrices");
     }
-    const bool same_set = have_build_ && gather_entities_ == device_entities_ &&
-                          (gather_boxes_.empty() || std::memcmp(gather_boxes_.data(), device_boxes_.data(), gather_boxes_.size() * sizeof(AABB)) == 0);
     if (same_set && rebuild_interval > 1 && frames_since_build_ + 1 < rebuild_interval) {
         Check(b2col_refit(ctx_), "b2col_refit");
         ++frames_since_build_;
     }
     else {
         if (!same_set) {
-            Check(b2col_set_colliders(ctx_, static_cast<uint32_t>(gather_entities_.size()), gather_entities_.data(),
-                                      reinterpret_cast<const b2col_aabb*>(gather_boxes_.data())),
+            Check(b2col_set_colliders(ctx_, static_cast<uint32_t>(device_entities_.size()), device_entities_.data(),
+                                      reinterpret_cast<const b2col_aabb*>(device_boxes_.data())),
                   "b2col_set_colliders");
-            device_entities_ = gather_entities_;
-            device_boxes_ = gather_boxes_;
         }
         Check(b2col_update(ctx_), "b2col_update");
         have_build_ = true;
@@ -99,7 +125,7 @@ Raycast CollisionSystem::GetRaycast(Ray ray)
 
 void CollisionSystem::SyncDebugBvh()
 {
-    bvh_.resize(2u * gather_entities_.size() + 1u);
+    bvh_.resize(2u * device_entities_.size() + 1u);
     std::size_t n = 0;
     Check(b2col_export_bitreenode(ctx_, reinterpret_cast<b2col_bitreenode*>(bvh_.data()), bvh_.size(), &n), "b2col_export_bitreenode");
     bvh_.resize(n);

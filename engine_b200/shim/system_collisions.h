@@ -77,16 +77,21 @@ class CollisionSystem : public System {
     // the previous frame's always rebuilds.  Query results do not depend on this setting except for the winner
     // among exactly tied hits.
     unsigned rebuild_interval = 1;
+    // ColliderComponent::aabb is compared with the uploaded copy every collider_check_interval-th frame (1 = every frame, the
+    // reference's semantics: it re-reads every box every frame; 0 = never: boxes are immutable once added).  New colliders are
+    // always picked up at once (onComponentInsert).
+    unsigned collider_check_interval = 1;
 
    private:
     struct B2colSceneCtx* shared_ = nullptr;
     b2col_ctx* ctx_ = nullptr;
     std::size_t colliders_inserted_ = 0;
-    std::vector<uint32_t> gather_entities_;
-    std::vector<AABB> gather_boxes_;
+    std::size_t seen_inserts_ = 0;
     std::vector<float> gather_world_;
-    std::vector<uint32_t> device_entities_;  // the collider set currently on the device
-    std::vector<AABB> device_boxes_;
+    std::vector<uint32_t> device_entities_;  // the collider set currently on the device, ascending entity IDs
+    std::vector<AABB> device_boxes_;         // ... and its local boxes, same order
+    unsigned frames_since_check_ = 0;
+    bool BoxesUnchanged(const ColliderComponent* base) const;
     unsigned frames_since_build_ = 0;
     bool have_build_ = false;
     void Check(int status, const char* what) const;

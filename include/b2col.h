@@ -131,6 +131,15 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
 b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3);
 /* Same, from device memory (async on the ctx stream; buffers must stay valid until b2col_sync). */
 b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3);
+/* Sparse TRS update for frames in which few entities moved (dirty tracking through
+ * TransformComponent::is_static, reference include/component_transform.h:24): row h_entity[i] of the device arrays takes
+ * pos / rot / scl [i]; everything else keeps the values of the last b2col_set_trs.  44 bytes per moved entity cross PCIe
+ * instead of 44 bytes per entity.  Enqueued; the caller's arrays are free on return.
+ * The _stage / _commit pair is the zero-copy form: _stage hands out page-locked arrays of n_rows rows owned by the ctx,
+ * the caller gathers its AoS components straight into them, _commit(n <= n_rows) uploads and scatters them. */
+b2col_status b2col_update_trs_rows(b2col_ctx* ctx, uint32_t n_rows, const uint32_t* h_entity, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3);
+b2col_status b2col_stage_trs_rows(b2col_ctx* ctx, uint32_t n_rows, uint32_t** h_entity, float** h_pos3, float** h_rot_xyzw, float** h_scl3);
+b2col_status b2col_commit_trs_rows(b2col_ctx* ctx, uint32_t n_rows);
 /* Alternative to hierarchy+TRS when the caller keeps the reference's CPU TransformSystem:
  * upload TransformComponent::world_matrix directly (rows 0..n_entities, 16 floats each);
  * b2col_update then skips propagation. */
@@ -183,6 +192,10 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
 /* ---- read-back (parity tests; world_matrix write-back for MeshRenderSystem) ------------------ */
 /* rows first_entity .. first_entity+count-1, 16 floats each, column-major */
 b2col_status b2col_get_world_matrices(b2col_ctx* ctx, uint32_t first_entity, uint32_t count, float* h_out16);
+/* world_matrix write-back of the rows that can have moved (TransformComponent::world_matrix, read by MeshRenderSystem,
+ * reference src/system_mesh_render.cpp:62): *h_rows16 = n_rows x 16 floats, row i = world matrix of h_entity[i], in
+ * page-locked memory owned by the ctx (valid until the next *_rows call).  Gathered on the device, one D2H copy. */
+b2col_status b2col_fetch_world_rows(b2col_ctx* ctx, uint32_t n_rows, const uint32_t* h_entity, const float** h_rows16);
 /* world AABBs in the order colliders were given to b2col_set_colliders */
 b2col_status b2col_get_world_aabbs(b2col_ctx* ctx, b2col_aabb* h_out);
 /* collider indices (into the b2col_set_colliders order) in BVH leaf order == Morton order ==

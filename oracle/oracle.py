@@ -212,6 +212,19 @@ class RefEngine:
         pos, rot, scl = _f32(pos, (n, 3)), _f32(rot_xyzw, (n, 4)), _f32(scl, (n, 3))
         self.lib.refh_set_trs(self.h, C.c_size_t(n), _p(entity), _p(pos), _p(rot), _p(scl))
 
+    def set_static(self, entity, is_static: bool = True) -> None:
+        """TransformComponent::is_static of the given entities (reference include/component_transform.h:24)"""
+        entity = np.ascontiguousarray(entity, dtype=np.uint32)
+        self.lib.refh_set_static(self.h, C.c_size_t(entity.shape[0]), _p(entity), C.c_int(1 if is_static else 0))
+
+    SHIM_OPTIONS = {"collider_check_interval": 0, "rebuild_interval": 1, "skip_static_rows": 2, "write_back_world_matrices": 3, "static_rescan_interval": 4,
+                    "full_uploads": 10, "sparse_uploads": 11}
+
+    def shim_option(self, name: str, value: int = 0) -> int:
+        """knobs / counters of the drop-in shims (no-op in the reference build)"""
+        self.lib.refh_shim_option.restype = C.c_long
+        return int(self.lib.refh_shim_option(self.h, C.c_int(self.SHIM_OPTIONS[name]), C.c_long(value)))
+
     def scene_update(self) -> float:
         return float(self.lib.refh_scene_update(self.h))
 

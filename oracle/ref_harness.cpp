@@ -98,6 +98,38 @@ void refh_set_trs(void* h, size_t n, const uint32_t* entity, const float* pos3, 
     }
 }
 
+// TransformComponent::is_static (include/component_transform.h:24): set by loadGLTF for static scenes; the reference's own
+// TransformSystem / CollisionSystem ignore it, the drop-in TransformSystem uploads such rows once.
+void refh_set_static(void* h, size_t n, const uint32_t* entity, int is_static)
+{
+    auto* H = static_cast<Harness*>(h);
+    for (size_t i = 0; i < n; ++i) H->scene.GetTransform(entity[i])->is_static = is_static != 0;
+}
+
+// knobs / counters of the drop-in shims (no-ops in the reference build). key: 0 collider_check_interval, 1 rebuild_interval,
+// 2 skip_static_rows, 3 write_back_world_matrices, 4 static_rescan_interval; returns 10: full uploads, 11: sparse uploads
+long refh_shim_option(void* h, int key, long value)
+{
+    auto* H = static_cast<Harness*>(h);
+    (void)H;
+    (void)key;
+    (void)value;
+#ifdef B2COL_DROPIN
+    auto* cs = H->scene.GetSystem<CollisionSystem>();
+    if (key == 0) cs->collider_check_interval = static_cast<unsigned>(value);
+    if (key == 1) cs->rebuild_interval = static_cast<unsigned>(value);
+#ifdef B2COL_DROPIN_TRANSFORM
+    auto* ts = H->scene.GetSystem<TransformSystem>();
+    if (key == 2) ts->skip_static_rows = value != 0;
+    if (key == 3) ts->write_back_world_matrices = value != 0;
+    if (key == 4) ts->static_rescan_interval = static_cast<unsigned>(value);
+    if (key == 10) return static_cast<long>(ts->full_uploads);
+    if (key == 11) return static_cast<long>(ts->sparse_uploads);
+#endif
+#endif
+    return 0;
+}
+
 // Full frame: Scene::Update (src/scene.cpp:59-66) = Transform + Collision (refit + BuildNode).
 // Returns seconds.
 double refh_scene_update(void* h)

@@ -692,6 +692,78 @@ def test_dropin_transform_and_collision_shims_inside_reference_scene(port):
             e.scene_update()
 
 
+@pytest.mark.skipif(not (Dropin2Engine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_dropin_sparse_updates_static_and_moving_entities(port):
+    """The drop-in pair at work on a mostly static scene (dirty tracking through is_static): after the first
+    frame only the non-static entities are read and uploaded (b2col_stage/commit_trs_rows) and only they and their descendants get
+    world_matrix written back (b2col_fetch_world_rows) — static CHILDREN of moving roots included.  Every frame: world_matrix of
+    every entity bit-equal to the unmodified reference's, raycasts equal; entities and colliders added mid-run, a collider box
+    edited in place and a dynamic entity turned static are all picked up."""
+    s = synth.hierarchy_scene(6000, 60, seed=19, extent=200)
+    E = s.n_entities
+    ids = np.arange(1, E + 1, dtype=np.uint32)
+    roots = ids[:60]
+    rng = np.random.default_rng(3)
+    moving_roots = roots[::3]                                        # 20 roots move; their (static-flagged) children follow
+    loose = np.sort(rng.choice(np.arange(61, E + 1), 400, replace=False)).astype(np.uint32)  # plus 400 non-static colliders
+    dynamic = np.union1d(moving_roots, loose).astype(np.uint32)
+    static = np.setdiff1d(ids, dynamic)
+    rays = np.concatenate([synth.random_rays(6000, seed=98, extent=230, normalised=False), synth.axis_rays(500, seed=99, extent=200)])
+    engines = []
+    for cls in (RefEngine, Dropin2Engine):
+        e = cls()
+        e.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+        e.add_colliders(s.collider_entity, s.collider_aabb)
+        e.set_static(static, True)
+        e.scene_update()
+        engines.append(e)
+    ref, drop = engines
+
+    def check(what, all_ids):
+        assert (bits(drop.world_matrices(all_ids)) == bits(ref.world_matrices(all_ids))).all(), f"world_matrix differs: {what}"
+        ent, box = port.tree_leaves_dfs(drop.bvh())
+        _, ties = port.raycast_brute(ent, box, rays, nthreads=4, want_ties=True)
+        assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), what, ignore_entity_on=ties > 0)
+
+    check("first frame", ids)
+    pos, rot = s.pos.copy(), s.rot.copy()
+    for frame in range(4):
+        pos[dynamic] += rng.uniform(-1.0, 1.0, (dynamic.shape[0], 3)).astype(np.float32)
+        rot[moving_roots] = synth.random_unit_quats(rng, moving_roots.shape[0])
+        for e in engines:
+            e.set_trs(dynamic, pos[dynamic], rot[dynamic], s.scl[dynamic])
+            e.scene_update()
+        check(f"sparse frame {frame}", ids)
+    assert drop.shim_option("full_uploads") == 1 and drop.shim_option("sparse_uploads") == 4
+    # new entities + colliders mid-run (a full upload), then sparse frames again
+    new_parent = np.array([0, int(moving_roots[0]), int(moving_roots[0])], np.uint32)
+    new_pos = np.array([[10, 20, 30], [1, 2, 3], [-2, 1, 0]], np.float32)
+    new_rot = synth.random_unit_quats(rng, 3)
+    new_scl = np.ones((3, 3), np.float32)
+    for e in engines:
+        new_ids = e.create_entities(new_parent, new_pos, new_rot, new_scl)
+        e.add_colliders(new_ids, np.tile(np.array([[-1, -1, -1, 1, 1, 1]], np.float32), (3, 1)))
+        e.scene_update()
+    ids2 = np.arange(1, E + 4, dtype=np.uint32)
+    check("after adding entities", ids2)
+    assert drop.shim_option("full_uploads") == 2
+    # a dynamic entity turns static: forces the long road once, results stay equal
+    for e in engines:
+        e.set_static(loose[:1], True)
+        e.scene_update()
+    check("dynamic entity turned static", ids2)
+    pos[dynamic] += np.float32(0.5)
+    for e in engines:
+        e.set_trs(dynamic[1:], pos[dynamic[1:]], rot[dynamic[1:]], s.scl[dynamic[1:]])
+        e.scene_update()
+    check("sparse frame after the change", ids2)
+    # a collider box edited in place is seen by the per-frame comparison (collider_check_interval = 1, the reference's semantics)
+    for e in engines:
+        e.add_colliders(s.collider_entity[:5], s.collider_aabb[:5] * np.float32(3.0))  # AddComponent again = overwrite the box
+        e.scene_update()
+    check("collider boxes edited", ids2)
+
+
 def _game(cls, scene, cam_pos, batched=False, rebuild_interval=1):
     e = cls()
     e.create_entities(scene.parent[1:], scene.pos[1:], scene.rot[1:], scene.scl[1:])
