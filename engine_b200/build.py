@@ -21,7 +21,7 @@ HEADERS = ["b2col_math.cuh", "b2col_bvh.cuh", "b2col_sort.cuh", "../../include/b
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",  # host arithmetic (b2col_expand_hits) rounds like the device's: no FMA
     "--expt-relaxed-constexpr",
 ]
 

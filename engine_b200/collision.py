@@ -141,6 +141,31 @@ class CollisionSystem:
         self._ck(self.lib.b2col_raycast_batch(self.h, ptr(rays), n, ptr(out), mode))
         return out
 
+    def get_hits(self, rays, out: np.ndarray | None = None) -> np.ndarray:
+        """compact results (b2col_hit: entity, distance, hit | side << 8): 12 instead of 36 bytes per ray leave the device"""
+        rays = _rays(rays)
+        n = rays.shape[0]
+        if out is None:
+            out = np.empty(n, capi.HIT_DTYPE)
+        self._ck(self.lib.b2col_raycast_hits_batch(self.h, ptr(rays), n, ptr(out)))
+        return out
+
+    def expand_hits(self, rays, hits, threads: int = 1, out: np.ndarray | None = None) -> np.ndarray:
+        """b2col_expand_hits: the Raycasts of get_raycasts from the compact hits, computed on the host"""
+        rays = _rays(rays)
+        n = rays.shape[0]
+        if out is None:
+            out = np.empty(n, RAYCAST_DTYPE)
+        st = self.lib.b2col_expand_hits(ptr(rays), ptr(hits), n, ptr(out), threads)
+        assert st == capi.OK
+        return out
+
+    def raycast_hits_device(self, d_rays, n: int, d_out) -> None:
+        self._ck(self.lib.b2col_raycast_hits_device(self.h, ptr(d_rays), n, ptr(d_out)))
+
+    def raycast_hits_host_pinned(self, h_rays, n: int, h_out) -> None:
+        self._ck(self.lib.b2col_raycast_hits_batch(self.h, ptr(h_rays), n, ptr(h_out)))
+
     def get_raycast(self, origin, direction, mode: int = MODE_LBVH):
         ray = np.zeros((1, 6), np.float32)
         ray[0, :3] = origin

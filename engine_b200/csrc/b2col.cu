@@ -12,6 +12,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "b2col_bvh.cuh"
@@ -20,6 +21,7 @@
 
 using namespace b2;
 
+static_assert(sizeof(b2col_hit) == 12, "compact result layout");
 static_assert(sizeof(b2col_ray) == 24 && sizeof(b2col_raycast) == 36 && sizeof(b2col_aabb) == 24 && sizeof(b2col_bitreenode) == 60,
               "POD layouts must equal the reference's (include/system_collisions.h:13-24,40-48)");
 
@@ -829,17 +831,18 @@ __device__ __noinline__ int trace_refill(TraceSmem& sm, int tid, const uint32_t*
 // rows, ray after ray (stride 9 words: conflict-free), and the warp writes the staged words out 32 at a time — each
 // instruction covers ~3.5 whole Raycasts, contiguous 36-byte runs in global memory.  The staging area holds STAGE_RAYS rays
 // per warp (shared memory is what limits the kernel's occupancy); more finished lanes than that take another round.
-template <bool STAGED>
+template <bool STAGED, int OUTW>
 __device__ __forceinline__ void flush_finished(TraceSmem& sm, int warp, int lane, uint32_t lt_mask, bool pending, const uint32_t* w9, unsigned long long my,
                                                b2col_raycast* __restrict__ out)
 {
-    if (!STAGED) {  // local memory: every lane writes its own Raycast, nine 4-byte stores at a 36-byte stride
+    if (!STAGED) {  // local memory: every lane writes its own result, OUTW 4-byte stores (9: Raycast, 3: b2col_hit)
         if (pending) {
 #pragma unroll
-            for (int k = 0; k < 9; ++k) reinterpret_cast<uint32_t*>(out)[9ull * my + k] = w9[k];
+            for (int k = 0; k < OUTW; ++k) reinterpret_cast<uint32_t*>(out)[(unsigned long long)OUTW * my + k] = w9[k];
         }
         return;
     }
+    static_assert(!STAGED || OUTW == 9, "only full Raycasts are staged");
     unsigned pend = __ballot_sync(0xffffffffu, pending);
     if (pend == 0u) return;
     uint32_t* st = sm.stage[warp];
@@ -892,7 +895,7 @@ __device__ __forceinline__ void flush_finished(TraceSmem& sm, int warp, int lane
 // WILD: the tree holds leaves the grid cannot bound (hdr->has_wild; b2col_bvh.cuh WILD_BIT): flagged slots are always
 // entered and no ray is dismissed by its distance from the grid.  Chosen once per kernel, so that sane scenes run the
 // instantiation that never looks at the bit.
-template <bool COUNT, bool WILD, bool STAGED>
+template <bool COUNT, bool WILD, bool STAGED, bool COMPACT>
 __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
                                            const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
                                            unsigned long long* counter, int fetch_threshold)
@@ -932,8 +935,11 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
         // run them together instead of one at a time inside the traversal loop.
         {
             uint32_t w9[9];
-            if (pending) finish_raycast<DevOps>(w9, exact_ray(), best, leaves);
-            flush_finished<STAGED>(sm, warp, lane, lt_mask, pending, w9, my, out);
+            if (pending) {
+                if (COMPACT) finish_hit<DevOps>(w9, exact_ray(), best, leaves);
+                else finish_raycast<DevOps>(w9, exact_ray(), best, leaves);
+            }
+            flush_finished<STAGED, COMPACT ? 3 : 9>(sm, warp, lane, lt_mask, pending, w9, my, out);
             pending = false;
         }
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -959,6 +965,10 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
                         lim = lim0;
                         cur = root;
                         active = true;
+                    }
+                    else if (COMPACT) {  // provable miss
+                        uint32_t* o3 = reinterpret_cast<uint32_t*>(out) + 3ull * my;
+                        o3[0] = o3[1] = o3[2] = 0u;
                     }
                     else {
                         write_raycast(reinterpret_cast<uint32_t*>(out + my), r, false, 0.0f, 0, 0u);  // provable miss
@@ -1017,15 +1027,16 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
     }
 }
 
-template <bool COUNT, bool STAGED>
+// COMPACT: `out` is an array of 12-byte b2col_hit records (entity, distance, hit | side << 8) instead of 36-byte Raycasts.
+template <bool COUNT, bool STAGED, bool COMPACT = false>
 __global__ void __launch_bounds__(TRACE_BLOCK, B2_TRACE_MIN_BLOCKS)
 k_trace_lbvh(const b2col_ray* __restrict__ rays, unsigned long long n_rays, b2col_raycast* __restrict__ out,
              const BlobHeader* __restrict__ hdr, const QNode* __restrict__ qnodes, const LeafRec* __restrict__ leaves, float T,
              unsigned long long* counter, int fetch_threshold)
 {
     __shared__ TraceSmem sm;
-    if (hdr->has_wild) trace_body<COUNT, true, STAGED>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
-    else trace_body<COUNT, false, STAGED>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
+    if (hdr->has_wild) trace_body<COUNT, true, STAGED, COMPACT>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
+    else trace_body<COUNT, false, STAGED, COMPACT>(sm, rays, n_rays, out, hdr, qnodes, leaves, T, counter, fetch_threshold);
 }
 
 // Same query, walking an uploaded reference-format tree with the reference's exact semantics.
@@ -1296,18 +1307,19 @@ inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
         if (s_ != B2COL_OK) return s_;      \
     } while (0)
 
-b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode, bool remote_out = false)
+b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode, bool remote_out = false, bool compact = false)
 {
+    const size_t out_bytes = compact ? 12 : sizeof(b2col_raycast);  // compact: d_out is an array of b2col_hit
     if (n == 0) return B2COL_OK;
     const bool count = mode == B2COL_MODE_LBVH_COUNT;
     if (mode == B2COL_MODE_LBVH || count) {
         if (!ctx->have_tree) {
             // frame-0 behaviour of the reference: bvh_ is empty before the first onUpdate, every query misses (:167)
-            CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
+            CU(cudaMemsetAsync(d_out, 0, n * out_bytes, ctx->stream));
             return B2COL_OK;
         }
         if (ctx->tree_leaves == 0) {  // empty tree: value-initialised Raycast (:164-167)
-            CU(cudaMemsetAsync(d_out, 0, n * sizeof(b2col_raycast), ctx->stream));
+            CU(cudaMemsetAsync(d_out, 0, n * out_bytes, ctx->stream));
             return B2COL_OK;
         }
         GUARD(ensure(ctx, ctx->d_counter, 16));
@@ -1323,7 +1335,10 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
             ctx->counted_rays += n;
         }
         else {
-            if (remote_out)
+            if (compact)
+                LAUNCH(ctx, (k_trace_lbvh<false, false, true>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                       blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
+            else if (remote_out)
                 LAUNCH(ctx, (k_trace_lbvh<false, true>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
                        blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
             else
@@ -2026,13 +2041,18 @@ b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_
 
 // b2col_raycast_batch in two halves, so that one host thread can keep the pipelines of several GPUs in flight
 // (b2col_mgpu_raycast_batch): _begin enqueues every copy and kernel of the batch, _end waits for them.
-static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode)
+// `compact`: results are 12-byte b2col_hit records instead of 36-byte Raycasts (h_out_any points at whichever it is).
+static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, void* h_out_any, int mode, bool compact = false)
 {
+    const size_t out_words = compact ? 3 : 9, out_bytes = 4 * out_words;
+    b2col_raycast* const h_out = static_cast<b2col_raycast*>(h_out_any);  // byte arithmetic below goes through h_out_b
+    char* const h_out_b = static_cast<char*>(h_out_any);
+    if (compact && mode != B2COL_MODE_LBVH) return fail(ctx, B2COL_ERR_INVALID, "compact results exist for the production tree only");
     if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
     ctx->pending = b2col_ctx::PendingBatch();
     if (n == 0) return B2COL_OK;
     CU(cudaSetDevice(ctx->device));
-    if (mode == B2COL_MODE_LBVH && n <= b2col_ctx::SMALL_MAX && ctx->have_tree && ctx->tree_leaves > 0 && !ctx->no_small_path) {
+    if (!compact && mode == B2COL_MODE_LBVH && n <= b2col_ctx::SMALL_MAX && ctx->have_tree && ctx->tree_leaves > 0 && !ctx->no_small_path) {
         if (!ctx->h_small) {
             CU(cudaHostAlloc(&ctx->h_small, b2col_ctx::SMALL_MAX * (sizeof(b2col_ray) + sizeof(b2col_raycast)), cudaHostAllocMapped));
             CU(cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0));
@@ -2054,7 +2074,7 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
         return B2COL_OK;
     }
     GUARD(ensure(ctx, ctx->d_rays, n * sizeof(b2col_ray)));
-    GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
+    GUARD(ensure(ctx, ctx->d_hits, n * out_bytes));
     // first chunk: e2e_first_chunk for large batches, halved down to e2e_min_chunk until the batch holds four of them: a
     // 256K-ray call runs as 64K + 128K + 64K instead of upload -> trace -> download back to back (300 -> 384 Mrays/s, 512K:
     // 521 -> 592; chunks below 64K cost more in launches and events than the overlap returns — tools/tune_e2e_small.py)
@@ -2071,7 +2091,7 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
             CU(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
         }
         b2col_ray* d_r = ctx->d_rays.as<b2col_ray>();
-        b2col_raycast* d_h = ctx->d_hits.as<b2col_raycast>();
+        char* d_h = ctx->d_hits.as<char>();
         // device->host leg: copy engine, or SM stores when the buffer is page-locked (device-accessible through UVA) and
         // 16-byte aligned.  Big calls time themselves: the first uses the copy engine, the second the SMs, later ones the
         // faster of the two (every 32nd call tries the other again: what else runs on the host changes).
@@ -2108,16 +2128,16 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
             CU(cudaMemcpyAsync(d_r + off, h_rays + off, m * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream_in));
             CU(cudaEventRecord(ev_in, ctx->stream_in));
             CU(cudaStreamWaitEvent(ctx->stream, ev_in, 0));
-            GUARD(enqueue_trace(ctx, d_r + off, m, d_h + off, mode));
+            GUARD(enqueue_trace(ctx, d_r + off, m, reinterpret_cast<b2col_raycast*>(d_h + off * out_bytes), mode, false, compact));
             CU(cudaEventRecord(ev_k, ctx->stream));
             CU(cudaStreamWaitEvent(ctx->stream_out, ev_k, 0));
             if (d2h == 1) {
-                k_copy_out<<<2 * ctx->n_sm, 256, 0, ctx->stream_out>>>(reinterpret_cast<const uint32_t*>(d_h + off), h_out_dev + 9 * off, 9 * m);
+                k_copy_out<<<2 * ctx->n_sm, 256, 0, ctx->stream_out>>>(reinterpret_cast<const uint32_t*>(d_h + off * out_bytes), h_out_dev + out_words * off, out_words * m);
                 ++ctx->launches;
                 if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "launch of k_copy_out failed: %s", cudaGetErrorString(e));
             }
             else {
-                CU(cudaMemcpyAsync(h_out + off, d_h + off, m * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream_out));
+                CU(cudaMemcpyAsync(h_out_b + off * out_bytes, d_h + off * out_bytes, m * out_bytes, cudaMemcpyDeviceToHost, ctx->stream_out));
             }
             off += m;
             ++c;
@@ -2133,8 +2153,8 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
         return B2COL_OK;
     }
     CU(cudaMemcpyAsync(ctx->d_rays.p, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));
-    GUARD(enqueue_trace(ctx, ctx->d_rays.as<b2col_ray>(), n, ctx->d_hits.as<b2col_raycast>(), mode));
-    CU(cudaMemcpyAsync(h_out, ctx->d_hits.p, n * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream));
+    GUARD(enqueue_trace(ctx, ctx->d_rays.as<b2col_ray>(), n, ctx->d_hits.as<b2col_raycast>(), mode, false, compact));
+    CU(cudaMemcpyAsync(h_out_b, ctx->d_hits.p, n * out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     ctx->pending.active = true;
     ctx->pending.mode = mode;
     ctx->pending.n = n;
@@ -2164,6 +2184,41 @@ static b2col_status raycast_batch_end(b2col_ctx* ctx)
         CU(cudaMemcpy(&flag, ctx->d_flag.p, 4, cudaMemcpyDeviceToHost));
         if (flag) return fail(ctx, B2COL_ERR_OVERFLOW, "reference-topology traversal stack overflow (tree deeper than %d)", REFTOPO_STACK);
     }
+    return B2COL_OK;
+}
+
+b2col_status b2col_raycast_hits_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_hit* d_out)
+{
+    if (!ctx || (n && (!d_rays || !d_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(ctx->device));
+    return enqueue_trace(ctx, d_rays, n, reinterpret_cast<b2col_raycast*>(d_out), B2COL_MODE_LBVH, false, true);
+}
+
+b2col_status b2col_raycast_hits_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_hit* h_out)
+{
+    if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n == 0) return B2COL_OK;
+    GUARD(raycast_batch_begin(ctx, h_rays, n, h_out, B2COL_MODE_LBVH, true));
+    return raycast_batch_end(ctx);
+}
+
+// Host side of the compact format: b2col_hit -> Raycast with the arithmetic of the device epilogue (b2col_bvh.cuh expand_hit; this
+// translation unit's host code is compiled without FMA contraction), sharded over n_threads host threads.
+b2col_status b2col_expand_hits(const b2col_ray* h_rays, const b2col_hit* h_hits, size_t n, b2col_raycast* h_out, int n_threads)
+{
+    if (n && (!h_rays || !h_hits || !h_out)) return B2COL_ERR_INVALID;
+    auto work = [=](size_t lo, size_t hi) {
+        for (size_t i = lo; i < hi; ++i)
+            expand_hit(reinterpret_cast<uint32_t*>(h_out + i), h_rays[i].origin, h_rays[i].direction, reinterpret_cast<const uint32_t*>(h_hits + i));
+    };
+    const int T = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, n_threads), n / 65536 + 1));
+    if (T == 1) {
+        work(0, n);
+        return B2COL_OK;
+    }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < T; ++t) pool.emplace_back(work, n * (size_t)t / T, n * (size_t)(t + 1) / T);
+    for (auto& th : pool) th.join();
     return B2COL_OK;
 }
 

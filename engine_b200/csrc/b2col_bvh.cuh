@@ -659,6 +659,40 @@ B2_HD void finish_raycast(uint32_t* out9, const RayPre& r, const Hit& best, cons
     write_raycast(out9, r, true, s.tmin, slab_side(s), rec.entity);
 }
 
+// The same winner as a 12-byte b2col_hit (include/b2col.h): entity, distance, hit | side << 8 — everything a Raycast holds that
+// is not a function of the ray itself (expand_hit below restores the rest on the host, bit for bit).
+template <class Ops>
+B2_HD void finish_hit(uint32_t* out3, const RayPre& r, const Hit& best, const LeafRec* leaves)
+{
+    if (best.leaf < 0) {
+        out3[0] = out3[1] = out3[2] = 0u;
+        return;
+    }
+    const LeafRec rec = Ops::load_leaf(&leaves[best.leaf]);
+    const SlabT s = slab(r, rec.lo, rec.hi);
+    union {
+        float f;
+        uint32_t u;
+    } cv;
+    cv.f = s.tmin;
+    out3[0] = rec.entity;
+    out3[1] = cv.u;
+    out3[2] = 1u | ((uint32_t)slab_side(s) << 8);
+}
+
+// b2col_hit -> Raycast (GetRaycast's epilogue, src/system_collisions.cpp:162,170-194,489): the direction is normalised again and
+// location = d * t + o, normal = axis of the side — the arithmetic of write_raycast, so the bytes equal the 36-byte path's.
+B2_HD void expand_hit(uint32_t* out9, const float* origin, const float* direction, const uint32_t* hit3)
+{
+    const RayPre r = ray_prepare(origin, direction);
+    union {
+        float f;
+        uint32_t u;
+    } cv;
+    cv.u = hit3[1];
+    write_raycast(out9, r, (hit3[2] & 1u) != 0u, cv.f, (int)((hit3[2] >> 8) & 7u), hit3[0]);
+}
+
 // Whole-ray form with a plain array stack (host emulation; the device kernel, k_trace_lbvh in b2col.cu,
 // runs the same visit_node per step with a shared-memory stack and interleaves ray fetching).  A
 // deferred child whose entry tmin has meanwhile fallen behind the best hit is dropped when popped.

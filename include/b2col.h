@@ -68,6 +68,14 @@ typedef struct b2col_raycast {
     uint8_t pad[3]; /* always written as 0 */
 } b2col_raycast;
 
+/* Compact result (additive; the reference has no such type): what a Raycast holds that is not a function of the ray itself.
+ * 12 instead of 36 bytes per ray leave the device; b2col_expand_hits restores the Raycast on the host, bit for bit. */
+typedef struct b2col_hit {
+    uint32_t hit_entity;
+    float distance;
+    uint32_t flags; /* bit 0: hit; bits 8-10: engine::AABBSide of the entry face (Left, Right, Bottom, Top, Front, Back) */
+} b2col_hit;
+
 /* engine::AABB — reference include/component_collider.h:7-10 (24 bytes) */
 typedef struct b2col_aabb {
     float min[3];
@@ -177,6 +185,16 @@ b2col_status b2col_refit(b2col_ctx* ctx);
 b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode);
 /* Device buffers; enqueued on the ctx stream, returns without waiting. */
 b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode);
+
+/* Compact-result forms of the two calls above (production tree): 12-byte b2col_hit records.  The host-buffer path is bound by
+ * the device->host copy of its results (36 of 60 bytes per ray), so a caller that can consume hits — or expand them on its own
+ * cores with b2col_expand_hits — moves 36 instead of 60 bytes per ray over PCIe. */
+b2col_status b2col_raycast_hits_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_hit* h_out);
+b2col_status b2col_raycast_hits_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_hit* d_out);
+/* replaces: the epilogue of GetRaycast (src/system_collisions.cpp:162,170-194,489) on the HOST: h_out[i] = the Raycast that
+ * b2col_raycast_batch would have returned for h_rays[i] (same bytes: direction normalised again, location = d*t + o, normal from
+ * the side).  Pure host function, n_threads worker threads. */
+b2col_status b2col_expand_hits(const b2col_ray* h_rays, const b2col_hit* h_hits, size_t n, b2col_raycast* h_out, int n_threads);
 
 /* ---- reference-topology mode / debug overlay ------------------------------------------------- */
 /* Upload a tree in the reference's own format (e.g. CollisionSystem::bvh_), root = LAST node

@@ -78,3 +78,26 @@ def test_no_cpu_fallback(lib):
 
     with pytest.raises(capi.B2ColError):
         CollisionSystem()
+
+
+def test_expand_hits_restores_reference_raycasts(lib):
+    """b2col_expand_hits (a pure host function: runs without a GPU) turns compact hits (entity, distance, hit | side << 8) back into
+    the reference's Raycast: location = normalise(d) * t + o, normal from the side — against the golden vectors the real reference produced."""
+    import numpy as np
+
+    from conftest import assert_raycast_equal, load_golden
+
+    g = load_golden("city2000")
+    rays, want = np.ascontiguousarray(g["rays"], np.float32), g["raycast"]
+    hits = np.zeros(rays.shape[0], capi.HIT_DTYPE)
+    hits["hit_entity"] = want["hit_entity"]
+    hits["distance"] = want["distance"]
+    n = want["normal"]
+    # engine::AABBSide { Left, Right, Bottom, Top, Front, Back } = -x, +x, -z, +z, -y, +y (reference src/system_collisions.cpp:175-194)
+    side = np.select([n[:, 0] < 0, n[:, 0] > 0, n[:, 2] < 0, n[:, 2] > 0, n[:, 1] < 0, n[:, 1] > 0], [0, 1, 2, 3, 4, 5], 0).astype(np.uint32)
+    hits["flags"] = want["hit"].astype(np.uint32) | (side << 8)
+    for threads in (1, 4):
+        out = np.empty(rays.shape[0], capi.RAYCAST_DTYPE)
+        assert lib.b2col_expand_hits(capi.ptr(rays), capi.ptr(hits), rays.shape[0], capi.ptr(out), threads) == capi.OK
+        assert_raycast_equal(out, want, f"expand_hits, {threads} threads")
+    assert want["hit"].sum() > 100

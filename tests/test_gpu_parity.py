@@ -367,6 +367,41 @@ def test_config2_100k_camera_rays(CollisionSystem, port):
     assert got["hit"].sum() > 1000
 
 
+REF_TREE_100K = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "config2_ref_bvh.npz")
+
+
+def test_config2_reference_built_tree(CollisionSystem, port):
+    """BASELINE config 2 with the reference's OWN tree: its O(N^2) BuildNode (src/system_collisions.cpp:205-376) was run once at
+    100 000 colliders (oracle/build_ref_tree.py, half an hour of one core, cached in the git-ignored oracle/_ref/ and shipped with
+    the snapshot).  The reference-topology kernel walks that tree and must return the reference's answers on all 1M camera rays bit
+    for bit — tie winners included; the production LBVH must agree everywhere except on exact ties."""
+    if not os.path.exists(REF_TREE_100K):
+        pytest.skip("oracle/_ref/config2_ref_bvh.npz absent: run `python -m oracle.build_ref_tree` where /root/reference exists (about 30 min)")
+    from oracle.build_ref_tree import scene_fingerprint
+
+    z = np.load(REF_TREE_100K)
+    s = synth.static_city(int(z["n"]))
+    assert bytes(z["fingerprint"]).decode() == scene_fingerprint(s), "the cached tree belongs to another scene generator"
+    ref_bvh = np.ascontiguousarray(z["bvh"]).view(capi.NODE_DTYPE).reshape(-1)
+    rays = synth.camera_rays(1000, 1000)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    assert (bits(cs.world_aabbs()) == bits(z["world_aabb"])).all(), "world AABBs differ from the reference's refit"
+    want = reference_walk(ref_bvh, rays, port)  # the reference's GetRaycast on the reference's own tree
+    assert want["hit"].sum() > 100_000
+    cs.upload_ref_bvh(ref_bvh)
+    got_ref = cs.get_raycasts(rays, mode=capi.MODE_REFTOPO)
+    assert_raycast_equal(got_ref, want, "config 2, reference topology (k_trace_reftopo) vs the reference")
+    assert (got_ref.view(np.uint8) == want.view(np.uint8)).all() or (got_ref["distance"] == want["distance"]).all()
+    got = cs.get_raycasts(rays)
+    order, boxes = cs.leaf_order(), cs.world_aabbs()
+    _, ties = port.raycast_brute(s.collider_entity[order], boxes[order], rays[::50], nthreads=8, want_ties=True)
+    differ = got["hit_entity"] != want["hit_entity"]
+    assert (got["hit"] == want["hit"]).all() and (got["distance"] == want["distance"]).all(), "LBVH vs reference tree: hit flags / distances"
+    assert differ.mean() < 1e-3 and not differ[::50][ties == 0].any(), "LBVH and the reference's tree may only disagree on exact tmin ties"
+
+
 def test_config3_1m_incoherent(CollisionSystem, port):
     n_rays = 1 << 21
     s = synth.uniform_boxes(1_000_000)
@@ -622,7 +657,15 @@ def test_device_resident_and_replicated_tree(CollisionSystem):
     cs.bvh_export_blob(blob, nbytes)
     cs.sync()
     replica.bvh_import_blob(blob, nbytes)
+    replica.sync()  # checks the header that travelled behind the import
     assert (replica.get_raycasts(rays).view(np.uint8) == want.view(np.uint8)).all()
+    with pytest.raises(capi.B2ColError):
+        replica.bvh_import_blob(blob, nbytes - 32)  # not the size of any blob
+    blob[:4] = 0x5A  # corrupt the magic: accepted asynchronously, rejected by the next sync, and the context has no tree then
+    replica.bvh_import_blob(blob, nbytes)
+    with pytest.raises(capi.B2ColError):
+        replica.sync()
+    assert not replica.get_raycasts(rays[:100]).view(np.uint8).any()
     st0, st1 = cs.stats(), replica.stats()
     assert st0["kernel_launches"] > 0 and st1["kernel_launches"] > 0
 
@@ -905,6 +948,53 @@ def test_host_pipeline_d2h_modes(CollisionSystem, monkeypatch, d2h_mode):
     # pageable host memory takes the copy-engine path whatever the mode
     rays = synth.random_rays(300_000, seed=99, extent=400)
     assert (cs.get_raycasts(rays)["hit"].sum()) > 0
+
+
+def test_compact_hits_expand_to_the_same_raycasts(CollisionSystem):
+    """b2col_raycast_hits_batch / _device + b2col_expand_hits (additive ABI: 12 instead of 36 bytes per ray leave the device):
+    the expanded Raycasts equal the 36-byte path's byte for byte, through the chunked host pipeline, the single-shot path and
+    from device buffers; misses are all-zero in both forms."""
+    s = synth.uniform_boxes(200_000, seed=41, extent=300)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    for n in (1, 31, 5000, 700_000):
+        rays = np.concatenate([synth.random_rays(n, seed=42, extent=320, normalised=False), synth.degenerate_rays(min(n, 2000), seed=43, extent=320)])[:max(n, 1)]
+        want = cs.get_raycasts(rays)
+        hits = cs.get_hits(rays)
+        assert ((hits["flags"] & 1) == want["hit"]).all() and (hits["hit_entity"] == want["hit_entity"]).all()
+        assert (hits.view(np.uint32).reshape(-1, 3)[want["hit"] == 0] == 0).all()
+        got = cs.expand_hits(rays, hits, threads=4)
+        assert (got.view(np.uint8) == want.view(np.uint8)).all(), f"expanded hits differ from the Raycast path at n = {n}"
+    d_rays = torch.from_numpy(rays).cuda()
+    d_hits = torch.empty(rays.shape[0] * 12, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    cs.raycast_hits_device(d_rays, rays.shape[0], d_hits)
+    cs.sync()
+    assert (d_hits.cpu().numpy() == hits.view(np.uint8)).all()
+
+
+def test_sparse_trs_rows_and_world_rows(CollisionSystem, port):
+    """b2col_update_trs_rows / b2col_fetch_world_rows (the drop-in TransformSystem's sparse frame): updating some rows equals
+    re-uploading everything; fetched rows equal the full read-back."""
+    s = synth.hierarchy_scene(30_000, 200, seed=23, extent=300)
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    rng = np.random.default_rng(4)
+    moved = np.sort(rng.choice(np.arange(1, s.n_entities + 1), 3000, replace=False)).astype(np.uint32)
+    s.pos[moved] += rng.uniform(-2, 2, (3000, 3)).astype(np.float32)
+    s.rot[moved] = synth.random_unit_quats(rng, 3000)
+    cs.update_trs_rows(moved, s.pos[moved], s.rot[moved], s.scl[moved])
+    cs.on_update()
+    world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+    assert (bits(cs.world_matrices()) == bits(world[1:])).all()
+    pick = np.sort(rng.choice(np.arange(1, s.n_entities + 1), 5000, replace=False)).astype(np.uint32)
+    assert (bits(cs.world_rows(pick)) == bits(world[pick])).all()
+    want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+    assert (bits(cs.world_aabbs()) == bits(want_boxes)).all()
+    with pytest.raises(capi.B2ColError):
+        cs.update_trs_rows(np.array([s.n_entities + 1], np.uint32), np.zeros((1, 3)), np.zeros((1, 4)), np.ones((1, 3)))
 
 
 def test_few_ray_calls_equal_batch(CollisionSystem):
