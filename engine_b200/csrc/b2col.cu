@@ -400,13 +400,13 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 #endif
 constexpr int MORTON_BLOCK = B2_MORTON_BLOCK;
 __global__ void __launch_bounds__(MORTON_BLOCK)
-k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, int packed, float T, uint64_t* __restrict__ keys,
-         uint32_t* __restrict__ vals, uint32_t* ghist)
+k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, int hist_lo, int packed, float T,
+         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* ghist)  // histograms of the radix passes hist_lo .. passes-1 (the MSD pipeline needs the top digit's only)
 {
     pdl_wait();
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
     __shared__ MortonPlan s_plan;
-    for (int p = 0; p < passes; ++p)
+    for (int p = hist_lo; p < passes; ++p)
         for (int b = threadIdx.x; b < RS_RADIX; b += MORTON_BLOCK) shist[p][b] = 0u;
     if (threadIdx.x == 0) {
         float cmin[3], cmax[3];
@@ -438,7 +438,7 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
                 keys[i] = key;
                 vals[i] = i;
             }
-            for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+            for (int p = hist_lo; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
         }
         if (two) {
             const float lo[3] = {c0.x, c0.y, c0.z}, hi[3] = {c0.w, c1.x, c1.y};
@@ -450,11 +450,11 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
                 keys[j] = key;
                 vals[j] = j;
             }
-            for (int p = 0; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+            for (int p = hist_lo; p < passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
         }
     }
     __syncthreads();
-    for (int p = 0; p < passes; ++p) {
+    for (int p = hist_lo; p < passes; ++p) {
         for (int b = threadIdx.x; b < RS_RADIX; b += MORTON_BLOCK) {
             const uint32_t c = shist[p][b];
             if (c) atomicAdd(&ghist[p * RS_RADIX + b], c);
@@ -1077,6 +1077,80 @@ k_export(uint32_t n, const BlobHeader* __restrict__ hdr, const Node* __restrict_
     if (i + 1u < n) export_internal(i, n, hdr->root, nodes, leaves, out, used);
 }
 
+// Compaction of the export candidates on the device (b2col_export_bitreenode): exclusive prefix sum of the `used` flags
+// (tile-local scan, scan of the tile sums by one block, no host round trip), then every used node moves to its final
+// place with its child indices renumbered — the order (wrappers, internal nodes, root last) is kept.
+constexpr int XS_THREADS = 256, XS_ITEMS = 4, XS_TILE = XS_THREADS * XS_ITEMS;
+__global__ void __launch_bounds__(XS_THREADS)
+k_export_scan_tiles(const uint8_t* __restrict__ used, uint32_t n, uint32_t* __restrict__ excl, uint32_t* __restrict__ tile_sums)
+{
+    __shared__ uint32_t s_warp[XS_THREADS / 32];
+    const uint32_t base = blockIdx.x * XS_TILE + threadIdx.x * XS_ITEMS;
+    uint32_t v[XS_ITEMS], mine = 0u;
+#pragma unroll
+    for (int k = 0; k < XS_ITEMS; ++k) {
+        v[k] = (base + k < n && used[base + k]) ? 1u : 0u;
+        mine += v[k];
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0u;
+    for (int w = 0; w < warp; ++w) before += s_warp[w];
+    uint32_t run = before + incl - mine;
+#pragma unroll
+    for (int k = 0; k < XS_ITEMS; ++k) {
+        if (base + k < n) excl[base + k] = run;
+        run += v[k];
+    }
+    if (threadIdx.x == XS_THREADS - 1) tile_sums[blockIdx.x] = run;
+}
+__global__ void __launch_bounds__(1024)
+k_export_scan_sums(uint32_t* tile_sums, uint32_t n_tiles, uint32_t* total)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0u;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < n_tiles; base += 1024u) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t mine = i < n_tiles ? tile_sums[i] : 0u;
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t before = s_carry;
+        for (int w = 0; w < warp; ++w) before += s_warp[w];
+        if (i < n_tiles) tile_sums[i] = before + incl - mine;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = before + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = s_carry;
+}
+__global__ void __launch_bounds__(256)
+k_export_compact(uint32_t n_cand, const BiTreeNode60* __restrict__ cand, const uint8_t* __restrict__ used, const uint32_t* __restrict__ excl,
+                 const uint32_t* __restrict__ tile_sums, BiTreeNode60* __restrict__ out)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_cand || !used[k]) return;
+    BiTreeNode60 nd = cand[k];
+    if (nd.type1 == 0) nd.index1 = excl[nd.index1] + tile_sums[nd.index1 / XS_TILE];
+    if (nd.type2 == 0) nd.index2 = excl[nd.index2] + tile_sums[nd.index2 / XS_TILE];
+    out[excl[k] + tile_sums[k / XS_TILE]] = nd;
+}
+
 // =================================================================================================
 // host side
 // =================================================================================================
@@ -1129,6 +1203,7 @@ struct b2col_ctx {
     int top_levels = -1;                         // -1: automatic (trees larger than L2); dev override B2COL_TOP_LEVELS
     DevBuf d_keys[2], d_vals[2], d_xch, d_zero;  // d_xch: per-node arrival/exchange words; d_zero: histograms, tickets, look-back words
     DevBuf d_nodes_full, d_other_bound;  // export only: full-precision two-slot nodes + their arrival words (k_build_exact)
+    DevBuf d_export_cand, d_export_out, d_export_used, d_export_scan;  // export only: candidates, compacted nodes, flags, prefix sums
     bool exact_nodes_valid = false;      // d_nodes_full matches the tree in the blob
     void* xch_ready = nullptr;           // the d_xch allocation whose words are all in the "nobody arrived" state
     size_t zero_bytes = 0;
@@ -1167,6 +1242,10 @@ struct b2col_ctx {
     int d2h_policy = 0;
     int n_sm = 148;
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
+    // sort pipeline of a full build: MSD pass + block-local sort (b2col_sort.cuh) where the buckets fit a block, LSD otherwise
+    int sort_policy = 0;              // 0 = automatic; 1 = always LSD; 2 = MSD whenever the keys are packed  (B2COL_SORT=lsd|msd)
+    bool sort_msd = false;            // this frame's choice (part of the graph key)
+    uint32_t* h_sort_stat = nullptr;  // page-locked: largest top-digit bucket of the last MSD frame, written by the frame itself
     int morton_blocks_per_sm = 0;  // 0 = by collider count; B2COL_MORTON_BLOCKS_PER_SM overrides (tuning)
     uint64_t d2h_calls = 0;
     double d2h_ns_per_ray[2] = {0.0, 0.0};
@@ -1412,6 +1491,13 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
+        if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "lsd") ? 1 : (!strcmp(e, "msd") ? 2 : 0);
+        cudaFuncSetAttribute(k_local_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem));
+        if (cudaHostAlloc((void**)&c->h_sort_stat, sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess) *c->h_sort_stat = 0u;
+        else {
+            c->h_sort_stat = nullptr;  // no stat word: the LSD pipeline only
+            cudaGetLastError();
+        }
         if (const char* e = getenv("B2COL_D2H_MODE")) c->d2h_policy = !strcmp(e, "ce") ? 0 : (!strcmp(e, "sm") ? 1 : -1);
         if (const char* e = getenv("B2COL_TOP_LEVELS")) c->top_levels = std::min(TOP_LEVELS, std::max(0, atoi(e)));
         c->use_graph = cfg && cfg->use_cuda_graph != 0;
@@ -1433,12 +1519,13 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
                       &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
-                      &ctx->d_other_bound, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
+                      &ctx->d_other_bound, &ctx->d_export_cand, &ctx->d_export_out, &ctx->d_export_used, &ctx->d_export_scan, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& g : ctx->graphs)
         if (g.exec) cudaGraphExecDestroy(g.exec);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_import_hdr) cudaFreeHost(ctx->h_import_hdr);
+    if (ctx->h_sort_stat) cudaFreeHost(ctx->h_sort_stat);
     if (ctx->h_rows) cudaFreeHost(ctx->h_rows);
     if (ctx->rows_ev) cudaEventDestroy(ctx->rows_ev);
     release(ctx->d_rows);
@@ -1671,6 +1758,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->n_colliders = n;
     ctx->have_colliders = true;
     ctx->topology_valid = false;  // a new collider set needs a new tree
+    if (ctx->h_sort_stat) *ctx->h_sort_stat = 0u;  // ... and gets a fresh try at the MSD sort pipeline
     return B2COL_OK;
 }
 
@@ -1806,15 +1894,39 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
     const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     uint32_t* ghist = scratch_ghist(ctx);
     const bool packed = 3 * ctx->bits - ctx->drop <= 32 && !ctx->no_packed_sort;  // key << 32 | index in one word through the sort
+    const bool msd = ctx->sort_msd;  // chosen by b2col_update
     {
         // 4 blocks per SM up to 2M colliders (fewer end-of-block atomics on the shared counters: -4 us at 1M), 8 beyond (the
         // stream dominates: 125 -> 119 us at 10M)
         const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
         const uint32_t grid = std::min<uint32_t>(cdiv(n, MORTON_BLOCK), (uint32_t)(ctx->n_sm * per_sm * 256 / MORTON_BLOCK));  // per_sm counts 256-thread blocks
-        LAUNCH_FRAME(ctx, k_morton, grid, MORTON_BLOCK, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes, (int)packed, ctx->T,
-               ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
+        LAUNCH_FRAME(ctx, k_morton, grid, MORTON_BLOCK, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes,
+               msd ? ctx->passes - 1 : 0, (int)packed, ctx->T, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
     }
     PHASE(ctx);  // morton
+    if (msd) {
+        // MSD pass on the top digit, then every bucket finished inside one block (b2col_sort.cuh): two launches instead of four
+        const int top = ctx->passes - 1;
+        const uint32_t* gh = ghist + top * RS_RADIX;
+        uint32_t* lb = scratch_lookback(ctx);
+        uint32_t* tk = scratch_tickets(ctx);
+        const uint64_t* kin = ctx->d_keys[0].as<uint64_t>();
+        uint64_t* kout = ctx->d_keys[1].as<uint64_t>();
+        const uint32_t* vnone = nullptr;
+        uint32_t* vnone_out = nullptr;
+        const int sh = 32 + top * RS_BITS;
+        if (tiles >= 128u) LAUNCH_FRAME(ctx, (k_onesweep<1, LB_GROUP_SMALL>), tiles, RS_THREADS, 0, kin, vnone, kout, vnone_out, n, tiles, sh, gh, lb, tk);
+        else LAUNCH_FRAME(ctx, (k_onesweep<1, LB_GROUP_LARGE>), tiles, RS_THREADS, 0, kin, vnone, kout, vnone_out, n, tiles, sh, gh, lb, tk);
+        PHASE(ctx);
+        LAUNCH_FRAME(ctx, k_local_sort, RS_RADIX, LS_THREADS, sizeof(LocalSortSmem), ctx->d_keys[1].as<uint64_t>(), ctx->d_keys[0].as<uint64_t>(), ctx->d_keys[0].as<uint64_t>(),
+                     ctx->d_vals[0].as<uint32_t>(), gh, scratch_tickets(ctx) + 12);
+        CU(cudaMemcpyAsync(ctx->h_sort_stat, scratch_tickets(ctx) + 12, 4, cudaMemcpyDeviceToHost, ctx->stream));  // largest bucket: read by the NEXT update
+        PHASE(ctx);
+        ctx->sorted_side = 0;
+        GUARD(launch_build(ctx, n, 0));
+        PHASE(ctx);  // last: build
+        return B2COL_OK;
+    }
     int side = 0;
     for (int p = 0; p < ctx->passes; ++p) {
         const uint64_t* kin = ctx->d_keys[side].as<uint64_t>();
@@ -1856,13 +1968,13 @@ b2col_status run_frame(b2col_ctx* ctx, bool full)
     const bool propagate = !ctx->world_external && !ctx->world_fresh;
     const uint64_t key[4] = {ctx->buffers_gen, ctx->shape_gen,
                              (uint64_t)propagate | ((uint64_t)(ctx->fusable && !ctx->no_fuse) << 1) | ((uint64_t)ctx->passes << 8) | ((uint64_t)ctx->bits << 16) |
-                                 ((uint64_t)ctx->drop << 24) | ((uint64_t)ctx->sorted_side << 32),
+                                 ((uint64_t)ctx->drop << 24) | ((uint64_t)ctx->sorted_side << 32) | ((uint64_t)ctx->sort_msd << 33),
                              ((uint64_t)ctx->n_colliders << 32) | ctx->n_entities};
     if (g.exec && memcmp(g.key, key, sizeof key) == 0) {
         CU(cudaGraphLaunch(g.exec, ctx->stream));
         ctx->launches += g.launches;
         ++ctx->graph_replays;
-        if (full) ctx->sorted_side = ctx->passes & 1;
+        if (full) ctx->sorted_side = ctx->sort_msd ? 0 : (ctx->passes & 1);
         ctx->scratch_clean = true;
         return B2COL_OK;
     }
@@ -1921,6 +2033,14 @@ static b2col_status prepare_build_inner(b2col_ctx* ctx, uint32_t n)
         ctx->drop = 3 * ctx->bits - key_bits;
     }
     ctx->passes = (3 * ctx->bits - ctx->drop + RS_BITS - 1) / RS_BITS;
+    // MSD + block-local sort: packed 32-bit keys (exactly four digits), a mean bucket comfortably inside a block, and
+    // the largest bucket of the last MSD frame inside one too (a crowded scene falls back to LSD from the next frame
+    // on; the oversized bucket itself is still sorted exactly, only slowly)
+    {
+        const bool packed32 = 3 * ctx->bits - ctx->drop == 32 && !ctx->no_packed_sort;
+        const bool fits = ctx->h_sort_stat && (uint64_t)n * 4u <= (uint64_t)LS_TILE * RS_RADIX * 3u && *ctx->h_sort_stat <= (uint32_t)LS_TILE;  // mean <= 3/4 tile
+        ctx->sort_msd = ctx->h_sort_stat && packed32 && n >= 4096u && (ctx->sort_policy == 2 || (ctx->sort_policy == 0 && fits));
+    }
     const uint32_t tiles = cdiv(n, RS_TILE);
     const size_t lb_words_per_pass = lookback_words_per_pass(tiles);
     GUARD(prepare_scratch(ctx, (SCRATCH_BOUNDS_WORDS + (size_t)RS_MAX_PASSES * RS_RADIX + 16 + (size_t)ctx->passes * lb_words_per_pass) * 4));
@@ -2303,32 +2423,31 @@ b2col_status b2col_export_bitreenode(b2col_ctx* ctx, b2col_bitreenode* h_out, si
                ctx->d_other_bound.as<uint32_t>() + n);
         ctx->exact_nodes_valid = true;
     }
+    // candidates -> flags -> prefix sum -> compacted nodes, all on the device and in buffers the context keeps (a debug overlay
+    // that exports every frame allocates nothing); the host only learns the node count before the one copy into h_out
     const size_t cand = 2 * (size_t)n - 1;
-    DevBuf d_nodes, d_used;
-    GUARD(ensure(ctx, d_nodes, cand * 60));
-    b2col_status st = ensure(ctx, d_used, cand);
-    if (st != B2COL_OK) {
-        release(d_nodes);
-        return st;
-    }
-    std::vector<b2col_bitreenode> tmp(cand);
-    std::vector<uint8_t> used(cand);
-    cudaError_t e = cudaMemsetAsync(d_used.p, 0, cand, ctx->stream);
-    if (e == cudaSuccess) {
-        k_export<<<cdiv(n, 256), 256, 0, ctx->stream>>>(n, blob_hdr(ctx), ctx->d_nodes_full.as<Node>(), blob_leaves(ctx, n), d_nodes.as<BiTreeNode60>(),
-                                                        d_used.as<uint8_t>());
-        ++ctx->launches;
-        e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp.data(), d_nodes.p, cand * 60, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(used.data(), d_used.p, cand, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    release(d_nodes);
-    release(d_used);
-    if (e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "export failed: %s", cudaGetErrorString(e));
+    const uint32_t tiles = cdiv(cand, XS_TILE);
+    GUARD(ensure(ctx, ctx->d_export_cand, cand * 60));
+    GUARD(ensure(ctx, ctx->d_export_out, cand * 60));
+    GUARD(ensure(ctx, ctx->d_export_used, cand));
+    GUARD(ensure(ctx, ctx->d_export_scan, (cand + tiles + 4) * 4));
+    uint32_t* excl = ctx->d_export_scan.as<uint32_t>();
+    uint32_t* tile_sums = excl + cand;
+    uint32_t* total = tile_sums + tiles;
+    CU(cudaMemsetAsync(ctx->d_export_used.p, 0, cand, ctx->stream));
+    LAUNCH(ctx, k_export, cdiv(n, 256), 256, n, blob_hdr(ctx), ctx->d_nodes_full.as<Node>(), blob_leaves(ctx, n), ctx->d_export_cand.as<BiTreeNode60>(),
+           ctx->d_export_used.as<uint8_t>());
+    LAUNCH(ctx, k_export_scan_tiles, tiles, XS_THREADS, ctx->d_export_used.as<uint8_t>(), (uint32_t)cand, excl, tile_sums);
+    LAUNCH(ctx, k_export_scan_sums, 1, 1024, tile_sums, tiles, total);
+    LAUNCH(ctx, k_export_compact, cdiv(cand, 256), 256, (uint32_t)cand, ctx->d_export_cand.as<BiTreeNode60>(), ctx->d_export_used.as<uint8_t>(), excl, tile_sums,
+           ctx->d_export_out.as<BiTreeNode60>());
+    uint32_t kept = 0;
+    CU(cudaMemcpyAsync(&kept, total, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
     static_assert(sizeof(BiTreeNode60) == sizeof(b2col_bitreenode), "export node layout");
-    const size_t kept = compact_export(reinterpret_cast<const BiTreeNode60*>(tmp.data()), used.data(), cand, reinterpret_cast<BiTreeNode60*>(h_out), capacity);
-    if (kept > capacity || !h_out) return fail(ctx, B2COL_ERR_INVALID, "capacity %zu too small, need %zu nodes", capacity, kept);
+    if (kept > capacity || !h_out) return fail(ctx, B2COL_ERR_INVALID, "capacity %zu too small, need %u nodes", capacity, kept);
+    CU(cudaMemcpyAsync(h_out, ctx->d_export_out.p, (size_t)kept * 60, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
     *n_out = kept;
     return B2COL_OK;
 }

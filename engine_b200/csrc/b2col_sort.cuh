@@ -274,4 +274,210 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
     RS_STAMP(5);
 }
 
+
+// =================================================================================================
+// MSD + block-local sort (keys of at most 32 bits, packed as key << 32 | index; up to ~1.2M pairs)
+// =================================================================================================
+// Four LSD passes at ~1M pairs are four dependent, latency-bound launches of ~15 us (look-back across tiles that all
+// start at the same moment: profiles/r1_e).  Instead: ONE onesweep pass on the TOP digit (k_onesweep with shift 56)
+// partitions the array into 256 buckets — each a contiguous range of the final order — and k_local_sort finishes every
+// bucket inside one block: the bucket's pairs live in registers / shared memory through three LSD passes on the
+// remaining 24 bits, with no communication between blocks at all.  Two launches instead of four, the second one free
+// of any look-back.
+//
+// A bucket larger than LS_TILE pairs (a scene whose colliders crowd into one 256th of the Morton range) is still
+// sorted correctly, by the same block, with three LSD passes through GLOBAL memory over its own segment (tile after
+// tile with running digit offsets — slow: one block, but exact); the largest bucket of the frame is reported to the
+// host, which then chooses the plain LSD pipeline for the following frames (b2col_update).
+constexpr int LS_THREADS = 512;
+constexpr int LS_ITEMS = 16;
+constexpr int LS_WARPS = LS_THREADS / 32;
+constexpr int LS_TILE = LS_THREADS * LS_ITEMS;  // 8192 pairs: twice the mean bucket at 1M
+
+struct LocalSortSmem {
+    uint64_t keys[LS_TILE];
+    uint32_t whist[LS_WARPS][RS_RADIX];  // per-warp digit counts, then each warp's offset inside the tile's digit run
+    uint32_t base[RS_RADIX];             // first tile-local position of each digit
+    uint32_t cnt[RS_RADIX];              // tile count of each digit
+    uint32_t run[RS_RADIX];              // oversized buckets: where the next pair of each digit goes in the segment
+    uint32_t warp_tot[LS_WARPS];
+};
+
+// exclusive scan of one value per thread over the first 256 threads of the block (threads >= 256 pass 0 and get garbage)
+__device__ __forceinline__ uint32_t ls_scan_256(uint32_t v, uint32_t* warp_tot)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t before = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w)
+        if (w < warp) before += warp_tot[w];
+    __syncthreads();
+    return before + inc - v;
+}
+
+// Stable tile-local position of every pair held in registers (warp-striped: item k of lane l is element
+// warp * 512 + k * 32 + l of the tile) for the digit at `shift`; leaves sm.base / sm.cnt for the tile.
+__device__ __forceinline__ void ls_rank_tile(LocalSortSmem& sm, const uint64_t* key, uint32_t valid, int shift, uint32_t* pos)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t wbase = (uint32_t)warp * (LS_ITEMS * 32u) + (uint32_t)lane;
+    for (int i = tid; i < LS_WARPS * RS_RADIX; i += LS_THREADS) (&sm.whist[0][0])[i] = 0u;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < LS_ITEMS; ++k) {
+        const bool ok = wbase + (uint32_t)k * 32u < valid;
+        const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
+        uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+        for (int b = 0; b < RS_BITS; ++b) {
+            const uint32_t m = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+            peers &= ((d >> b) & 1u) ? m : ~m;
+        }
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0u;
+        if (ok && lane == leader) {
+            old = sm.whist[warp][d];
+            sm.whist[warp][d] = old + __popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, ok ? leader : 0);
+        pos[k] = old + __popc(peers & lt_mask);
+        __syncwarp();
+    }
+    __syncthreads();
+    uint32_t tile_count = 0u;
+    if (tid < RS_RADIX) {
+#pragma unroll
+        for (int w = 0; w < LS_WARPS; ++w) {
+            const uint32_t c = sm.whist[w][tid];
+            sm.whist[w][tid] = tile_count;
+            tile_count += c;
+        }
+    }
+    const uint32_t excl = ls_scan_256(tid < RS_RADIX ? tile_count : 0u, sm.warp_tot);
+    if (tid < RS_RADIX) {
+        sm.base[tid] = excl;
+        sm.cnt[tid] = tile_count;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < LS_ITEMS; ++k) {
+        if (wbase + (uint32_t)k * 32u < valid) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
+            pos[k] += sm.base[d] + sm.whist[warp][d];
+        }
+    }
+}
+
+// One block per bucket of the MSD pass.  in: packed pairs partitioned by the top digit (counts in top_hist);
+// scratch: the other packed buffer (same size; only oversized buckets use their segment of it);
+// out: kout[i] = key, vout[i] = index, sorted.  stat[0] = largest bucket of the frame (atomicMax; host-visible).
+__global__ void __launch_bounds__(LS_THREADS, 2)
+k_local_sort(uint64_t* in, uint64_t* scratch, uint64_t* kout, uint32_t* vout, const uint32_t* __restrict__ top_hist, uint32_t* stat)  // kout may alias scratch
+{
+    extern __shared__ __align__(16) unsigned char ls_raw[];
+    LocalSortSmem& sm = *reinterpret_cast<LocalSortSmem*>(ls_raw);
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();
+#endif
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t wbase = (uint32_t)warp * (LS_ITEMS * 32u) + (uint32_t)lane;
+    // this bucket's segment: exclusive scan of the top-digit histogram
+    const uint32_t mine = tid < RS_RADIX ? top_hist[tid] : 0u;
+    const uint32_t excl = ls_scan_256(mine, sm.warp_tot);
+    if (tid == (int)blockIdx.x) {
+        sm.run[0] = excl;
+        sm.run[1] = mine;
+    }
+    __syncthreads();
+    const uint32_t start = sm.run[0], count = sm.run[1];
+    __syncthreads();
+    if (count == 0u) return;
+    if (tid == 0) atomicMax(stat, count);
+    uint64_t key[LS_ITEMS];
+    uint32_t pos[LS_ITEMS];
+    if (count <= (uint32_t)LS_TILE) {
+        // ---- the bucket fits the block: three LSD passes through registers and shared memory
+#pragma unroll
+        for (int k = 0; k < LS_ITEMS; ++k) {
+            const uint32_t idx = wbase + (uint32_t)k * 32u;
+            key[k] = idx < count ? in[start + idx] : ~0ull;
+        }
+#pragma unroll 1
+        for (int pass = 0; pass < 3; ++pass) {
+            ls_rank_tile(sm, key, count, 32 + RS_BITS * pass, pos);
+#pragma unroll
+            for (int k = 0; k < LS_ITEMS; ++k)
+                if (wbase + (uint32_t)k * 32u < count) sm.keys[pos[k]] = key[k];
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < LS_ITEMS; ++k) {
+                const uint32_t idx = wbase + (uint32_t)k * 32u;
+                if (idx < count) key[k] = sm.keys[idx];
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int k = 0; k < LS_ITEMS; ++k) {
+            const uint32_t idx = wbase + (uint32_t)k * 32u;
+            if (idx < count) {
+                kout[start + idx] = key[k] >> 32;
+                vout[start + idx] = (uint32_t)key[k];
+            }
+        }
+        return;
+    }
+    // ---- oversized bucket: the same three passes over the segment in global memory, tile after tile (exact, slow)
+#pragma unroll 1
+    for (int pass = 0; pass < 3; ++pass) {
+        const int shift = 32 + RS_BITS * pass;
+        const uint64_t* src = (pass == 1) ? scratch : in;  // in -> scratch -> in -> (kout, vout)
+        uint64_t* dst = (pass == 0) ? scratch : in;
+        if (tid < RS_RADIX) sm.run[tid] = 0u;
+        __syncthreads();
+        for (uint32_t i = tid; i < count; i += LS_THREADS) atomicAdd(&sm.run[(uint32_t)(__ldcg(src + start + i) >> shift) & (RS_RADIX - 1)], 1u);
+        __syncthreads();
+        const uint32_t c = tid < RS_RADIX ? sm.run[tid] : 0u;
+        const uint32_t e = ls_scan_256(c, sm.warp_tot);
+        if (tid < RS_RADIX) sm.run[tid] = e;
+        __syncthreads();
+        for (uint32_t tile = 0; tile < count; tile += LS_TILE) {
+            const uint32_t valid = min((uint32_t)LS_TILE, count - tile);
+#pragma unroll
+            for (int k = 0; k < LS_ITEMS; ++k) {
+                const uint32_t idx = wbase + (uint32_t)k * 32u;
+                key[k] = idx < valid ? __ldcg(src + start + tile + idx) : ~0ull;  // written by this block in the pass before: read at L2
+            }
+            ls_rank_tile(sm, key, valid, shift, pos);
+#pragma unroll
+            for (int k = 0; k < LS_ITEMS; ++k) {
+                if (wbase + (uint32_t)k * 32u < valid) {
+                    const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
+                    const uint32_t at = start + sm.run[d] + (pos[k] - sm.base[d]);
+                    if (pass == 2) {
+                        kout[at] = key[k] >> 32;
+                        vout[at] = (uint32_t)key[k];
+                    }
+                    else {
+                        dst[at] = key[k];
+                    }
+                }
+            }
+            __syncthreads();
+            if (tid < RS_RADIX) sm.run[tid] += sm.cnt[tid];
+            __syncthreads();
+        }
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
 }  // namespace b2

@@ -6,7 +6,7 @@
  * CUDA path can be checked on machines where /root/reference is absent (the GPU box) and at
  * sizes where the reference's O(N^2) builder cannot run.  It is pinned against the real
  * reference (oracle/_ref/libref_engine.so, built from the reference's own sources) by
- * tests/test_oracle_pin.py in this container and against tests/golden/ fixtures, which
+ * tests/test_oracle.py in this container and against tests/golden/ fixtures, which
  * were produced by that real reference (tests/golden/make_golden.py), everywhere else.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
