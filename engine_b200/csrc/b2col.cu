@@ -1446,6 +1446,16 @@ extern "C" {
 
 int b2col_abi_version(void) { return B2COL_ABI_VERSION; }
 
+b2col_status b2col_device_count(int* out)
+{
+    if (!out) return B2COL_ERR_INVALID;
+    int count = 0;
+    const cudaError_t e = cudaGetDeviceCount(&count);
+    *out = e == cudaSuccess ? count : 0;
+    if (e != cudaSuccess) cudaGetLastError();
+    return *out > 0 ? B2COL_OK : B2COL_ERR_NO_DEVICE;
+}
+
 b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
 {
     b2col_ctx* ctx = nullptr;  // for the CU/fail macros: errors before the ctx exists go to g_create_error

@@ -56,6 +56,8 @@ def replicate_bvh(cs, src: int = 0, group=None) -> int:
         return t
 
     def import_fn(t):
+        # the broadcast ran on torch's stream; the import copies on the context's own: order them here
+        torch.cuda.current_stream(device).synchronize()
         cs.bvh_import_blob(t, t.numel())
         cs.sync()
 

@@ -15,6 +15,7 @@
 namespace engine {
 
 static_assert(sizeof(Ray) == sizeof(b2col_ray) && sizeof(Raycast) == sizeof(b2col_raycast), "query PODs must match the C ABI");
+static_assert(sizeof(CollisionSystem::RaycastHit) == sizeof(b2col_hit), "compact results must match the C ABI");
 static_assert(sizeof(AABB) == sizeof(b2col_aabb) && sizeof(CollisionSystem::BiTreeNode) == sizeof(b2col_bitreenode), "tree PODs must match the C ABI");
 
 CollisionSystem::CollisionSystem(Scene* scene)
@@ -107,11 +108,40 @@ void CollisionSystem::onUpdate(float ts)
         have_build_ = true;
         frames_since_build_ = 0;
     }
+    shared_->replicas_fresh = false;  // the other GPUs (UseDevices) still hold the previous tree
     if (keep_debug_bvh) SyncDebugBvh();
+}
+
+void CollisionSystem::UseDevices(const std::vector<int>& devices)
+{
+    // devices[0] must be the device this Scene's context was created on (B2COL_DEVICES chooses it; default 0)
+    B2colUseDevices(shared_, devices.data(), static_cast<int>(devices.size()));
+}
+
+int CollisionSystem::devices_in_use() const { return shared_->ranks.empty() ? 1 : static_cast<int>(shared_->ranks.size()); }
+
+void CollisionSystem::GetRaycastHits(const Ray* rays, std::size_t count, RaycastHit* results)
+{
+    Check(b2col_raycast_hits_batch(ctx_, reinterpret_cast<const b2col_ray*>(rays), count, reinterpret_cast<b2col_hit*>(results)), "b2col_raycast_hits_batch");
+}
+
+void CollisionSystem::ExpandHits(const Ray* rays, const RaycastHit* hits, std::size_t count, Raycast* results, int threads)
+{
+    b2col_expand_hits(reinterpret_cast<const b2col_ray*>(rays), reinterpret_cast<const b2col_hit*>(hits), count, reinterpret_cast<b2col_raycast*>(results), threads);
 }
 
 void CollisionSystem::GetRaycasts(const Ray* rays, std::size_t count, Raycast* results)
 {
+    if (shared_->ranks.size() > 1 && count >= multi_gpu_min_rays && have_build_) {
+        const int n = static_cast<int>(shared_->ranks.size());
+        if (!shared_->replicas_fresh) {
+            Check(b2col_comm_replicate_all(shared_->ranks.data(), n, 0), "b2col_comm_replicate_all");
+            shared_->replicas_fresh = true;
+        }
+        Check(b2col_mgpu_raycast_batch(shared_->ranks.data(), n, reinterpret_cast<const b2col_ray*>(rays), count, reinterpret_cast<b2col_raycast*>(results), B2COL_MODE_LBVH),
+              "b2col_mgpu_raycast_batch");
+        return;
+    }
     Check(b2col_raycast_batch(ctx_, reinterpret_cast<const b2col_ray*>(rays), count, reinterpret_cast<b2col_raycast*>(results), B2COL_MODE_LBVH),
           "b2col_raycast_batch");
 }

@@ -7,7 +7,8 @@
 // in front of the reference's include path.  The bodies (system_collisions.cpp next to this file)
 // forward to the C ABI of libb2col.so (include/b2col.h): the BVH lives on the GPU.
 //
-// Additive API: GetRaycasts (batch), SyncDebugBvh / keep_debug_bvh (materialise bvh_ on demand).
+// Additive API: GetRaycasts (batch), GetRaycastHits (batch, compact results), UseDevices (several GPUs),
+// SyncDebugBvh / keep_debug_bvh (materialise bvh_ on demand).
 #pragma once
 
 #include <cstddef>
@@ -53,6 +54,22 @@ class CollisionSystem : public System {
     // Nearest hit, reference semantics. One ray = a batch of one (latency-bound; prefer GetRaycasts).
     Raycast GetRaycast(Ray ray);
     void GetRaycasts(const Ray* rays, std::size_t count, Raycast* results);
+    // Compact results: 12 bytes per ray cross PCIe instead of 36 (hit entity, distance, hit flag and box side); ExpandHits
+    // recomputes location and normal on the host, bit-identical to GetRaycasts (threads = host threads to use).
+    struct RaycastHit {
+        Entity hit_entity;
+        float distance;
+        uint32_t hit_and_side;  // bit 0: hit; bits 8-10: AABBSide
+    };
+    void GetRaycastHits(const Ray* rays, std::size_t count, RaycastHit* results);
+    static void ExpandHits(const Ray* rays, const RaycastHit* hits, std::size_t count, Raycast* results, int threads = 1);
+
+    // Several GPUs of this machine (also: environment B2COL_DEVICES=all|<count>|<id>,<id>,...): the first device builds, the
+    // tree is replicated with one NCCL broadcast after an update that a large batch follows, and GetRaycasts batches of at
+    // least multi_gpu_min_rays are cut into one contiguous slice per GPU (results bit-identical to one GPU).
+    void UseDevices(const std::vector<int>& devices);
+    std::size_t multi_gpu_min_rays = 262144;
+    int devices_in_use() const;
 
     // One node of the BVH in the reference's exchange format (60 bytes, align 4).
     struct BiTreeNode {

@@ -120,6 +120,8 @@ typedef struct b2col_stats {
 
 /* ---- lifecycle ------------------------------------------------------------------------------ */
 int b2col_abi_version(void);
+/* CUDA devices visible to this process (0 and B2COL_ERR_NO_DEVICE when there is none: the library has no CPU path) */
+b2col_status b2col_device_count(int* out);
 /* replaces: CollisionSystem::CollisionSystem(Scene*) — reference src/system_collisions.cpp:104 */
 b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg /* may be NULL */);
 void b2col_destroy(b2col_ctx* ctx);

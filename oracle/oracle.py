@@ -218,7 +218,7 @@ class RefEngine:
         self.lib.refh_set_static(self.h, C.c_size_t(entity.shape[0]), _p(entity), C.c_int(1 if is_static else 0))
 
     SHIM_OPTIONS = {"collider_check_interval": 0, "rebuild_interval": 1, "skip_static_rows": 2, "write_back_world_matrices": 3, "static_rescan_interval": 4,
-                    "full_uploads": 10, "sparse_uploads": 11}
+                    "use_devices": 5, "multi_gpu_min_rays": 6, "full_uploads": 10, "sparse_uploads": 11, "devices_in_use": 12}
 
     def shim_option(self, name: str, value: int = 0) -> int:
         """knobs / counters of the drop-in shims (no-op in the reference build)"""
@@ -351,6 +351,14 @@ class DropinEngine(RefEngine):
         out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
         self.lib.refh_raycast_batch(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(out))
         return out
+
+    def raycast_hits_expanded(self, rays, threads: int = 2):
+        """drop-in GetRaycastHits (12-byte results) + ExpandHits on the host: (hits as (n,3) uint32 words, Raycasts)"""
+        rays = as_rays(rays)
+        hits = np.zeros((rays.shape[0], 3), np.uint32)
+        out = np.zeros(rays.shape[0], RAYCAST_DTYPE)
+        self.lib.refh_raycast_hits_expanded(self.h, C.c_size_t(rays.shape[0]), _p(rays), _p(hits), _p(out), C.c_int(threads))
+        return hits, out
 
     def batched_counters(self) -> dict:
         out = np.zeros(4, np.uint64)

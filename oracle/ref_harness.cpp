@@ -107,7 +107,8 @@ void refh_set_static(void* h, size_t n, const uint32_t* entity, int is_static)
 }
 
 // knobs / counters of the drop-in shims (no-ops in the reference build). key: 0 collider_check_interval, 1 rebuild_interval,
-// 2 skip_static_rows, 3 write_back_world_matrices, 4 static_rescan_interval; returns 10: full uploads, 11: sparse uploads
+// 2 skip_static_rows, 3 write_back_world_matrices, 4 static_rescan_interval, 5 UseDevices(0..value-1), 6 multi_gpu_min_rays;
+// returns 10: full uploads, 11: sparse uploads, 12: devices in use
 long refh_shim_option(void* h, int key, long value)
 {
     auto* H = static_cast<Harness*>(h);
@@ -118,6 +119,13 @@ long refh_shim_option(void* h, int key, long value)
     auto* cs = H->scene.GetSystem<CollisionSystem>();
     if (key == 0) cs->collider_check_interval = static_cast<unsigned>(value);
     if (key == 1) cs->rebuild_interval = static_cast<unsigned>(value);
+    if (key == 5) {
+        std::vector<int> devices;
+        for (long d = 0; d < value; ++d) devices.push_back(static_cast<int>(d));
+        cs->UseDevices(devices);
+    }
+    if (key == 6) cs->multi_gpu_min_rays = static_cast<std::size_t>(value);
+    if (key == 12) return cs->devices_in_use();
 #ifdef B2COL_DROPIN_TRANSFORM
     auto* ts = H->scene.GetSystem<TransformSystem>();
     if (key == 2) ts->skip_static_rows = value != 0;
@@ -281,6 +289,13 @@ void refh_normalize(const float* v3, float* out3)
 void refh_raycast_batch(void* h, size_t n, const void* rays24, void* out36)
 {
     static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>()->GetRaycasts(static_cast<const Ray*>(rays24), n, static_cast<Raycast*>(out36));
+}
+// compact results, then the host expansion to Raycasts (both additive)
+void refh_raycast_hits_expanded(void* h, size_t n, const void* rays24, void* hits12, void* out36, int threads)
+{
+    auto* cs = static_cast<Harness*>(h)->scene.GetSystem<CollisionSystem>();
+    cs->GetRaycastHits(static_cast<const Ray*>(rays24), n, static_cast<CollisionSystem::RaycastHit*>(hits12));
+    CollisionSystem::ExpandHits(static_cast<const Ray*>(rays24), static_cast<const CollisionSystem::RaycastHit*>(hits12), n, static_cast<Raycast*>(out36), threads);
 }
 #endif
 

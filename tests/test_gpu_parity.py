@@ -707,6 +707,38 @@ def test_dropin_shim_inside_reference_scene(port):
     assert_raycast_equal(drop.raycast_batch(rays), ref.raycast(rays), "frame 2", ignore_entity_on=ties > 0)
 
 
+@pytest.mark.skipif(not DropinEngine.available(), reason="drop-in harness not built (needs /root/reference at build time)")
+def test_dropin_compact_hits_and_device_sets():
+    """Additive API of the drop-in CollisionSystem: GetRaycastHits + ExpandHits give GetRaycasts' bytes; with UseDevices (>= 2 GPUs)
+    large batches are cut across the GPUs after one tree broadcast — same bytes again, also after the next update."""
+    s = synth.game_scene(5000)
+    rays = np.concatenate([synth.game_rays(200), synth.random_rays(600_000, seed=96, extent=150, normalised=False)])
+    e = DropinEngine()
+    e.create_entities(s.parent[1:], s.pos[1:], s.rot[1:], s.scl[1:])
+    e.add_colliders(s.collider_entity, s.collider_aabb)
+    e.scene_update()
+    want = e.raycast_batch(rays)
+    assert want["hit"].sum() > 1000
+    hits, expanded = e.raycast_hits_expanded(rays, threads=3)
+    assert (expanded.view(np.uint8) == want.view(np.uint8)).all()
+    assert ((hits[:, 2] & 1) == want["hit"]).all() and (hits[:, 0] == want["hit_entity"]).all()
+    if torch.cuda.device_count() < 2:
+        return
+    n_dev = min(torch.cuda.device_count(), 8)
+    e.shim_option("use_devices", n_dev)
+    assert e.shim_option("devices_in_use") == n_dev
+    e.shim_option("multi_gpu_min_rays", 100_000)
+    assert (e.raycast_batch(rays).view(np.uint8) == want.view(np.uint8)).all()
+    s.pos[1:400] += 2.5  # next frame: the replicas must follow the new tree
+    e.set_trs(np.arange(1, s.n_entities + 1, dtype=np.uint32), s.pos[1:], s.rot[1:], s.scl[1:])
+    e.scene_update()
+    multi = e.raycast_batch(rays)
+    e.shim_option("multi_gpu_min_rays", 1 << 40)  # back to one GPU: the reference for the new frame
+    single = e.raycast_batch(rays)
+    assert (multi.view(np.uint8) == single.view(np.uint8)).all()
+    assert (single.view(np.uint8) != want.view(np.uint8)).any()
+
+
 @pytest.mark.skipif(not (Dropin2Engine.available() and RefEngine.available()), reason="drop-in harness not built (needs /root/reference at build time)")
 def test_dropin_transform_and_collision_shims_inside_reference_scene(port):
     """SURVEY.md 8(f) row 1: the reference's Scene::Update with BOTH systems replaced — TransformSystem (AoS

@@ -29,5 +29,7 @@ for name, scene in ((f"flat {n}", synth.uniform_boxes(n)), (f"hier {n}", synth.h
     fused = len(a) - cs.stats()["sort_passes"] == 4
     names = ["setup"] + (["propagate+refit(%d launches)" % levels] if fused else ["propagate(%d launches)" % levels, "refit"]) + ["morton"]
     names += [f"radix{p}" for p in range(len(a) - len(names) - 1)] + ["build"]
+    if os.environ.get("B2COL_SORT", "") != "lsd":  # MSD pipeline: [setup, transform/refit phases..., morton, msd pass, local sort, build]
+        names = [f"p{i}" for i in range(len(a) - 4)] + ["morton", "msd", "local", "build"]
     print(name, " ".join(f"{nm}={v:.1f}" for nm, v in zip(names, a)), f"sum={a.sum():.1f} us")
     cs.close()

@@ -10,7 +10,7 @@ from engine_b200.collision import CollisionSystem  # noqa: E402
 def main():
     n = int(os.environ.get("N_COL", 1_000_000))
     for name, scene in ((f"flat {n}", synth.uniform_boxes(n)), (f"hier {n} (1000 roots, depth 3)", synth.hierarchy_scene(n, 1000))):
-        cs = CollisionSystem()
+        cs = CollisionSystem(use_cuda_graph=os.environ.get('GRAPH', '1') != '0')
         cs.set_scene(scene)
         for _ in range(5):
             cs.on_update(wait=False)
