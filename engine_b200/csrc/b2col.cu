@@ -633,6 +633,8 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     }
 }
 
+#include "b2col_build.inl"  // k_build_direct: the same hierarchy, block-local nodes computed from range queries instead of climbed
+
 // Compact copy of the top levels of the tree, for trees larger than L2.
 //
 // A node lives at its split position, so the few thousand nodes of the upper levels — visited by every ray — are
@@ -1243,6 +1245,7 @@ struct b2col_ctx {
     int n_sm = 148;
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
     // sort pipeline of a full build: MSD pass + block-local sort (b2col_sort.cuh) where the buckets fit a block, LSD otherwise
+    bool build_climb = false;         // B2COL_BUILD=climb: k_build instead of k_build_direct
     int sort_policy = 0;              // 0 = automatic; 1 = always LSD; 2 = MSD whenever the keys are packed  (B2COL_SORT=lsd|msd)
     bool sort_msd = false;            // this frame's choice (part of the graph key)
     uint32_t* h_sort_stat = nullptr;  // page-locked: largest top-digit bucket of the last MSD frame, written by the frame itself
@@ -1501,6 +1504,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
+        if (const char* e = getenv("B2COL_BUILD")) c->build_climb = !strcmp(e, "climb");
         if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "lsd") ? 1 : (!strcmp(e, "msd") ? 2 : 0);
         cudaFuncSetAttribute(k_local_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem));
         if (cudaHostAlloc((void**)&c->h_sort_stat, sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess) *c->h_sort_stat = 0u;
@@ -1775,9 +1779,14 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
 // hierarchy + bounds from the sorted keys in d_keys/d_vals[side]
 static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
 {
-    LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
-           ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
-           ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+    if (ctx->build_climb)  // B2COL_BUILD=climb: the per-thread climb with shared-memory arrivals (A/B timing; same tree, same bytes)
+        LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+               ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
+               ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+    else
+        LAUNCH_FRAME(ctx, k_build_direct, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+               ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
+               ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
     ctx->scratch_clean = true;  // k_build leaves every scratch word zero
     // Trees that do not fit L2: compact copy of the top levels (see k_top_layout).  Below ~2M colliders the whole tree is
     // L2-resident and the copy buys nothing (measured at 1M: 1875 Mrays/s either way) but would cost the frame ~15 us.
