@@ -1245,7 +1245,7 @@ struct b2col_ctx {
     int n_sm = 148;
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
     // sort pipeline of a full build: MSD pass + block-local sort (b2col_sort.cuh) where the buckets fit a block, LSD otherwise
-    bool build_climb = false;         // B2COL_BUILD=climb: k_build instead of k_build_direct
+    int build_variant = 2;            // B2COL_BUILD=climb|direct|warp: k_build (0), k_build_direct (1), k_build_warp (2)
     int sort_policy = 0;              // 0 = automatic; 1 = always LSD; 2 = MSD whenever the keys are packed  (B2COL_SORT=lsd|msd)
     bool sort_msd = false;            // this frame's choice (part of the graph key)
     uint32_t* h_sort_stat = nullptr;  // page-locked: largest top-digit bucket of the last MSD frame, written by the frame itself
@@ -1504,7 +1504,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
-        if (const char* e = getenv("B2COL_BUILD")) c->build_climb = !strcmp(e, "climb");
+        if (const char* e = getenv("B2COL_BUILD")) c->build_variant = !strcmp(e, "climb") ? 0 : (!strcmp(e, "direct") ? 1 : 2);
         if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "lsd") ? 1 : (!strcmp(e, "msd") ? 2 : 0);
         cudaFuncSetAttribute(k_local_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem));
         if (cudaHostAlloc((void**)&c->h_sort_stat, sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess) *c->h_sort_stat = 0u;
@@ -1779,8 +1779,12 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
 // hierarchy + bounds from the sorted keys in d_keys/d_vals[side]
 static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
 {
-    if (ctx->build_climb)  // B2COL_BUILD=climb: the per-thread climb with shared-memory arrivals (A/B timing; same tree, same bytes)
+    if (ctx->build_variant == 0)  // B2COL_BUILD=climb: the per-thread climb with shared-memory arrivals (A/B timing; same tree, same bytes)
         LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
+               ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
+               ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+    else if (ctx->build_variant == 2)
+        LAUNCH_FRAME(ctx, k_build_warp, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
                ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
     else

@@ -251,3 +251,185 @@ k_build_direct(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __
         }
     }
 }
+
+// k_build_warp: k_build with the lowest levels of the climb done by WARP ROUNDS instead of arrivals.
+//
+// The roots of the partial subtrees over a warp's 32 consecutive leaves always partition those leaves into contiguous
+// ranges; the root of the range starting at leaf x stays with lane x - warp_base.  Range A = [l..r] joins its right
+// neighbour iff the split beyond r is the lower of its two outer splits; the neighbour B = [r+1..] joins to the left iff
+// the split before it is its lower one.  When both hold they are siblings (their parent is node r), and A learns that
+// with shuffles from lane r+1 - warp_base: no arrival word, no atomic, no divergence — every round all mutual pairs of
+// the warp merge at once, A stores the finished 32-byte node in ONE piece and carries the union on, B retires.  A few
+// rounds (the height of the forest inside 32 leaves) finish ~29 of every 31 nodes; the roots that are left — subtrees
+// whose parent spans a warp boundary — continue with k_build's arrival protocol (shared-memory exchange inside the
+// block, global exchange across blocks).  Same nodes, same bytes as k_build.
+__global__ void __launch_bounds__(BUILD_BLOCK)
+k_build_warp(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes,
+             LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
+{
+    pdl_wait();
+    for (uint32_t w = blockIdx.x * BUILD_BLOCK + threadIdx.x; w < scratch_words; w += gridDim.x * BUILD_BLOCK) scratch[w] = 0u;  // as k_build
+    __shared__ uint32_t s_lev[BUILD_BLOCK + 1];
+    __shared__ uint32_t s_wmax[2][BUILD_BLOCK / 32];
+    __shared__ uint8_t s_local[BUILD_BLOCK + 1];
+    __shared__ Xch s_xch[BUILD_BLOCK + 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t b0 = blockIdx.x * BUILD_BLOCK;
+    const uint32_t i = b0 + (uint32_t)tid;
+    const bool valid = i < n;
+    const Grid grid = hdr->grid;
+
+    QBox box;
+    box.w[0] = box.w[1] = box.w[2] = 0u;
+    uint64_t key = 0ull;
+    uint32_t lev_l = LEVEL_END;
+    bool wild = false;
+    if (valid) {
+        const LeafRec rec = DevOps::load_leaf(&world_rec[sorted_prim[i]]);
+        DevOps::store_leaf(&leaves[i], rec);
+        box = quantise_box(rec.lo, rec.hi, grid);
+        wild = box_is_wild(rec.lo, rec.hi);
+        key = keys[i];
+        if (i > 0u) lev_l = split_level(keys[i - 1u], key, i - 1u);
+    }
+    if (n == 1u) {
+        if (i == 0u) {
+            QNode nd;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) nd.w[k] = nd.w[3 + k] = box.w[k];
+            nd.w[6] = LEAF_BIT | (wild ? WILD_BIT : 0u) | 0u;
+            nd.w[7] = nd.w[6];
+            DevOps::store_qnode(&qnodes[0], nd);
+            hdr->root = 0u;
+            hdr->trace_root = 0u;
+            hdr->top_count = 0u;
+            hdr->has_wild = wild ? 1u : 0u;
+        }
+        return;
+    }
+    s_lev[tid] = lev_l;
+    *reinterpret_cast<uint4*>(&s_xch[tid]) = make_uint4(0u, 0u, 0u, UNVISITED);
+    if (tid == BUILD_BLOCK - 1) {
+        s_lev[BUILD_BLOCK] = (valid && i + 1u < n) ? split_level(key, keys[i + 1u], i) : LEVEL_END;
+        *reinterpret_cast<uint4*>(&s_xch[BUILD_BLOCK]) = make_uint4(0u, 0u, 0u, UNVISITED);
+    }
+    uint32_t pm = lev_l, sx = lev_l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, pm, o), c = __shfl_down_sync(0xffffffffu, sx, o);
+        if (lane >= o) pm = max(pm, a);
+        if (lane + o < 32) sx = max(sx, c);
+    }
+    if (lane == 31) s_wmax[0][warp] = pm;
+    if (lane == 0) s_wmax[1][warp] = sx;
+    __syncthreads();
+    {
+        uint32_t before = 0u, after = s_lev[BUILD_BLOCK];
+#pragma unroll
+        for (int w = 0; w < BUILD_BLOCK / 32; ++w) {
+            if (w < warp) before = max(before, s_wmax[0][w]);
+            if (w > warp) after = max(after, s_wmax[1][w]);
+        }
+        const uint32_t pm_in = __shfl_up_sync(0xffffffffu, pm, 1), sx_in = __shfl_down_sync(0xffffffffu, sx, 1);
+        const uint32_t left_max = max(before, lane > 0 ? pm_in : 0u);
+        const uint32_t right_max = max(after, lane < 31 ? sx_in : 0u);
+        s_local[tid] = (tid > 0 && left_max > lev_l && right_max > lev_l) ? 1 : 0;
+        if (tid == 0) s_local[BUILD_BLOCK] = 0;
+    }
+    __syncthreads();
+
+    // ---- phase 1: warp rounds
+    uint32_t l = i, r = i;
+    uint32_t lev_r = s_lev[tid + 1];
+    uint32_t refw = LEAF_BIT | i | (wild ? WILD_BIT : 0u);  // this subtree's child ref incl. the wild flag
+    bool active = valid;
+    const uint32_t wbase = i - (uint32_t)lane;
+    for (;;) {
+        const bool want_right = active && lev_r < lev_l;  // joins the neighbour beyond the LOWER split; array ends never win
+        const uint32_t pl = r + 1u - wbase;               // lane holding the root of the range that starts behind mine
+        const int src = (int)(pl & 31u);
+        const uint32_t o_r = __shfl_sync(0xffffffffu, r, src);
+        const uint32_t o_lv = __shfl_sync(0xffffffffu, lev_r | (want_right ? 0x100u : 0u), src);
+        const uint32_t o_b0 = __shfl_sync(0xffffffffu, box.w[0], src);
+        const uint32_t o_b1 = __shfl_sync(0xffffffffu, box.w[1], src);
+        const uint32_t o_b2 = __shfl_sync(0xffffffffu, box.w[2], src);
+        const uint32_t o_ref = __shfl_sync(0xffffffffu, refw, src);
+        const bool merge = want_right && pl < 32u && !(o_lv & 0x100u);  // the neighbour wants to join to the left: siblings, parent = node r
+        const uint32_t taken = __reduce_or_sync(0xffffffffu, merge ? 1u << src : 0u);
+        if (taken == 0u) break;
+        if (merge) {
+            const uint32_t p = r;
+            QNode nd;
+            nd.w[0] = box.w[0];
+            nd.w[1] = box.w[1];
+            nd.w[2] = box.w[2];
+            nd.w[3] = o_b0;
+            nd.w[4] = o_b1;
+            nd.w[5] = o_b2;
+            nd.w[6] = refw;
+            nd.w[7] = o_ref;
+            DevOps::store_qnode(&qnodes[p], nd);
+            box.w[0] = qplane_merge(box.w[0], o_b0);
+            box.w[1] = qplane_merge(box.w[1], o_b1);
+            box.w[2] = qplane_merge(box.w[2], o_b2);
+            refw = p | ((refw | o_ref) & WILD_BIT);
+            r = o_r;
+            lev_r = o_lv & 0xFFu;
+            if (lev_l == LEVEL_END && lev_r == LEVEL_END) {  // the range is the whole array (a tree inside one warp)
+                hdr->root = p;
+                hdr->trace_root = p;
+                hdr->top_count = 0u;
+                hdr->has_wild = (refw & WILD_BIT) ? 1u : 0u;
+                active = false;
+            }
+        }
+        if ((taken >> lane) & 1u) active = false;  // merged into the left neighbour's subtree
+    }
+    if (!active) return;
+
+    // ---- phase 2: the remaining roots climb with k_build's arrival protocol
+    wild = (refw & WILD_BIT) != 0u;
+    uint32_t ref = refw & ~WILD_BIT;
+    for (;;) {
+        const bool is_left = lev_r < lev_l;
+        const uint32_t p = is_left ? r : l - 1u;
+        const uint32_t j = p - (b0 - 1u);
+        const bool local = j <= (uint32_t)BUILD_BLOCK && s_local[j] != 0;
+        QBox sib;
+        uint32_t bound, level;
+        bool sib_wild;
+        DevOps::store_ref(&qnodes[p], is_left ? 0 : 1, ref | (wild ? WILD_BIT : 0u));
+        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r, wild);
+        Xch got;
+        if (local) {
+            got = DevOps::exchange_shared(&s_xch[j], mine);
+            if (got.w[3] == UNVISITED) return;
+        }
+        else {
+            got = DevOps::exchange(&xch[p], mine);
+            if (got.w[3] == UNVISITED) return;
+            *reinterpret_cast<uint4*>(&xch[p]) = make_uint4(0u, 0u, 0u, UNVISITED);
+        }
+        xch_unpack(got, sib, bound, level, sib_wild);
+        wild = wild || sib_wild;
+        DevOps::store_qboxes(&qnodes[p], is_left ? box.w : sib.w, is_left ? sib.w : box.w);
+        if (is_left) {
+            r = bound;
+            lev_r = level;
+        }
+        else {
+            l = bound;
+            lev_l = level;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) box.w[k] = qplane_merge(box.w[k], sib.w[k]);
+        ref = p;
+        if (lev_l == LEVEL_END && lev_r == LEVEL_END) {
+            hdr->root = p;
+            hdr->trace_root = p;
+            hdr->top_count = 0u;
+            hdr->has_wild = wild ? 1u : 0u;
+            return;
+        }
+    }
+}

@@ -1,7 +1,7 @@
 #!/bin/bash
 # MSD sort: correctness first, then A/B timing, then the whole suite and the bench
 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "build or refit or degenerate or config" 2>&1 | tail -8
-for s in lsd msd; do for b in climb direct; do echo "== B2COL_SORT=$s B2COL_BUILD=$b"; B2COL_BUILD=$b B2COL_SORT=$s python tools/time_update.py; B2COL_BUILD=$b B2COL_SORT=$s python tools/phase_timing.py; done; done
+for s in lsd msd; do for b in climb direct warp; do echo "== B2COL_SORT=$s B2COL_BUILD=$b"; B2COL_BUILD=$b B2COL_SORT=$s python tools/time_update.py; B2COL_BUILD=$b B2COL_SORT=$s python tools/phase_timing.py; done; done
 python -m pytest tests -m gpu -x -q 2>&1 | tail -25
 python tools/trace_timing.py | tail -1
 python bench.py --steps 5 --warmup 3 > gpurun_out/r2e_bench.json 2> gpurun_out/r2e_bench.err; echo rc=$?; tail -3 gpurun_out/r2e_bench.err
