@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb2col.so")
 SOURCES = ["b2col.cu"]
-HEADERS = ["b2col_math.cuh", "b2col_bvh.cuh", "b2col_sort.cuh", "b2col_build.inl", "b2col_comm.inl", "../../include/b2col.h"]
+HEADERS = ["b2col_math.cuh", "b2col_bvh.cuh", "b2col_sort.cuh", "b2col_build.inl", "b2col_trace.inl", "b2col_comm.inl", "../../include/b2col.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
