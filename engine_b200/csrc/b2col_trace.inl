@@ -169,6 +169,11 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
     bool pending = false;    // this lane's ray is finished but its Raycast is not written yet
     bool exhausted = false;  // warp-uniform: the pool has no rays left
     unsigned long long visits = 0ull;  // COUNT only
+#ifdef B2_REG_TOS
+    uint32_t tos_n = REF_EMPTY;
+    float tos_t = 0.0f;
+    bool has_tos = false;
+#endif
     auto exact_ray = [&]() {
         RayPre r;
 #pragma unroll
@@ -236,6 +241,24 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
 #pragma unroll
             for (int step = 0; step < B2_TRACE_STEPS; ++step) {
                 // ---- pop (predicated): a lane without a current node takes its most recent deferred child
+#ifdef B2_REG_TOS  // dev variant: the newest deferred child stays in registers; shared memory holds the older ones
+                if (active && cur == REF_EMPTY && !has_tos && sp == 0) {  // rare; lsp > 0 here
+                    lsp = trace_refill(sm, tid, l_node, l_t, lsp);
+                    sp = TRACE_SPILL;
+                }
+                const bool pop = active && cur == REF_EMPTY;
+                if (pop) {
+                    uint32_t pn = tos_n;
+                    float pt = tos_t;
+                    if (!has_tos) {
+                        --sp;
+                        pn = sm.node[sp][tid];
+                        pt = sm.t[sp][tid];
+                    }
+                    has_tos = false;
+                    cur = (pt <= lim) ? pn : REF_EMPTY;
+                }
+#else
                 if (active && cur == REF_EMPTY && sp == 0) {  // rare; lsp > 0 here
                     lsp = trace_refill(sm, tid, l_node, l_t, lsp);
                     sp = TRACE_SPILL;
@@ -245,23 +268,41 @@ __device__ __forceinline__ void trace_body(TraceSmem& sm, const b2col_ray* __res
                 const uint32_t pn = sm.node[sp][tid];  // sp < TRACE_SMEM_STACK always: harmless when not popping
                 const float pt = sm.t[sp][tid];
                 if (pop) cur = (pt <= lim) ? pn : REF_EMPTY;
+#endif
                 // ---- visit
                 if (cur != REF_EMPTY) {
                     if (COUNT) ++visits;
                     const QNode nd = DevOps::load_qnode(&qnodes[cur]);
                     const VisitOut v = visit_node<DevOps, WILD>(best, lim, q, nd, leaves, T, exact_ray);
+#ifdef B2_REG_TOS
+                    if (v.push) {
+                        if (has_tos) {
+                            sm.node[sp][tid] = tos_n;
+                            sm.t[sp][tid] = tos_t;
+                            ++sp;
+                        }
+                        tos_n = v.far;
+                        tos_t = v.tfar;
+                        has_tos = true;
+                    }
+#else
                     if (v.push) {
                         sm.node[sp][tid] = v.far;
                         sm.t[sp][tid] = v.tfar;
                     }
                     sp += v.push ? 1 : 0;
+#endif
                     cur = v.next;
                 }
                 if (sp == TRACE_SMEM_STACK) {  // rare
                     lsp = trace_spill(sm, tid, l_node, l_t, lsp);
                     sp = TRACE_SMEM_STACK - TRACE_SPILL;
                 }
+#ifdef B2_REG_TOS
+                if (active && cur == REF_EMPTY && sp == 0 && lsp == 0 && !has_tos) {
+#else
                 if (active && cur == REF_EMPTY && sp == 0 && lsp == 0) {
+#endif
                     active = false;
                     pending = true;
                 }

@@ -4,4 +4,6 @@ python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "build or refit or deg
 for s in lsd msd; do for b in climb direct warp; do echo "== B2COL_SORT=$s B2COL_BUILD=$b"; B2COL_BUILD=$b B2COL_SORT=$s python tools/time_update.py; B2COL_BUILD=$b B2COL_SORT=$s python tools/phase_timing.py; done; done
 python -m pytest tests -m gpu -x -q 2>&1 | tail -25
 python tools/trace_timing.py | tail -1
+echo "== register top-of-stack variant"; B2COL_LIB=variants/libb2col_regtos.so python tools/trace_timing.py | tail -1
+B2COL_LIB=variants/libb2col_regtos.so python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "golden or config3_1m or duplicate" 2>&1 | tail -3
 python bench.py --steps 5 --warmup 3 > gpurun_out/r2e_bench.json 2> gpurun_out/r2e_bench.err; echo rc=$?; tail -3 gpurun_out/r2e_bench.err

@@ -4,5 +4,5 @@ log=$1; shift
 for i in $(seq 1 40); do
   timeout 3400 gpurun "$@" > "$log" 2>&1
   if ! grep -q "status=transient" "$log"; then exit 0; fi
-  sleep 90
+  sleep 20
 done
