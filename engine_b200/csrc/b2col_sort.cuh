@@ -323,17 +323,20 @@ __device__ __forceinline__ uint32_t ls_scan_256(uint32_t v, uint32_t* warp_tot)
     return before + inc - v;
 }
 
-// Stable tile-local position of every pair held in registers (warp-striped: item k of lane l is element
-// warp * 512 + k * 32 + l of the tile) for the digit at `shift`; leaves sm.base / sm.cnt for the tile.
-__device__ __forceinline__ void ls_rank_tile(LocalSortSmem& sm, const uint64_t* key, uint32_t valid, int shift, uint32_t* pos)
+// Stable tile-local position of every pair held in registers for the digit at `shift`; leaves sm.base / sm.cnt for the
+// tile.  Layout: warp-striped over `items` rounds — item k < items of lane l is element warp * items * 32 + k * 32 + l —
+// where items = ceil(valid / LS_THREADS) is block-uniform: a bucket of 4096 pairs keeps all 16 warps busy for 8 rounds
+// instead of half of the warps for 16.
+__device__ __forceinline__ void ls_rank_tile(LocalSortSmem& sm, const uint64_t* key, uint32_t valid, int shift, uint32_t* pos, int items)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t wbase = (uint32_t)warp * (LS_ITEMS * 32u) + (uint32_t)lane;
+    const uint32_t wbase = (uint32_t)warp * ((uint32_t)items * 32u) + (uint32_t)lane;
     for (int i = tid; i < LS_WARPS * RS_RADIX; i += LS_THREADS) (&sm.whist[0][0])[i] = 0u;
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < LS_ITEMS; ++k) {
+        if (k >= items) break;  // block-uniform
         const bool ok = wbase + (uint32_t)k * 32u < valid;
         const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
         uint32_t peers = __ballot_sync(0xffffffffu, ok);
@@ -370,7 +373,7 @@ __device__ __forceinline__ void ls_rank_tile(LocalSortSmem& sm, const uint64_t* 
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < LS_ITEMS; ++k) {
-        if (wbase + (uint32_t)k * 32u < valid) {
+        if (k < items && wbase + (uint32_t)k * 32u < valid) {
             const uint32_t d = (uint32_t)(key[k] >> shift) & (RS_RADIX - 1);
             pos[k] += sm.base[d] + sm.whist[warp][d];
         }
@@ -389,7 +392,6 @@ k_local_sort(uint64_t* in, uint64_t* scratch, uint64_t* kout, uint32_t* vout, co
     cudaGridDependencySynchronize();
 #endif
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t wbase = (uint32_t)warp * (LS_ITEMS * 32u) + (uint32_t)lane;
     // this bucket's segment: exclusive scan of the top-digit histogram
     const uint32_t mine = tid < RS_RADIX ? top_hist[tid] : 0u;
     const uint32_t excl = ls_scan_256(mine, sm.warp_tot);
@@ -406,35 +408,38 @@ k_local_sort(uint64_t* in, uint64_t* scratch, uint64_t* kout, uint32_t* vout, co
     uint32_t pos[LS_ITEMS];
     if (count <= (uint32_t)LS_TILE) {
         // ---- the bucket fits the block: three LSD passes through registers and shared memory
+        const int items = (int)((count + LS_THREADS - 1u) / LS_THREADS);  // rounds this bucket needs (block-uniform)
+        const uint32_t wbase = (uint32_t)warp * ((uint32_t)items * 32u) + (uint32_t)lane;
 #pragma unroll
         for (int k = 0; k < LS_ITEMS; ++k) {
             const uint32_t idx = wbase + (uint32_t)k * 32u;
-            key[k] = idx < count ? in[start + idx] : ~0ull;
+            key[k] = (k < items && idx < count) ? in[start + idx] : ~0ull;
         }
 #pragma unroll 1
         for (int pass = 0; pass < 3; ++pass) {
-            ls_rank_tile(sm, key, count, 32 + RS_BITS * pass, pos);
+            ls_rank_tile(sm, key, count, 32 + RS_BITS * pass, pos, items);
 #pragma unroll
             for (int k = 0; k < LS_ITEMS; ++k)
-                if (wbase + (uint32_t)k * 32u < count) sm.keys[pos[k]] = key[k];
+                if (k < items && wbase + (uint32_t)k * 32u < count) sm.keys[pos[k]] = key[k];
             __syncthreads();
 #pragma unroll
             for (int k = 0; k < LS_ITEMS; ++k) {
                 const uint32_t idx = wbase + (uint32_t)k * 32u;
-                if (idx < count) key[k] = sm.keys[idx];
+                if (k < items && idx < count) key[k] = sm.keys[idx];
             }
             __syncthreads();
         }
 #pragma unroll
         for (int k = 0; k < LS_ITEMS; ++k) {
             const uint32_t idx = wbase + (uint32_t)k * 32u;
-            if (idx < count) {
+            if (k < items && idx < count) {
                 kout[start + idx] = key[k] >> 32;
                 vout[start + idx] = (uint32_t)key[k];
             }
         }
         return;
     }
+    const uint32_t wbase = (uint32_t)warp * (LS_ITEMS * 32u) + (uint32_t)lane;
     // ---- oversized bucket: the same three passes over the segment in global memory, tile after tile (exact, slow)
 #pragma unroll 1
     for (int pass = 0; pass < 3; ++pass) {
@@ -456,7 +461,7 @@ k_local_sort(uint64_t* in, uint64_t* scratch, uint64_t* kout, uint32_t* vout, co
                 const uint32_t idx = wbase + (uint32_t)k * 32u;
                 key[k] = idx < valid ? __ldcg(src + start + tile + idx) : ~0ull;  // written by this block in the pass before: read at L2
             }
-            ls_rank_tile(sm, key, valid, shift, pos);
+            ls_rank_tile(sm, key, valid, shift, pos, LS_ITEMS);
 #pragma unroll
             for (int k = 0; k < LS_ITEMS; ++k) {
                 if (wbase + (uint32_t)k * 32u < valid) {
