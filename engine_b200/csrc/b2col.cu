@@ -961,8 +961,9 @@ struct b2col_ctx {
     int n_sm = 148;
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
     // sort pipeline of a full build: MSD pass + block-local sort (b2col_sort.cuh) where the buckets fit a block, LSD otherwise
-    int build_variant = 2;            // B2COL_BUILD=climb|direct|warp: k_build (0), k_build_direct (1), k_build_warp (2)
-    int sort_policy = 0;              // 0 = automatic; 1 = always LSD; 2 = MSD whenever the keys are packed  (B2COL_SORT=lsd|msd)
+    // B2COL_BUILD=climb|direct|warp: k_build (0, default: measured fastest at 1M — 61.5 us vs 71.7 / 73.8, profiles/r2_experiments.txt), k_build_direct (1), k_build_warp (2)
+    int build_variant = 0;
+    int sort_policy = 1;              // 0 = automatic (MSD where the buckets fit); 1 = always LSD; 2 = MSD whenever the keys are packed  (B2COL_SORT=auto|lsd|msd)
     bool sort_msd = false;            // this frame's choice (part of the graph key)
     uint32_t* h_sort_stat = nullptr;  // page-locked: largest top-digit bucket of the last MSD frame, written by the frame itself
     int morton_blocks_per_sm = 0;  // 0 = by collider count; B2COL_MORTON_BLOCKS_PER_SM overrides (tuning)
@@ -1220,8 +1221,8 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
-        if (const char* e = getenv("B2COL_BUILD")) c->build_variant = !strcmp(e, "climb") ? 0 : (!strcmp(e, "direct") ? 1 : 2);
-        if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "lsd") ? 1 : (!strcmp(e, "msd") ? 2 : 0);
+        if (const char* e = getenv("B2COL_BUILD")) c->build_variant = !strcmp(e, "direct") ? 1 : (!strcmp(e, "warp") ? 2 : 0);
+        if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "auto") ? 0 : (!strcmp(e, "msd") ? 2 : 1);
         cudaFuncSetAttribute(k_local_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem));
         if (cudaHostAlloc((void**)&c->h_sort_stat, sizeof(uint32_t), cudaHostAllocDefault) == cudaSuccess) *c->h_sort_stat = 0u;
         else {

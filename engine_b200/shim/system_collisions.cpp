@@ -7,8 +7,11 @@
 #include <string>
 #include <typeinfo>
 
+#include <atomic>
+
 #include "b2col.h"
 #include "b2col_scene_ctx.h"
+#include "b2col_workers.h"
 #include "component_transform.h"
 #include "scene.h"
 
@@ -47,14 +50,17 @@ bool CollisionSystem::BoxesUnchanged(const ColliderComponent* base) const
 {
     static_assert(sizeof(ColliderComponent) == sizeof(AABB), "ColliderComponent is its AABB: runs of entities are runs of boxes");
     const std::size_t n = device_entities_.size();
-    std::size_t i = 0;
-    while (i < n) {
-        std::size_t j = i + 1;
-        while (j < n && device_entities_[j] == device_entities_[j - 1] + 1u) ++j;
-        if (std::memcmp(&base[device_entities_[i]], &device_boxes_[i], (j - i) * sizeof(AABB)) != 0) return false;
-        i = j;
-    }
-    return true;
+    std::atomic<bool> same{true};
+    B2colWorkers::Get().ParallelFor(n, 65536, [&](std::size_t lo, std::size_t hi) {
+        std::size_t i = lo;
+        while (i < hi && same.load(std::memory_order_relaxed)) {
+            std::size_t j = i + 1;
+            while (j < hi && device_entities_[j] == device_entities_[j - 1] + 1u) ++j;
+            if (std::memcmp(&base[device_entities_[i]], &device_boxes_[i], (j - i) * sizeof(AABB)) != 0) same.store(false, std::memory_order_relaxed);
+            i = j;
+        }
+    });
+    return same.load();
 }
 
 void CollisionSystem::onUpdate(float ts)
@@ -78,7 +84,9 @@ void CollisionSystem::onUpdate(float ts)
     if (!same_set) {
         device_entities_.assign(m_entities.begin(), m_entities.end());  // ascending IDs (std::set), the reference's own iteration order
         device_boxes_.resize(device_entities_.size());
-        for (std::size_t i = 0; i < device_entities_.size(); ++i) device_boxes_[i] = cbase[device_entities_[i]].aabb;
+        B2colWorkers::Get().ParallelFor(device_entities_.size(), 65536, [&](std::size_t lo, std::size_t hi) {
+            for (std::size_t i = lo; i < hi; ++i) device_boxes_[i] = cbase[device_entities_[i]].aabb;
+        });
         seen_inserts_ = colliders_inserted_;
         frames_since_check_ = 0;
     }
@@ -91,7 +99,9 @@ void CollisionSystem::onUpdate(float ts)
         gather_world_.resize(16u * (static_cast<std::size_t>(n_entities) + 1u));
         const Entity first = device_entities_.front();
         const TransformComponent* tbase = m_scene->GetComponent<TransformComponent>(first) - first;
-        for (Entity entity : device_entities_) std::memcpy(&gather_world_[16u * entity], &tbase[entity].world_matrix, 64);
+        B2colWorkers::Get().ParallelFor(device_entities_.size(), 16384, [&](std::size_t lo, std::size_t hi) {
+            for (std::size_t i = lo; i < hi; ++i) std::memcpy(&gather_world_[16u * device_entities_[i]], &tbase[device_entities_[i]].world_matrix, 64);
+        });
         Check(b2col_set_world_matrices(ctx_, n_entities, gather_world_.data()), "b2col_set_world_matrices");
     }
     if (same_set && rebuild_interval > 1 && frames_since_build_ + 1 < rebuild_interval) {

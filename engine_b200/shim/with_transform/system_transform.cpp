@@ -10,7 +10,9 @@
 //     (include/component_transform.h:24) — gathers their TRS straight into page-locked staging and uploads those rows
 //     (b2col_stage_trs_rows / b2col_commit_trs_rows: 44 bytes per MOVED entity),
 //   * writes world_matrix back only where it can have changed: non-static entities and their descendants, gathered on
-//     the device into one copy (b2col_fetch_world_rows).
+//     the device into one copy (b2col_fetch_world_rows),
+//   * cuts the two per-entity loops that remain (TRS gather, world_matrix scatter: one cache miss per entity on a 144-byte
+//     stride) into slices over a few helper threads (b2col_workers.h).
 #include "system_transform.h"
 
 #include <cstring>
@@ -18,8 +20,11 @@
 #include <string>
 #include <typeinfo>
 
+#include <atomic>
+
 #include "b2col.h"
 #include "b2col_scene_ctx.h"
+#include "b2col_workers.h"
 #include "component_transform.h"
 #include "scene.h"
 
@@ -94,22 +99,24 @@ void TransformSystem::onUpdate(float ts)
         uint32_t* ids = nullptr;
         float *p = nullptr, *r = nullptr, *s = nullptr;
         Check(b2col_stage_trs_rows(shared_->ctx, n, &ids, &p, &r, &s), "b2col_stage_trs_rows");
-        uint32_t k = 0;
-        for (uint32_t i = 0; i < n; ++i) {
-            const Entity e = dynamic_[i];
-            const TransformComponent& t = base[e];
-            if (t.parent != parent_[e] || t.is_static) {  // re-parented, or no longer dynamic: take the long road this frame
-                full = true;
-                break;
+        std::atomic<bool> changed{false};  // an entity was re-parented or is no longer dynamic: take the long road this frame
+        B2colWorkers::Get().ParallelFor(n, 16384, [&](std::size_t lo, std::size_t hi) {
+            for (std::size_t i = lo; i < hi; ++i) {
+                const Entity e = dynamic_[i];
+                const TransformComponent& t = base[e];
+                if (t.parent != parent_[e] || t.is_static) {
+                    changed.store(true, std::memory_order_relaxed);
+                    return;
+                }
+                ids[i] = e;
+                std::memcpy(p + 3u * i, &t.position, 12);
+                std::memcpy(r + 4u * i, &t.rotation, 16);
+                std::memcpy(s + 3u * i, &t.scale, 12);
             }
-            ids[k] = e;
-            std::memcpy(p + 3u * k, &t.position, 12);
-            std::memcpy(r + 4u * k, &t.rotation, 16);
-            std::memcpy(s + 3u * k, &t.scale, 12);
-            ++k;
-        }
+        });
+        full = changed.load();
         if (!full) {
-            Check(b2col_commit_trs_rows(shared_->ctx, k), "b2col_commit_trs_rows");
+            Check(b2col_commit_trs_rows(shared_->ctx, n), "b2col_commit_trs_rows");
             ++sparse_uploads;
         }
         else Check(b2col_commit_trs_rows(shared_->ctx, 0), "b2col_commit_trs_rows");
@@ -128,7 +135,9 @@ void TransformSystem::onUpdate(float ts)
     const std::vector<uint32_t>& rows = first_frame_of_layout ? entities_ : writeback_;  // a new layout writes every row once
     const float* w = nullptr;
     Check(b2col_fetch_world_rows(shared_->ctx, static_cast<uint32_t>(rows.size()), rows.data(), &w), "b2col_fetch_world_rows");
-    for (std::size_t i = 0; i < rows.size(); ++i) std::memcpy(&base[rows[i]].world_matrix, w + 16u * i, 64);
+    B2colWorkers::Get().ParallelFor(rows.size(), 16384, [&](std::size_t lo, std::size_t hi) {
+        for (std::size_t i = lo; i < hi; ++i) std::memcpy(&base[rows[i]].world_matrix, w + 16u * i, 64);
+    });
 }
 
 Entity TransformSystem::GetChildEntity(Entity parent, const std::string& tag)
