@@ -952,6 +952,12 @@ struct b2col_ctx {
     DevBuf d_small_counters;   // SMALL_SLOTS x u64, all zero beyond small_next
     size_t small_next = SMALL_SLOTS;
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
+    // second trace stream of the pipeline (B2COL_E2E_STREAMS=2): chunks alternate between ctx->stream and this one, so that the
+    // tail of one chunk's persistent kernel (its last rays, most SMs idle) overlaps the head of the next chunk's
+    cudaStream_t stream_trace2 = nullptr;
+    cudaEvent_t pipe_start_ev = nullptr;
+    DevBuf d_pipe_counters;  // one pre-zeroed work counter per chunk (the kernels of two streams must not share one)
+    int e2e_streams = 1;
     std::vector<cudaEvent_t> pipe_events;
     // device->host leg of the pipeline: 0 = copy engine (default), 1 = SM stores (k_copy_out), -1 = measure both and keep the
     // faster (big calls only); B2COL_D2H_MODE=ce|sm|auto.  Measured (profiles/r1_e_d2h_modes.txt): alone on the host the copy
@@ -1106,7 +1112,9 @@ inline LeafRec* blob_leaves(const b2col_ctx* c, uint32_t n_leaves)
         if (s_ != B2COL_OK) return s_;      \
     } while (0)
 
-b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode, bool remote_out = false, bool compact = false)
+// `on` / `counter`: launch on another stream of the context with a work counter the caller has already zeroed (chunked pipeline)
+b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode, bool remote_out = false, bool compact = false,
+                           cudaStream_t on = nullptr, unsigned long long* counter = nullptr)
 {
     const size_t out_bytes = compact ? 12 : sizeof(b2col_raycast);  // compact: d_out is an array of b2col_hit
     if (n == 0) return B2COL_OK;
@@ -1121,11 +1129,19 @@ b2col_status enqueue_trace(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2
             CU(cudaMemsetAsync(d_out, 0, n * out_bytes, ctx->stream));
             return B2COL_OK;
         }
+        const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        if (on && counter && !count) {
+            if (compact) k_trace_lbvh<false, false, true><<<grid, TRACE_BLOCK, 0, on>>>(d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                                                                                      blob_leaves(ctx, ctx->tree_leaves), ctx->T, counter, ctx->fetch_threshold);
+            else k_trace_lbvh<false, false><<<grid, TRACE_BLOCK, 0, on>>>(d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+                                                                        blob_leaves(ctx, ctx->tree_leaves), ctx->T, counter, ctx->fetch_threshold);
+            ++ctx->launches;
+            if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return fail(ctx, B2COL_ERR_CUDA, "launch of k_trace_lbvh failed: %s", cudaGetErrorString(e));
+            return B2COL_OK;
+        }
         GUARD(ensure(ctx, ctx->d_counter, 16));
         CU(cudaMemsetAsync(ctx->d_counter.p, 0, 16, ctx->stream));
-        const uint32_t grid = (uint32_t)std::min<size_t>((size_t)ctx->trace_grid, (n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-        if (count) {
-            LAUNCH(ctx, (k_trace_lbvh<true, false>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
+        if (count) {            LAUNCH(ctx, (k_trace_lbvh<true, false>), grid, TRACE_BLOCK, d_rays, (unsigned long long)n, d_out, blob_hdr(ctx), blob_qnodes(ctx),
                    blob_leaves(ctx, ctx->tree_leaves), ctx->T, ctx->d_counter.as<unsigned long long>(), ctx->fetch_threshold);
             unsigned long long v = 0;
             CU(cudaMemcpyAsync(&v, ctx->d_counter.as<unsigned long long>() + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1212,6 +1228,7 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         if (const char* e = getenv("B2COL_TRACE_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));  // tuning knobs
         if (const char* e = getenv("B2COL_E2E_CHUNK")) c->e2e_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         if (const char* e = getenv("B2COL_E2E_FIRST_CHUNK")) c->e2e_first_chunk = std::max<size_t>(1024, (size_t)atoll(e));
+        if (const char* e = getenv("B2COL_E2E_STREAMS")) c->e2e_streams = atoi(e) >= 2 ? 2 : 1;
         if (const char* e = getenv("B2COL_E2E_MIN_CHUNK")) c->e2e_min_chunk = std::max<size_t>(1024, (size_t)atoll(e));
         c->e2e_chunk = std::max(c->e2e_chunk, c->e2e_first_chunk);
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
@@ -1264,6 +1281,9 @@ void b2col_destroy(b2col_ctx* ctx)
     for (auto& ev : ctx->events)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->pipe_events) cudaEventDestroy(ev);
+    if (ctx->stream_trace2) cudaStreamDestroy(ctx->stream_trace2);
+    if (ctx->pipe_start_ev) cudaEventDestroy(ctx->pipe_start_ev);
+    release(ctx->d_pipe_counters);
     if (ctx->stream_in) cudaStreamDestroy(ctx->stream_in);
     if (ctx->stream_out) cudaStreamDestroy(ctx->stream_out);
     cudaStreamDestroy(ctx->stream);
@@ -1976,6 +1996,18 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
         }
         const auto t_begin = std::chrono::steady_clock::now();
         size_t off = 0, m = first_chunk, c = 0;
+        const bool two = ctx->e2e_streams >= 2 && ctx->have_tree && ctx->tree_leaves > 0;
+        if (two) {
+            if (!ctx->stream_trace2) {
+                CU(cudaStreamCreateWithFlags(&ctx->stream_trace2, cudaStreamNonBlocking));
+                CU(cudaEventCreateWithFlags(&ctx->pipe_start_ev, cudaEventDisableTiming));
+            }
+            const size_t max_chunks = n / first_chunk + 2;
+            GUARD(ensure(ctx, ctx->d_pipe_counters, max_chunks * 16));
+            CU(cudaMemsetAsync(ctx->d_pipe_counters.p, 0, max_chunks * 16, ctx->stream));
+            CU(cudaEventRecord(ctx->pipe_start_ev, ctx->stream));  // behind the tree's build and the counters' memset
+            CU(cudaStreamWaitEvent(ctx->stream_trace2, ctx->pipe_start_ev, 0));
+        }
         while (off < n) {
             m = std::min(m, n - off);
             if (n - off - m < first_chunk) m = n - off;  // no tiny tail chunk
@@ -1987,9 +2019,11 @@ static b2col_status raycast_batch_begin(b2col_ctx* ctx, const b2col_ray* h_rays,
             cudaEvent_t ev_in = ctx->pipe_events[2 * c], ev_k = ctx->pipe_events[2 * c + 1];
             CU(cudaMemcpyAsync(d_r + off, h_rays + off, m * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream_in));
             CU(cudaEventRecord(ev_in, ctx->stream_in));
-            CU(cudaStreamWaitEvent(ctx->stream, ev_in, 0));
-            GUARD(enqueue_trace(ctx, d_r + off, m, reinterpret_cast<b2col_raycast*>(d_h + off * out_bytes), mode, false, compact));
-            CU(cudaEventRecord(ev_k, ctx->stream));
+            cudaStream_t ts = (two && (c & 1)) ? ctx->stream_trace2 : ctx->stream;
+            CU(cudaStreamWaitEvent(ts, ev_in, 0));
+            GUARD(enqueue_trace(ctx, d_r + off, m, reinterpret_cast<b2col_raycast*>(d_h + off * out_bytes), mode, false, compact, two ? ts : nullptr,
+                                two ? ctx->d_pipe_counters.as<unsigned long long>() + 2 * c : nullptr));
+            CU(cudaEventRecord(ev_k, ts));
             CU(cudaStreamWaitEvent(ctx->stream_out, ev_k, 0));
             if (d2h == 1) {
                 k_copy_out<<<2 * ctx->n_sm, 256, 0, ctx->stream_out>>>(reinterpret_cast<const uint32_t*>(d_h + off * out_bytes), h_out_dev + out_words * off, out_words * m);
@@ -2030,6 +2064,7 @@ static b2col_status raycast_batch_end(b2col_ctx* ctx)
     if (pb.pipeline) {
         CU(cudaStreamSynchronize(ctx->stream_out));
         CU(cudaStreamSynchronize(ctx->stream));
+        if (ctx->stream_trace2) CU(cudaStreamSynchronize(ctx->stream_trace2));
         if (pb.timed && pb.has_dev_out && ctx->d2h_policy < 0) {
             const double ns = std::chrono::duration<double, std::nano>(std::chrono::steady_clock::now() - pb.t_begin).count() / (double)pb.n;
             double& est = ctx->d2h_ns_per_ray[pb.d2h];
