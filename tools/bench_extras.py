@@ -120,14 +120,29 @@ def config5(torch, n=10_000_000, n_rays=16 << 20):
     rec = {"workload": f"configs[4] at its largest 1-GPU size: {n} clustered AABBs (1000 Gaussian clusters, Zipf populations, 5 % background, seed 5), {n_rays} rays; "
                        f"the {blob} byte BVH exceeds the 126 MB L2",
            "colliders": n, "bvh_bytes": blob, "update_ms": upd, "update_frac": 280.0 * n / (upd * 1e-3) / 1e9 / peak}
+    # dram__bytes of these two launches from the committed ncu capture of THIS build of the trace kernel (tools/capture_traffic.py --config5)
+    captured = {}
+    try:
+        import bench
+
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic_config5.json")))
+        if tr.get("source_hash") == bench.source_hash() and (tr["colliders"], tr["rays"]) == (n, n_rays):
+            captured = tr
+    except (OSError, KeyError, ValueError, ImportError):
+        pass
     for name, rays in (("aimed", aimed), ("random", None)):
         if rays is None:
             rays = synth.random_rays(n_rays, seed=4, extent=2000.0)
         r = _trace(cs, torch, rays, steps=3)
         algo = 60.0 * n_rays + 64.0 * (n - 1)
         r["roofline"] = {"bound": "hbm", "algorithmic_bytes": algo, "achieved": algo / (r["ms_per_step"] * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": algo / (r["ms_per_step"] * 1e-3) / 1e9 / peak,
-                         "note": "60 B/ray + the node set once; the dram__bytes of this kernel on this workload are in profiles/ (ncu)"}
+                         "frac": algo / (r["ms_per_step"] * 1e-3) / 1e9 / peak, "traffic": None,
+                         "note": "60 B/ray + the node set once"}
+        if name in captured:
+            t = captured[name]["dram_bytes_read"] + captured[name]["dram_bytes_write"]
+            r["roofline"].update({"traffic": t, "traffic_gbs": t / (r["ms_per_step"] * 1e-3) / 1e9, "traffic_frac_of_peak": t / (r["ms_per_step"] * 1e-3) / 1e9 / peak,
+                                  "l2_hit_rate_pct": captured[name].get("lts_sector_hit_rate_pct"),
+                                  "traffic_source": f"ncu --set full capture of this build ({captured['source_hash']}), profiles/r2_traffic_config5.json"})
         rec[name] = r
         del rays
     cs.close()

@@ -34,19 +34,50 @@ def num(x: str) -> float:
     return float(x.replace(",", ""))
 
 
+def units_of(rep: str) -> dict:
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], check=True, capture_output=True, text=True).stdout
+    rr = list(csv.reader(io.StringIO(txt)))
+    return dict(zip(rr[0], rr[1]))
+
+
+def config5(args, rows, bench) -> None:
+    """dram bytes of the 10M-collider trace (the 640 MB tree does not fit L2: this one IS HBM traffic) -> profiles/r2_traffic_config5.json"""
+    if len(rows) < 7:
+        raise SystemExit(f"expected 7 captured launches (aimed: 0, random: 6), found {len(rows)}")
+    units = units_of(args.report)
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tscale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}
+    out = {"kernel": "k_trace_lbvh", "workload": "config5", "colliders": 10_000_000, "rays": 16 * 1024 * 1024, "source_hash": bench.source_hash(),
+           "report": os.path.basename(args.report),
+           "source": "ncu --set full --clock-control none -k regex:k_trace_lbvh -s 4 -c 7 python tools/bench_extras.py config5 (launch 0: aimed rays, launch 6: random rays)"}
+    for name, r in (("aimed", rows[0]), ("random", rows[6])):
+        rd = num(r["dram__bytes_read.sum"]) * scale.get(units.get("dram__bytes_read.sum", "byte"), 1.0)
+        wr = num(r["dram__bytes_write.sum"]) * scale.get(units.get("dram__bytes_write.sum", "byte"), 1.0)
+        out[name] = {"dram_bytes_read": int(rd), "dram_bytes_write": int(wr),
+                     "duration_ms": num(r["gpu__time_duration.sum"]) * tscale.get(units.get("gpu__time_duration.sum", "ns"), 1e-6),
+                     "lts_sector_hit_rate_pct": num(r.get("lts__t_sector_hit_rate.pct", "nan"))}
+    path = args.out or os.path.join(ROOT, "profiles", "r2_traffic_config5.json")
+    json.dump(out, open(path, "w"), indent=1)
+    print(json.dumps(out))
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("report")
     ap.add_argument("--workload", default="config3")
     ap.add_argument("--colliders", type=int, default=1_000_000)
     ap.add_argument("--rays", type=int, default=16 * 1024 * 1024)
-    ap.add_argument("--out", default=os.path.join(ROOT, "profiles", "r2_traffic.json"))
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--config5", action="store_true", help="report of `python tools/bench_extras.py config5` captured with -s 4 -c 7: launch 0 = aimed rays, launch 6 = random rays")
     args = ap.parse_args()
     import bench
 
     rows = [r for r in raw_page(args.report) if "k_trace_lbvh" in r.get("Kernel Name", "")]
     if not rows:
         raise SystemExit("no k_trace_lbvh launch in the report")
+    if args.config5:
+        return config5(args, rows, bench)
+    args.out = args.out or os.path.join(ROOT, "profiles", "r2_traffic.json")
     r = rows[-1]
     units = {}
     rd, wr = num(r["dram__bytes_read.sum"]), num(r["dram__bytes_write.sum"])

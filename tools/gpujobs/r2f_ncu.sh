@@ -11,4 +11,8 @@ upd="python tools/run_updates.py"
 $upd > gpurun_out/r2_updates_plain.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'k_propagate|k_refit|k_morton|k_onesweep|k_local_sort|k_build' -s 10 -c 6 -f -o gpurun_out/r2_update $upd > gpurun_out/r2_ncu_update.log 2>&1
 echo "update capture rc=$?"
-ls -la gpurun_out | tail -12
+c5="python tools/bench_extras.py config5"
+$c5 > gpurun_out/r2_config5_plain.log 2>&1 &&
+ncu --set full --clock-control none -k regex:k_trace_lbvh -s 4 -c 7 -f -o gpurun_out/r2_config5_trace $c5 > gpurun_out/r2_ncu_config5.log 2>&1
+echo "config5 capture rc=$?"
+ls -la gpurun_out | tail -14
