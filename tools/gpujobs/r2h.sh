@@ -1,4 +1,5 @@
 #!/bin/bash
+./tools/micro/gather_bench | grep -E "records= *(1048576|2097152)" 
 # e2e host-buffer pipeline: one vs two trace streams x largest chunk (rays), full and compact result formats
 B2COL_E2E_STREAMS=2 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "host_pipeline or compact_hits or few_ray or config3_1m or multi" 2>&1 | tail -3
 for st in 1 2; do for ch in 1048576 2097152 4194304; do

@@ -57,6 +57,22 @@ __global__ void __launch_bounds__(128) k(const uint4* __restrict__ tab, cudaText
                 acc += a ^ h;
             }
         }
+        else if (MODE == 7) {  // 64-byte records (two adjacent sectors of one line): what a 4-wide node would cost
+            const uint4* q = tab + 4 * (size_t)(idx >> 1);
+            uint32_t a, b, c, d, e, f, g, h, a2, b2, c2, d2, e2, f2, g2, h2;
+            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d), "=r"(e), "=r"(f), "=r"(g), "=r"(h) : "l"(q));
+            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(a2), "=r"(b2), "=r"(c2), "=r"(d2), "=r"(e2), "=r"(f2), "=r"(g2), "=r"(h2) : "l"(q + 2));
+            acc += a ^ h ^ a2 ^ h2;
+        }
+        else if (MODE == 8) {  // 128-byte records (a whole line)
+            const uint4* q = tab + 8 * (size_t)(idx >> 2);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint32_t a, b, c, d, e, f, g, h;
+                asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d), "=r"(e), "=r"(f), "=r"(g), "=r"(h) : "l"(q + 2 * j));
+                acc += a ^ h;
+            }
+        }
     }
     if (acc == 0x12345678u) *sink = acc;
 }
@@ -96,6 +112,8 @@ int main()
         run<6>("1 LDG.256 : 2 (2x tex)", tab, tex, recs - 1, sink, p.multiProcessorCount, ghz);
         run<4>("LSU  LDG.128 (16 B)", tab, tex, recs - 1, sink, p.multiProcessorCount, ghz);
         run<5>("TEX  tex1Dfetch (16 B)", tab, tex, recs - 1, sink, p.multiProcessorCount, ghz);
+        run<7>("LSU  2x LDG.256 (64 B record)", tab, tex, recs - 1, sink, p.multiProcessorCount, ghz);
+        run<8>("LSU  4x LDG.256 (128 B line)", tab, tex, recs - 1, sink, p.multiProcessorCount, ghz);
         cudaDestroyTextureObject(tex); cudaFree(tab); cudaFree(sink);
     }
     return 0;
