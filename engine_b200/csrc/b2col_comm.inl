@@ -117,6 +117,15 @@ struct b2col_comm_state {
     void* d_word = nullptr;      // 64 bytes of device scratch: completion word, IPC handle exchange
     cudaEvent_t done = nullptr;  // single-process completion
     bool stage_remote = true;    // B2COL_REMOTE_STAGE=0: plain per-lane stores into the peer window too (A/B timing)
+    // How a rank's hits reach a window in ANOTHER GPU's memory (B2COL_GATHER=fused|bulk; default by rank count):
+    //   fused  the trace kernel stores them straight into the window (warp-staged 36-byte runs).  Nothing follows the traversal,
+    //          but every Raycast is its own small NVLink write: measured fine up to 4 ranks (97.7 % of the no-gather rate) and
+    //          at 46 % with 8, where seven peers' small writes saturate the destination's inbound path at ~215 GB/s.
+    //   bulk   the slice is traced in chunks into LOCAL memory (alternating between two streams, so that one chunk's tail overlaps
+    //          the next one's head) and every finished chunk is shipped into the window by the copy engine — large NVLink
+    //          transfers that overlap the following chunks' traversal; only the last chunk's copy is exposed.
+    int gather_bulk = -1;        // -1: bulk when n_ranks > 4
+    size_t gather_chunk = (size_t)2 << 20;  // rays per chunk of the bulk gather (B2COL_GATHER_CHUNK)
     uint64_t gathers = 0, replications = 0;
 };
 
@@ -155,7 +164,12 @@ b2col_status comm_attach(b2col_ctx* ctx, b2_ncclComm_t comm, int n_ranks, int ra
     CU(cudaMalloc(&c->d_word, 64));
     CU(cudaMemsetAsync(c->d_word, 0, 64, ctx->stream));
     CU(cudaEventCreateWithFlags(&c->done, cudaEventDisableTiming));
-    if (const char* e = getenv("B2COL_GATHER")) c->win_fallback = !strcmp(e, "nccl");  // A/B: force the send / recv gather
+    if (const char* e = getenv("B2COL_GATHER")) {
+        c->win_fallback = !strcmp(e, "nccl");  // A/B: force the send / recv gather
+        if (!strcmp(e, "bulk")) c->gather_bulk = 1;
+        if (!strcmp(e, "fused")) c->gather_bulk = 0;
+    }
+    if (const char* e = getenv("B2COL_GATHER_CHUNK")) c->gather_chunk = std::max<size_t>(65536, (size_t)atoll(e));
     if (const char* e = getenv("B2COL_REMOTE_STAGE")) c->stage_remote = atoi(e) != 0;
     return B2COL_OK;
 }
@@ -257,6 +271,45 @@ b2col_status comm_enqueue_shard(b2col_ctx* ctx, const b2col_ray* d_rays_shard, s
     if (c->win_fallback && c->rank != dst) {
         GUARD(ensure(ctx, ctx->d_hits, (hi - lo) * sizeof(b2col_raycast)));
         return enqueue_trace(ctx, d_rays_shard, hi - lo, ctx->d_hits.as<b2col_raycast>(), B2COL_MODE_LBVH);
+    }
+    const bool bulk = c->gather_bulk >= 0 ? c->gather_bulk != 0 : c->n_ranks > 4;
+    if (c->rank != dst && bulk && ctx->have_tree && ctx->tree_leaves > 0) {
+        const size_t n = hi - lo;
+        // at most gather_chunk rays per chunk, at least four chunks per slice (the last chunk's copy is what stays exposed), never tiny ones
+        const size_t chunk = std::min(c->gather_chunk, std::max<size_t>((size_t)256 << 10, (n / 4 + 65535) & ~(size_t)65535));
+        const size_t n_chunks = (n + chunk - 1) / chunk;
+        GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
+        if (!ctx->stream_in) {
+            CU(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
+            CU(cudaStreamCreateWithFlags(&ctx->stream_out, cudaStreamNonBlocking));
+        }
+        if (!ctx->stream_trace2) {
+            CU(cudaStreamCreateWithFlags(&ctx->stream_trace2, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&ctx->pipe_start_ev, cudaEventDisableTiming));
+        }
+        while (ctx->pipe_events.size() < n_chunks + 1) {
+            cudaEvent_t ev;
+            CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            ctx->pipe_events.push_back(ev);
+        }
+        GUARD(ensure(ctx, ctx->d_pipe_counters, n_chunks * 16));
+        CU(cudaMemsetAsync(ctx->d_pipe_counters.p, 0, n_chunks * 16, ctx->stream));
+        CU(cudaEventRecord(ctx->pipe_start_ev, ctx->stream));  // behind the tree (replicate / update), the rays' producer and the memset
+        CU(cudaStreamWaitEvent(ctx->stream_trace2, ctx->pipe_start_ev, 0));
+        CU(cudaStreamWaitEvent(ctx->stream_out, ctx->pipe_start_ev, 0));  // also: behind the previous gather's completion step
+        b2col_raycast* local = ctx->d_hits.as<b2col_raycast>();
+        b2col_raycast* remote = static_cast<b2col_raycast*>(c->win) + lo;
+        for (size_t k = 0; k < n_chunks; ++k) {
+            const size_t off = k * chunk, m = std::min(chunk, n - off);
+            cudaStream_t ts = (k & 1) ? ctx->stream_trace2 : ctx->stream;
+            GUARD(enqueue_trace(ctx, d_rays_shard + off, m, local + off, B2COL_MODE_LBVH, false, false, ts, ctx->d_pipe_counters.as<unsigned long long>() + 2 * k));
+            CU(cudaEventRecord(ctx->pipe_events[k], ts));
+            CU(cudaStreamWaitEvent(ctx->stream_out, ctx->pipe_events[k], 0));
+            CU(cudaMemcpyAsync(remote + off, local + off, m * sizeof(b2col_raycast), cudaMemcpyDefault, ctx->stream_out));  // copy engine, over NVLink
+        }
+        CU(cudaEventRecord(ctx->pipe_events[n_chunks], ctx->stream_out));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->pipe_events[n_chunks], 0));  // the completion step (callers) follows the last copy
+        return B2COL_OK;
     }
     // the window is another GPU's memory on every rank but dst: there the kernel writes whole staged Raycasts (see flush_finished)
     return enqueue_trace(ctx, d_rays_shard, hi - lo, static_cast<b2col_raycast*>(c->win) + lo, B2COL_MODE_LBVH, c->rank != dst && c->stage_remote);
