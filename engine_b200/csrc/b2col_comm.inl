@@ -116,7 +116,7 @@ struct b2col_comm_state {
     bool win_fallback = false;   // the window could not be mapped somewhere: every rank sends its slice with NCCL instead
     void* d_word = nullptr;      // 64 bytes of device scratch: completion word, IPC handle exchange
     cudaEvent_t done = nullptr;  // single-process completion
-    bool stage_remote = true;    // B2COL_REMOTE_STAGE=0: plain per-lane stores into the peer window too (A/B timing)
+    bool stage_remote = true;    // fused mode: warp-staged 36-byte runs (default from 3 ranks on) or plain per-lane stores (B2COL_REMOTE_STAGE=0|1)
     // How a rank's hits reach a window in ANOTHER GPU's memory (B2COL_GATHER=fused|bulk; default by rank count):
     //   fused  the trace kernel stores them straight into the window (warp-staged 36-byte runs).  Nothing follows the traversal,
     //          but every Raycast is its own small NVLink write: measured fine up to 4 ranks (97.7 % of the no-gather rate) and
@@ -170,6 +170,7 @@ b2col_status comm_attach(b2col_ctx* ctx, b2_ncclComm_t comm, int n_ranks, int ra
         if (!strcmp(e, "fused")) c->gather_bulk = 0;
     }
     if (const char* e = getenv("B2COL_GATHER_CHUNK")) c->gather_chunk = std::max<size_t>(65536, (size_t)atoll(e));
+    c->stage_remote = n_ranks > 2;  // one peer's per-lane stores beat the staged form (3665 vs 3605 Mrays/s on 2 GPUs); from three peers on staging wins
     if (const char* e = getenv("B2COL_REMOTE_STAGE")) c->stage_remote = atoi(e) != 0;
     return B2COL_OK;
 }
