@@ -952,12 +952,12 @@ struct b2col_ctx {
     DevBuf d_small_counters;   // SMALL_SLOTS x u64, all zero beyond small_next
     size_t small_next = SMALL_SLOTS;
     cudaStream_t stream_in = nullptr, stream_out = nullptr;  // copy streams of the chunked host-buffer pipeline
-    // second trace stream of the pipeline (B2COL_E2E_STREAMS=2): chunks alternate between ctx->stream and this one, so that the
+    // second trace stream of the pipeline (B2COL_E2E_STREAMS=1 turns it off): chunks alternate between ctx->stream and this one, so that the
     // tail of one chunk's persistent kernel (its last rays, most SMs idle) overlaps the head of the next chunk's
     cudaStream_t stream_trace2 = nullptr;
     cudaEvent_t pipe_start_ev = nullptr;
     DevBuf d_pipe_counters;  // one pre-zeroed work counter per chunk (the kernels of two streams must not share one)
-    int e2e_streams = 1;
+    int e2e_streams = 2;  // measured (profiles/r2_experiments.txt): compact results 1428 -> 1559 Mrays/s, 36-byte results unchanged (download-bound)
     std::vector<cudaEvent_t> pipe_events;
     // device->host leg of the pipeline: 0 = copy engine (default), 1 = SM stores (k_copy_out), -1 = measure both and keep the
     // faster (big calls only); B2COL_D2H_MODE=ce|sm|auto.  Measured (profiles/r1_e_d2h_modes.txt): alone on the host the copy
