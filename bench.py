@@ -253,17 +253,18 @@ def measure_rebuild(cs, scene, args, torch):
                 evs[f][2].record(ext)
             cs.sync()
             times[mode] = np.array([[e[1].elapsed_time(e[2]), e[0].elapsed_time(e[2])] for e in evs[5:]])  # [update alone, whole frame]
+    st_timed = cs.stats()  # key width / radix passes of the builds that were timed (the policy adapts them to the scene after the first build)
     cs.set_scene(scene)
     cs.on_update()  # leave the tree of the unperturbed scene for the traversal
     ms = float(np.median(times["rebuild"][:, 0]))
     return {"ms": ms, "p99_ms": float(np.percentile(times["rebuild"][:, 0], 99)), "frames": frames,
             "frame_ms": float(np.median(times["rebuild"][:, 1])), "frame_p99_ms": float(np.percentile(times["rebuild"][:, 1], 99)),
-            "static_ms": static_ms, "colliders": N,
+            "static_ms": static_ms, "colliders": N, "key_bits": st_timed["key_bits"], "sort_passes": st_timed["sort_passes"],
             "launches_per_update": launches_per_update, "algorithmic_bytes": algo, "achieved_gbs": algo / (ms * 1e-3) / 1e9, "frac": algo / (ms * 1e-3) / 1e9 / peak,
             "static_frac": algo / (static_ms * 1e-3) / 1e9 / peak, "refit_only_ms": float(np.median(times["refit_only"][:, 0])),
             "refit_only_frame_ms": float(np.median(times["refit_only"][:, 1])),
             "what": f"every collider moves every frame: a device op perturbs all positions and the TRS arrays are handed over (b2col_set_trs_device, 44 B/entity device to "
-                    f"device); ms = b2col_update alone on that moving scene (fused propagate+refit, Morton, sort [{cs.stats()['sort_passes']} digits], hierarchy/bounds as one "
+                    f"device); ms = b2col_update alone on that moving scene (fused propagate+refit, Morton [{st_timed['key_bits']}-bit keys, chosen by the key-width policy from the collisions the previous build counted], sort [{st_timed['sort_passes']} digits], hierarchy/bounds as one "
                     f"CUDA-graph replay), frame_ms = animation + hand-over + update; medians of {frames} frames, each bracketed by CUDA events on the context's stream; "
                     "static_ms = the same TRS replayed back to back without events in between (round-1 definition)"}
 

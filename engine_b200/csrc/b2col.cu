@@ -148,7 +148,8 @@ struct BlobHeader {
     uint32_t trace_root;         // where k_trace_lbvh starts: `root`, or the compact copy of the root (k_top_layout)
     uint32_t top_count;          // nodes in the compact copy of the top levels behind the leaf records (0: none)
     uint32_t has_wild;           // 1: some leaf box cannot be bounded on the grid (NaN / inf / > 1e37: WILD_BIT slots in the tree)
-    uint32_t reserved[36];
+    uint32_t key_bits;           // Morton key width of the build (k_morton)
+    uint32_t reserved[35];
 };
 static_assert(sizeof(BlobHeader) == 256, "blob header");
 constexpr uint32_t BLOB_MAGIC = 0xB2C0117Eu;
@@ -179,8 +180,10 @@ constexpr int BOUNDS_WORDS = 12;
 constexpr uint32_t NO_COLLIDER = 0xFFFFFFFFu;
 
 // world matrix of entity e (reference src/system_transform.cpp:22-36): local T*R*S, times the parent's world matrix
+// root_level: every entity of hierarchy level 0 has parent 0 (b2col_set_hierarchy), so the parent load — and with it the only
+// data-dependent branch of the level — is skipped there.
 __device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restrict__ parent, const float* __restrict__ pos3, const float4* __restrict__ rot4,
-                                             const float* __restrict__ scl3, const float4* world, float* W)
+                                             const float* __restrict__ scl3, const float4* world, float* W, bool root_level = false)
 {
     const float4 q4 = __ldg(rot4 + e);
     const float p[3] = {__ldg(pos3 + 3 * (size_t)e), __ldg(pos3 + 3 * (size_t)e + 1), __ldg(pos3 + 3 * (size_t)e + 2)};
@@ -188,7 +191,7 @@ __device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restr
     const float q[4] = {q4.x, q4.y, q4.z, q4.w};
     float L[16];
     local_matrix(p, q, s, L);
-    const uint32_t par = __ldg(parent + e);
+    const uint32_t par = root_level ? 0u : __ldg(parent + e);
     if (par != 0u) {
         float P[16];
         const float4* pw = world + 4 * (size_t)par;  // written by the previous launch
@@ -210,12 +213,21 @@ __device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restr
 // The result is stored as a 32-byte record {lo, hi, entity, collider index} — the layout of a LeafRec, one sector —
 // so that the build's gather by primitive index costs ONE sector per leaf (a 24-byte AABB at 24-byte stride
 // straddles two sectors half of the time, and the entity ID was a third).
-__device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const float* M, const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec,
-                                          float* cmin, float* cmax)
+struct LocalBox {
+    float2 a, b, c;  // the 24 bytes of a collider's local AABB (min.xyz, max.xyz) as three 8-byte loads
+};
+__device__ __forceinline__ LocalBox load_local_box(const Aabb24* __restrict__ col_local, uint32_t c)
 {
     const float2* lp = reinterpret_cast<const float2*>(col_local + c);
-    const float2 l0 = __ldg(lp), l1 = __ldg(lp + 1), l2 = __ldg(lp + 2);
-    const float lmin[3] = {l0.x, l0.y, l1.x}, lmax[3] = {l1.y, l2.x, l2.y};
+    LocalBox l;
+    l.a = __ldg(lp);
+    l.b = __ldg(lp + 1);
+    l.c = __ldg(lp + 2);
+    return l;
+}
+__device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const float* M, const LocalBox& l, LeafRec* __restrict__ world_rec, float* cmin, float* cmax)
+{
+    const float lmin[3] = {l.a.x, l.a.y, l.b.x}, lmax[3] = {l.b.y, l.c.x, l.c.y};
     const Box b = transform_box(lmin, lmax, M);
     float4* op = reinterpret_cast<float4*>(world_rec + c);
     op[0] = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
@@ -300,27 +312,38 @@ k_propagate_level(const uint32_t* __restrict__ level_entities, uint32_t count, c
 
 // The same level, FUSED with the refit of the colliders that sit on this level's entities (b2col_update's normal
 // path): the world matrix is still in registers when transformBox needs it, so the refit's 64-byte re-read per
-// collider and one launch disappear.  col_of_entity[e] = index of e's collider or NO_COLLIDER.
+// collider and one launch disappear.
+// The kernel is bound by memory LATENCY, not bandwidth (ncu, profiles/r2_ncu_update_counters.txt: 3.0 TB/s at 45 % warps
+// active): what a thread has in flight is one link of a chain of dependent loads.  The chain used to be entity list ->
+// {TRS, parent, entity's collider index} -> {parent matrix, local box}.  level_col[i] = collider index of level_entities[i]
+// (NO_COLLIDER = none) is a second list in LEVEL order, loaded together with the entity ID; and a level whose entities AND
+// colliders are consecutive runs (DENSE: e = e0 + i, c = c0 + i — every flat scene, every scene whose colliders were created
+// in entity order) needs neither list: all of its loads are independent and issued at once.
 #ifndef B2_REFIT_MIN_BLOCKS
 #define B2_REFIT_MIN_BLOCKS 8
 #endif
+template <bool DENSE>
 __global__ void __launch_bounds__(REFIT_BLOCK, B2_REFIT_MIN_BLOCKS)
-k_propagate_refit_level(const uint32_t* __restrict__ level_entities, uint32_t count, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
-                        const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const uint32_t* __restrict__ col_of_entity,
+k_propagate_refit_level(const uint32_t* __restrict__ level_entities, const uint32_t* __restrict__ level_col, uint32_t e0, uint32_t c0, uint32_t count, int root_level,
+                        const uint32_t* __restrict__ parent, const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world,
                         const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds)
 {
     pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
     if (i < count) {
-        const uint32_t e = level_entities[i];
+        const uint32_t e = DENSE ? e0 + i : level_entities[i];
+        const uint32_t c = DENSE ? c0 + i : level_col[i];
+        // the local box is requested together with the TRS (behind the matrix stores it would be a second round trip)
+        LocalBox lb;
+        lb.a = lb.b = lb.c = make_float2(0.0f, 0.0f);
+        if (c != NO_COLLIDER) lb = load_local_box(col_local, c);
         float W[16];
-        entity_world(e, parent, pos3, rot4, scl3, world, W);
+        entity_world(e, parent, pos3, rot4, scl3, world, W, root_level != 0);
         float4* ow = world + 4 * (size_t)e;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) ow[c] = make_float4(W[4 * c], W[4 * c + 1], W[4 * c + 2], W[4 * c + 3]);
-        const uint32_t c = __ldg(col_of_entity + e);
-        if (c != NO_COLLIDER) refit_one(c, e, W, col_local, world_rec, cmin, cmax);
+        for (int k = 0; k < 4; ++k) ow[k] = make_float4(W[4 * k], W[4 * k + 1], W[4 * k + 2], W[4 * k + 3]);
+        if (c != NO_COLLIDER) refit_one(c, e, W, lb, world_rec, cmin, cmax);
     }
     bounds_reduce(cmin, cmax, bounds);
 }
@@ -343,7 +366,7 @@ k_refit(uint32_t n, const uint32_t* __restrict__ col_entity, const Aabb24* __res
             const float4 v = pw[c];
             M[4 * c] = v.x; M[4 * c + 1] = v.y; M[4 * c + 2] = v.z; M[4 * c + 3] = v.w;
         }
-        refit_one(i, e, M, col_local, world_rec, cmin, cmax);
+        refit_one(i, e, M, load_local_box(col_local, i), world_rec, cmin, cmax);
     }
     bounds_reduce(cmin, cmax, bounds);
 }
@@ -373,6 +396,12 @@ k_gather_world(uint32_t n, const uint32_t* __restrict__ ids, const float4* __res
     packed[t] = world[4 * (size_t)ids[t >> 2] + (t & 3)];
 }
 
+// key-width statistic (b2col_update's policy): k_build counts the leaves whose key equals the key KEY_RUN sorted places before
+// them — the members of runs the key does not separate — into KEY_CTR_SLOTS counter pairs, one 32-byte sector each (a block adds
+// to slot blockIdx % KEY_CTR_SLOTS; scenes the keys resolve add nothing at all); the next frame's k_morton sums and clears them
+constexpr int KEY_RUN = 4;
+constexpr uint32_t KEY_CTR_SLOTS = 64;
+
 // Header fields every build needs besides the bounds: leaf / node counts and the quantisation grid of the
 // traversal nodes, derived from the box bounds k_refit reduced into the header.  One thread.
 __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t n, float T)
@@ -401,7 +430,8 @@ __device__ void finish_header(BlobHeader* hdr, const uint32_t* bounds, uint32_t 
 constexpr int MORTON_BLOCK = B2_MORTON_BLOCK;
 __global__ void __launch_bounds__(MORTON_BLOCK)
 k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, const uint32_t* __restrict__ bounds, int key_bits, int passes, int hist_lo, int packed, float T,
-         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* ghist)  // histograms of the radix passes hist_lo .. passes-1 (the MSD pipeline needs the top digit's only)
+         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* ghist,  // histograms of the radix passes hist_lo .. passes-1 (the MSD pipeline needs the top digit's only)
+         uint32_t* key_ctr, uint4* host_stat)
 {
     pdl_wait();
     __shared__ uint32_t shist[RS_MAX_PASSES][RS_RADIX];
@@ -460,7 +490,19 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
             if (c) atomicAdd(&ghist[p * RS_RADIX + b], c);
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) finish_header(hdr, bounds, n, T);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // key-width statistic of the PREVIOUS full build (k_build's counters; hdr still describes that build): one 16-byte store into
+        // page-locked host memory, read by the host's policy before a later build (b2col_update); the counters start this frame at zero
+        uint32_t dc = 0u, dn = 0u;
+        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) {
+            dc += __ldcg(key_ctr + 8u * sl);
+            dn += __ldcg(key_ctr + 8u * sl + 1u);
+        }
+        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) *reinterpret_cast<uint2*>(key_ctr + 8u * sl) = make_uint2(0u, 0u);
+        if (host_stat && hdr->magic == BLOB_MAGIC) *host_stat = make_uint4(dc, dn, hdr->n_leaves, hdr->key_bits);
+        finish_header(hdr, bounds, n, T);
+        hdr->key_bits = (uint32_t)key_bits;
+    }
 }
 
 // b2col_comm_replicate_records: the scene bounds a replica needs for its Morton / quantisation grids arrive inside the
@@ -479,10 +521,11 @@ __global__ void k_bounds_from_header(const BlobHeader* hdr, uint32_t* bounds)
 
 // Refit-only frames (b2col_refit) skip k_morton: this fills the header fields k_morton would have written,
 // from the bounds k_refit has just reduced.
-__global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T)
+__global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, float T, uint32_t* key_ctr)
 {
     pdl_wait();
-    finish_header(hdr, bounds, n, T);
+    if (threadIdx.x < KEY_CTR_SLOTS) *reinterpret_cast<uint2*>(key_ctr + 8u * threadIdx.x) = make_uint2(0u, 0u);  // the re-bounding pass counts the same keys again
+    if (threadIdx.x == 0) finish_header(hdr, bounds, n, T);
 }
 
 // LBVH hierarchy + bounds, production form: traversal structure only, merged in grid space — the per-thread
@@ -504,7 +547,8 @@ __global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, fl
 #endif
 constexpr int BUILD_BLOCK = B2_BUILD_BLOCK;  // update at 1M: 64 -> 170.4 us, 96 -> 168.4, 128 -> 167.8, 256 -> 170.1, 512 -> 178.9, 1024 -> 204.0
 __global__ void __launch_bounds__(BUILD_BLOCK)
-k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words)
+k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words,
+        uint32_t* key_ctr)  // KEY_CTR_SLOTS x 8 words, one 32-byte sector per slot: [0] / [1] = leaves in runs of equal keys / of keys equal above their low 8 bits
 {
     pdl_wait();
     // The frame's zero-initialised scratch (scene bounds, digit histograms, tile tickets, look-back words) has been
@@ -526,6 +570,7 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     uint64_t key = 0ull;
     uint32_t lev_l = LEVEL_END;
     bool wild = false;  // this subtree holds a leaf the grid cannot bound (b2col_bvh.cuh, WILD_BIT)
+    bool dup_cur = false, dup_narrow = false;
     if (valid) {
         const LeafRec rec = DevOps::load_leaf(&world_rec[sorted_prim[i]]);  // one 256-bit load: the world record IS the leaf record
         DevOps::store_leaf(&leaves[i], rec);
@@ -533,6 +578,11 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         wild = box_is_wild(rec.lo, rec.hi);
         key = keys[i];
         if (i > 0u) lev_l = split_level(keys[i - 1u], key, i - 1u);
+        if (i >= (uint32_t)KEY_RUN) {  // sorted: equal to the key KEY_RUN places back = inside a run of more than KEY_RUN leaves the key does not separate
+            const uint64_t x = keys[i - (uint32_t)KEY_RUN] ^ key;
+            dup_cur = x == 0ull;
+            dup_narrow = (x >> 8) == 0ull;  // ... and which 8 bits fewer (one radix pass) would not separate
+        }
     }
     if (n == 1u) {  // a lone leaf still gets a node; both slots = the leaf (an empty slot has no grid encoding)
         if (i == 0u) {
@@ -565,7 +615,7 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     }
     if (lane == 31) s_wmax[0][warp] = pm;
     if (lane == 0) s_wmax[1][warp] = sx;
-    __syncthreads();
+    const int n_dup_narrow = __syncthreads_count(dup_narrow);  // the two barriers of this prologue also count the block's key collisions
     {
         const uint32_t right_boundary = s_lev[BUILD_BLOCK];
         uint32_t before = 0u, after = right_boundary;
@@ -582,7 +632,12 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         s_local[tid] = (tid > 0 && left_max > lev_l && right_max > lev_l) ? 1 : 0;
         if (tid == 0) s_local[BUILD_BLOCK] = 0;
     }
-    __syncthreads();
+    const int n_dup_cur = __syncthreads_count(dup_cur);
+    if (tid == 0) {  // rare in scenes the keys resolve; spread over KEY_CTR_SLOTS sectors of their own where they do not
+        uint32_t* slot = key_ctr + 8u * (blockIdx.x & (KEY_CTR_SLOTS - 1u));
+        if (n_dup_cur) atomicAdd(slot, (uint32_t)n_dup_cur);
+        if (n_dup_narrow) atomicAdd(slot + 1, (uint32_t)n_dup_narrow);
+    }
     if (!valid) return;
 
     // ---- climb
@@ -927,14 +982,18 @@ struct b2col_ctx {
     size_t zero_bytes = 0;
     bool scratch_clean = false;          // d_zero[0, zero_bytes) is all zero (left so by the last k_build)
     // fused propagate + refit: collider index of every entity (NO_COLLIDER = none); needs one collider per entity at most
-    std::vector<uint32_t> h_col_entity;
-    DevBuf d_col_of_entity;
+    std::vector<uint32_t> h_col_entity, h_level_entities;
+    DevBuf d_col_of_entity, d_level_col;  // collider index by entity (host-side product only) / by position in d_level_entities
+    struct LevelRun { bool dense = false; uint32_t e0 = 0, c0 = 0; };
+    std::vector<LevelRun> level_runs;     // per hierarchy level: entities and colliders are consecutive runs (k_propagate_refit_level<true>)
+    bool no_dense_refit = false;          // dev: B2COL_NO_DENSE_REFIT=1 keeps the list-driven kernel for every level (A/B timing)
     bool fuse_map_valid = false, fusable = false;
     int sorted_side = 0;
     // traversal structure: one allocation [BlobHeader | QNode x (N-1) | LeafRec x N]
     DevBuf d_blob;
     size_t blob_bytes = 0;
     uint32_t tree_leaves = 0;  // leaves of the tree currently in the blob
+    int tree_key_bits = 0;     // Morton key width that tree was built with (b2col_update; 0: imported / received)
     bool have_tree = false;
     bool topology_valid = false;  // keys / leaf order in d_keys/d_vals[sorted_side] describe the tree in the blob and the current collider set (b2col_refit)
     uint64_t full_builds = 0, refits = 0;
@@ -965,6 +1024,15 @@ struct b2col_ctx {
     // processes sharing the host the SM stores win by 4 % (2130 vs 2044) — not worth a default that depends on the neighbours.
     int d2h_policy = 0;
     int n_sm = 148;
+    int env_key_bits = 0;         // dev: B2COL_KEY_BITS overrides the automatic key width (0 = automatic)
+    // Adaptive key width (b2col_update's policy, prepare_build_inner): the hierarchy pass of every frame reports how many adjacent
+    // sorted leaves its keys failed to separate — at the current width and at a width one radix pass (8 bits) narrower — into this
+    // page-locked, mapped block {dup_cur, dup_narrow, leaves, key_bits}; the NEXT full build narrows or widens its keys accordingly.
+    DevBuf d_key_ctr;             // k_build's counters (KEY_CTR_SLOTS sectors), summed and cleared by the next k_morton
+    uint32_t* h_key_stat = nullptr;
+    void* d_key_stat = nullptr;   // device address of the same block
+    int adapt_key_bits = 0;       // width chosen by the policy (0: none yet, the static width by collider count)
+    bool adaptive_keys = true;    // B2COL_ADAPTIVE_KEYS=0: always the static width
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
     // sort pipeline of a full build: MSD pass + block-local sort (b2col_sort.cuh) where the buckets fit a block, LSD otherwise
     // B2COL_BUILD=climb|direct|warp: k_build (0, default: measured fastest at 1M — 61.5 us vs 71.7 / 73.8, profiles/r2_experiments.txt), k_build_direct (1), k_build_warp (2)
@@ -1233,10 +1301,28 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
         c->e2e_chunk = std::max(c->e2e_chunk, c->e2e_first_chunk);
         if (const char* e = getenv("B2COL_PHASE_EVENTS")) c->phase_timing = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_FUSE")) c->no_fuse = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_NO_DENSE_REFIT")) c->no_dense_refit = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_SMALL")) c->no_small_path = atoi(e) != 0;
         cudaFuncSetAttribute(k_top_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TOP_SMEM);  // 64 KB frontier; a failure surfaces at the launch
         if (const char* e = getenv("B2COL_PDL")) c->pdl = atoi(e) != 0;
         if (const char* e = getenv("B2COL_NO_PACKED_SORT")) c->no_packed_sort = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_KEY_BITS")) c->env_key_bits = std::min(63, std::max(0, atoi(e)));  // dev: total Morton key width (A/B timing)
+        if (const char* e = getenv("B2COL_ADAPTIVE_KEYS")) c->adaptive_keys = atoi(e) != 0;
+        if (cudaMalloc(&c->d_key_ctr.p, KEY_CTR_SLOTS * 32) != cudaSuccess || cudaMemset(c->d_key_ctr.p, 0, KEY_CTR_SLOTS * 32) != cudaSuccess) {
+            cudaGetLastError();
+            b2col_destroy(c);
+            return fail(nullptr, B2COL_ERR_CUDA, "cudaMalloc of the key statistic counters failed");
+        }
+        c->d_key_ctr.cap = KEY_CTR_SLOTS * 32;
+        if (cudaHostAlloc((void**)&c->h_key_stat, 16, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&c->d_key_stat, c->h_key_stat, 0) == cudaSuccess) {
+            memset(c->h_key_stat, 0, 16);
+        }
+        else {
+            cudaGetLastError();
+            if (c->h_key_stat) cudaFreeHost(c->h_key_stat);
+            c->h_key_stat = nullptr;  // no statistic: the static width only
+            c->d_key_stat = nullptr;
+        }
         if (const char* e = getenv("B2COL_MORTON_BLOCKS_PER_SM")) c->morton_blocks_per_sm = std::max(0, atoi(e));
         if (const char* e = getenv("B2COL_BUILD")) c->build_variant = !strcmp(e, "direct") ? 1 : (!strcmp(e, "warp") ? 2 : 0);
         if (const char* e = getenv("B2COL_SORT")) c->sort_policy = !strcmp(e, "auto") ? 0 : (!strcmp(e, "msd") ? 2 : 1);
@@ -1266,7 +1352,7 @@ void b2col_destroy(b2col_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (DevBuf* b : {&ctx->d_parent, &ctx->d_level_entities, &ctx->d_pos, &ctx->d_rot, &ctx->d_scl, &ctx->d_world, &ctx->d_col_entity,
-                      &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
+                      &ctx->d_col_local, &ctx->d_world_aabb, &ctx->d_col_of_entity, &ctx->d_level_col, &ctx->d_key_ctr, &ctx->d_keys[0], &ctx->d_keys[1], &ctx->d_vals[0], &ctx->d_vals[1],
                       &ctx->d_other_bound, &ctx->d_export_cand, &ctx->d_export_out, &ctx->d_export_used, &ctx->d_export_scan, &ctx->d_xch, &ctx->d_zero, &ctx->d_nodes_full, &ctx->d_blob, &ctx->d_ref_nodes, &ctx->d_flag, &ctx->d_rays, &ctx->d_hits, &ctx->d_counter})
         release(*b);
     for (auto& g : ctx->graphs)
@@ -1274,6 +1360,7 @@ void b2col_destroy(b2col_ctx* ctx)
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_import_hdr) cudaFreeHost(ctx->h_import_hdr);
     if (ctx->h_sort_stat) cudaFreeHost(ctx->h_sort_stat);
+    if (ctx->h_key_stat) cudaFreeHost(ctx->h_key_stat);
     if (ctx->h_rows) cudaFreeHost(ctx->h_rows);
     if (ctx->rows_ev) cudaEventDestroy(ctx->rows_ev);
     release(ctx->d_rows);
@@ -1340,6 +1427,7 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
     CU(cudaMemcpyAsync(ctx->d_parent.p, h_parent, rows * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (n_entities) CU(cudaMemcpyAsync(ctx->d_level_entities.p, order.data(), (size_t)n_entities * 4, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));  // `order` is a local
+    ctx->h_level_entities.swap(order);       // kept for prepare_fuse_map (collider index in level order)
     ctx->n_entities = n_entities;
     ctx->have_hierarchy = true;
     ctx->have_trs = false;
@@ -1510,6 +1598,7 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->have_colliders = true;
     ctx->topology_valid = false;  // a new collider set needs a new tree
     if (ctx->h_sort_stat) *ctx->h_sort_stat = 0u;  // ... and gets a fresh try at the MSD sort pipeline
+    ctx->adapt_key_bits = 0;                       // ... and starts from the static key width again
     return B2COL_OK;
 }
 
@@ -1519,7 +1608,7 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
     if (ctx->build_variant == 0)  // B2COL_BUILD=climb: the per-thread climb with shared-memory arrivals (A/B timing; same tree, same bytes)
         LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
-               ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+               ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4), ctx->d_key_ctr.as<uint32_t>());
     else if (ctx->build_variant == 2)
         LAUNCH_FRAME(ctx, k_build_warp, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
@@ -1600,9 +1689,25 @@ b2col_status prepare_fuse_map(b2col_ctx* ctx)
         if (slot != NO_COLLIDER) return B2COL_OK;  // two colliders on one entity: keep the separate refit kernel
         slot = c;
     }
-    GUARD(ensure(ctx, ctx->d_col_of_entity, ((size_t)E + 1) * 4));
-    CU(cudaMemcpyAsync(ctx->d_col_of_entity.p, map.data(), ((size_t)E + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));  // `map` is a local
+    if (ctx->h_level_entities.size() != E) return B2COL_OK;
+    // the same map in LEVEL order (what the kernel reads), and which levels are consecutive runs of entities and colliders
+    std::vector<uint32_t> level_col(E);
+    for (uint32_t i = 0; i < E; ++i) level_col[i] = map[ctx->h_level_entities[i]];
+    const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
+    ctx->level_runs.assign(n_levels, b2col_ctx::LevelRun());
+    for (size_t k = 0; k < n_levels; ++k) {
+        const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
+        if (!cnt) continue;
+        b2col_ctx::LevelRun& run = ctx->level_runs[k];
+        run.e0 = ctx->h_level_entities[off];
+        run.c0 = level_col[off];
+        run.dense = run.c0 != NO_COLLIDER;
+        for (uint32_t i = 0; run.dense && i < cnt; ++i) run.dense = ctx->h_level_entities[off + i] == run.e0 + i && level_col[off + i] == run.c0 + i;
+    }
+    GUARD(ensure(ctx, ctx->d_level_col, (size_t)E * 4 + 4));
+    if (E) CU(cudaMemcpyAsync(ctx->d_level_col.p, level_col.data(), (size_t)E * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));  // `level_col` is a local
+    ++ctx->shape_gen;  // a captured frame holds the per-level kernel choice and run origins
     ctx->fusable = true;
     return B2COL_OK;
 }
@@ -1617,9 +1722,14 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx)
         for (size_t k = 0; k < n_levels; ++k) {
             const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
             if (!cnt) continue;
-            LAUNCH_FRAME(ctx, k_propagate_refit_level, cdiv(cnt, REFIT_BLOCK), REFIT_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
-                   ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_of_entity.as<uint32_t>(),
-                   ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx));
+            const b2col_ctx::LevelRun run = k < ctx->level_runs.size() ? ctx->level_runs[k] : b2col_ctx::LevelRun();
+#define B2_REFIT_LEVEL(D)                                                                                                                                              \
+    LAUNCH_FRAME(ctx, k_propagate_refit_level<D>, cdiv(cnt, REFIT_BLOCK), REFIT_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, ctx->d_level_col.as<uint32_t>() + off, \
+                 run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(),                 \
+                 ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx))
+            if (run.dense && !ctx->no_dense_refit) B2_REFIT_LEVEL(true);
+            else B2_REFIT_LEVEL(false);
+#undef B2_REFIT_LEVEL
         }
         PHASE(ctx);
         return B2COL_OK;
@@ -1645,7 +1755,7 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
     if (n_records) LAUNCH_FRAME(ctx, k_bounds_from_header, 1, 32, 0, (const BlobHeader*)blob_hdr_n(ctx), scratch_bounds(ctx));
     else GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
     if (!full) {
-        LAUNCH_FRAME(ctx, k_header, 1, 1, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T);
+        LAUNCH_FRAME(ctx, k_header, 1, 64, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T, ctx->d_key_ctr.as<uint32_t>());
         GUARD(launch_build(ctx, n, ctx->sorted_side));
         PHASE(ctx);
         return B2COL_OK;
@@ -1661,7 +1771,8 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
         const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
         const uint32_t grid = std::min<uint32_t>(cdiv(n, MORTON_BLOCK), (uint32_t)(ctx->n_sm * per_sm * 256 / MORTON_BLOCK));  // per_sm counts 256-thread blocks
         LAUNCH_FRAME(ctx, k_morton, grid, MORTON_BLOCK, 0, n, ctx->d_world_aabb.as<LeafRec>(), blob_hdr(ctx), scratch_bounds(ctx), 3 * ctx->bits - ctx->drop, ctx->passes,
-               msd ? ctx->passes - 1 : 0, (int)packed, ctx->T, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist);
+               msd ? ctx->passes - 1 : 0, (int)packed, ctx->T, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), ghist, ctx->d_key_ctr.as<uint32_t>(),
+               static_cast<uint4*>(ctx->d_key_stat));
     }
     PHASE(ctx);  // morton
     if (msd) {
@@ -1788,7 +1899,31 @@ static b2col_status prepare_build_inner(b2col_ctx* ctx, uint32_t n)
         ctx->drop = 0;
     }
     else {
-        const int key_bits = n <= (1u << 21) ? 32 : (n <= (1u << 25) ? 40 : 48);
+        const int static_bits = n <= (1u << 21) ? 32 : (n <= (1u << 25) ? 40 : 48);
+        int key_bits = ctx->env_key_bits > 0 ? ctx->env_key_bits : static_bits;
+        // Adaptive width.  One radix pass costs ~15 us at 1M colliders and the last 8 key bits only order leaves that share a cell
+        // of the grid 8 bits coarser: where few do (uniform and city-like scenes: 6 % of the leaves at 1M colliders and 24 bits,
+        // traversal rate unchanged) the pass buys nothing; where many do (clustered scenes: 2M colliders traced at 1540 instead of
+        // 4050 Mrays/s with 24-bit keys, profiles/r2_experiments.txt) every bit counts.  The hierarchy pass counts both kinds of
+        // collision (k_build: leaves inside runs of more than KEY_RUN equal keys; isolated pairs cost nothing — 23 % of the leaves of
+        // a 1M-collider hierarchy scene pair up at 24 bits and it traces exactly as fast as at 32); a full build narrows by one pass
+        // while fewer than 1/32 of the leaves would sit in such runs and widens by one — up to 48 bits — when more than 1/8 do
+        // (2M clustered colliders at 32 bits: 56 % of the leaves; rays aimed at the clusters trace 34 % faster at 40 bits, for 1.5 %
+        // more update time).  The first builds of a collider set use the static width (the statistic arrives one frame late).
+        const bool adaptive = ctx->adaptive_keys && ctx->env_key_bits == 0 && ctx->h_key_stat && ctx->build_variant == 0 && !ctx->comm;
+        if (!adaptive) {
+            ctx->adapt_key_bits = 0;
+        }
+        else {
+            if (ctx->adapt_key_bits == 0) ctx->adapt_key_bits = static_bits;
+            const volatile uint32_t* st = ctx->h_key_stat;
+            const uint32_t dup_cur = st[0], dup_narrow = st[1], leaves = st[2], at_bits = st[3];
+            if (leaves == n && (int)at_bits == ctx->adapt_key_bits) {  // the statistic describes this collider count at the width in use
+                if ((uint64_t)dup_narrow * 32u < n && ctx->adapt_key_bits - 8 >= 16) ctx->adapt_key_bits -= 8;
+                else if ((uint64_t)dup_cur * 8u > n && ctx->adapt_key_bits + 8 <= 48) ctx->adapt_key_bits += 8;
+            }
+            key_bits = ctx->adapt_key_bits;
+        }
         ctx->bits = (key_bits + 2) / 3;
         ctx->drop = 3 * ctx->bits - key_bits;
     }
@@ -1870,6 +2005,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(run_frame(ctx, true));
     ctx->blob_bytes = blob_bytes;
     ctx->tree_leaves = n;
+    ctx->tree_key_bits = 3 * ctx->bits - ctx->drop;
     ctx->have_tree = true;
     ctx->topology_valid = true;
     ++ctx->full_builds;
@@ -2286,6 +2422,7 @@ b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out)
     out->n_colliders = ctx->n_colliders;
     out->n_levels = ctx->level_offsets.empty() ? 0 : (uint32_t)ctx->level_offsets.size() - 1;
     out->sort_passes = (uint32_t)ctx->passes;
+    out->key_bits = (uint32_t)ctx->tree_key_bits;
     out->kernel_launches = ctx->launches;
     out->full_builds = ctx->full_builds;
     out->refits = ctx->refits;

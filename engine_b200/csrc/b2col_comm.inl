@@ -528,6 +528,11 @@ b2col_status b2col_comm_replicate_records(b2col_ctx* ctx, int src_rank, uint32_t
     if (c->rank == src_rank) {
         if (!ctx->have_tree || !ctx->topology_valid || ctx->tree_leaves != n_colliders)
             return fail(ctx, B2COL_ERR_STATE, "source rank needs a tree built by b2col_update for %u colliders", n_colliders);
+        // the receivers rebuild with the static key width (contexts with a communicator never adapt it, prepare_build_inner): a tree
+        // built at another width BEFORE the communicator existed would differ from theirs in leaf order, i.e. in tie winners
+        const int static_bits = n_colliders <= (1u << 21) ? 32 : (n_colliders <= (1u << 25) ? 40 : 48);
+        if (ctx->cfg_bits == 0 && ctx->env_key_bits == 0 && ctx->tree_key_bits != static_bits)
+            return fail(ctx, B2COL_ERR_STATE, "the source's tree was built with %d-bit keys before b2col_comm_init; call b2col_update again", ctx->tree_key_bits);
     }
     else {
         const void* before = ctx->d_blob.p;

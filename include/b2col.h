@@ -116,6 +116,8 @@ typedef struct b2col_stats {
     uint64_t full_builds, refits; /* b2col_update / b2col_refit calls that built or re-bounded a tree */
     uint64_t graph_replays;     /* frames that ran as a replay of a captured CUDA graph (cfg.use_cuda_graph) */
     float scene_min[3], scene_max[3]; /* centroid bounds used for the Morton grid */
+    uint32_t key_bits;          /* Morton key width of the last full build (b2col_update adapts it to the scene: one radix pass per 8 bits) */
+    uint32_t reserved0;
 } b2col_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------ */

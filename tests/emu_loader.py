@@ -55,11 +55,16 @@ class Emu:
         bits = (key_bits + 2) // 3
         return bits, 3 * bits - key_bits
 
-    def build(self, world_aabb, entity, bits=0, order=None, T=1000.0):
+    def build(self, world_aabb, entity, bits=0, order=None, T=1000.0, key_bits=0):
+        """bits: bits per axis (cfg.morton_bits_per_axis); key_bits: total key width, as b2col_update's key-width policy picks it; neither: the static width"""
         world_aabb = np.ascontiguousarray(world_aabb, np.float32).reshape(-1, 6)
         entity = np.ascontiguousarray(entity, np.uint32)
         n = entity.shape[0]
-        bits, drop = (bits, 0) if bits else self.auto_bits(n)
+        if key_bits:
+            bits = (key_bits + 2) // 3
+            drop = 3 * bits - key_bits
+        else:
+            bits, drop = (bits, 0) if bits else self.auto_bits(n)
         nodes = np.zeros(max(n - 1, 1), NODE64)
         qnodes = np.zeros(max(n - 1, 1), QNODE)
         leaves = np.zeros(n, LEAFREC)

@@ -323,6 +323,51 @@ def test_build_on_flat_and_degenerate_worlds(CollisionSystem, emu, port, squash,
     sel = np.arange(0, 3000, 10)
     assert_raycast_equal(got[sel], port.raycast_brute(s.collider_entity[order], boxes[order], rays[sel], nthreads=8), f"flat world {squash}")
     assert_raycast_equal(got, port.raycast_tree(cs.bvh, rays, nthreads=8), f"flat world {squash} vs reference traversal")
+@pytest.mark.gpu
+def test_adaptive_key_width(CollisionSystem, port, emu):
+    """b2col_update's key-width policy: the first build of a collider set uses the static width (32 bits here); the hierarchy pass
+    counts the leaves inside runs of more than four equal keys, at the current width and 8 bits narrower, and a later full build
+    drops one radix pass where fewer than 1/32 of the leaves would sit in such runs (uniform scene: none at 24 bits) and adds one
+    where more than 1/8 do (clustered scene: 28 % at 32 bits).
+    Whatever the width: the tree is the host restatement's tree for that width, and every ray agrees with the live reference
+    walking the exported tree."""
+    s = synth.uniform_boxes(200_000)
+    rays = np.concatenate([synth.random_rays(60_000, seed=5), synth.axis_rays(4_000, seed=6, extent=1000.0)])
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    cs.on_update()
+    st = cs.stats()
+    assert st["key_bits"] == 32 and st["sort_passes"] == 4
+    wide = cs.get_raycasts(rays)
+    seen = []
+    for frame in range(5):  # the statistic of build k is collected by frame k+1 and read by the host before build k+2
+        cs.on_update()
+        seen.append(cs.stats()["key_bits"])
+    assert seen[0] == 32 and seen[-3:] == [24, 24, 24] and sorted(seen, reverse=True) == seen, f"the uniform scene should narrow to 24-bit keys once and stay there: {seen}"
+    assert cs.stats()["sort_passes"] == 3
+    tree = emu.build(cs.world_aabbs(), s.collider_entity, key_bits=24)
+    assert (cs.leaf_order() == tree["sorted_prim"]).all(), "leaf order at 24 bits"
+    exported = cs.bvh
+    assert (exported.view(np.uint8) == emu.export(tree).view(np.uint8)).all(), "24-bit tree differs from the host restatement"
+    got = cs.get_raycasts(rays)
+    assert_raycast_equal(got, reference_walk(exported, rays, port), "24-bit keys vs the reference's GetRaycast on the exported tree")
+    same = got["hit_entity"] == wide["hit_entity"]
+    assert (got["hit"] == wide["hit"]).all() and (got["distance"] == wide["distance"]).all() and same.mean() > 0.999  # the rest: exact ties, other leaf order
+    cs.on_update_refit()  # refit-only frames keep the narrowed tree
+    assert_raycast_equal(cs.get_raycasts(rays), reference_walk(cs.bvh, rays, port), "refit of the 24-bit tree")
+    # a new collider set starts from the static width again; a clustered one widens
+    c = synth.clustered_boxes(200_000)
+    crays = synth.random_rays(40_000, seed=7, extent=2000.0)
+    cs.set_scene(c)
+    seen = []
+    for frame in range(5):
+        cs.on_update()
+        seen.append(cs.stats()["key_bits"])
+    assert seen[0] == 32 and seen[-3:] == [40, 40, 40] and sorted(seen) == seen, f"the clustered scene (28 % of the leaves in long runs at 32 bits) should widen to 40-bit keys once: {seen}"
+    tree = emu.build(cs.world_aabbs(), c.collider_entity, key_bits=40)
+    assert (cs.leaf_order() == tree["sorted_prim"]).all(), "leaf order at 40 bits"
+    assert_raycast_equal(cs.get_raycasts(crays), reference_walk(cs.bvh, crays, port), "clustered scene")
+    cs.close()
 
 
 def test_duplicate_boxes_and_ties(CollisionSystem, port):

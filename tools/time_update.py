@@ -13,8 +13,7 @@ def main():
         cs = CollisionSystem(use_cuda_graph=os.environ.get('GRAPH', '1') != '0')
         cs.set_scene(scene)
         for _ in range(5):
-            cs.on_update(wait=False)
-        cs.sync()
+            cs.on_update()  # synchronous: the key-width policy reads the statistic of the previous build
         K = 50
         cs.event_record(0)
         for _ in range(K):
@@ -27,7 +26,7 @@ def main():
         for _ in range(K):
             cs.on_update_refit(wait=False)
         cs.event_record(3)
-        print(f"{name:32s} update {upd:8.1f} us   refit-only {cs.event_elapsed_ms(2, 3) / K * 1e3:8.1f} us", flush=True)
+        print(f"{name:32s} [{cs.stats()['key_bits']}-bit keys] update {upd:8.1f} us   refit-only {cs.event_elapsed_ms(2, 3) / K * 1e3:8.1f} us", flush=True)
         cs.close()
 
 

@@ -11,6 +11,7 @@ def main():
     ap.add_argument("--rays", type=int, default=1 << 24)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--sort-rays", type=int, default=0, help="experiment: order the rays by (origin cell Morton code at this many bits per axis, direction octant) first")
+    ap.add_argument("--aimed", action="store_true", help="rays aimed at colliders from ~50 units away (hit fraction > 99 %) instead of the workload's own rays")
     a = ap.parse_args()
     import torch
     from engine_b200 import synth
@@ -25,6 +26,11 @@ def main():
         s = synth.static_city(a.colliders)
         w = int(np.sqrt(a.rays))
         rays = synth.camera_rays(w, w) if a.workload == "config2" else synth.random_rays(a.rays, seed=4, extent=500.0)
+    if a.aimed:
+        rng = np.random.default_rng(58)
+        target = s.pos[1 + rng.integers(0, s.n_colliders, a.rays)] + rng.uniform(-0.1, 0.1, (a.rays, 3)).astype(np.float32)
+        origin = target + rng.standard_normal((a.rays, 3)).astype(np.float32) * 50.0
+        rays = np.concatenate([origin, target - origin], axis=1).astype(np.float32)
     R = rays.shape[0]
     if a.sort_rays:
         b = a.sort_rays
@@ -52,7 +58,7 @@ def main():
     cs.sync()
     ms = cs.event_elapsed_ms(2, 3) / a.steps
     out = d_out.view(R, 36)
-    print(json.dumps({"sort_rays": a.sort_rays, "lib": os.environ.get("B2COL_LIB", "default"), "workload": a.workload, "colliders": s.n_colliders, "rays": R, "ms": ms, "mrays_s": R / ms / 1e3,
+    print(json.dumps({"sort_rays": a.sort_rays, "lib": os.environ.get("B2COL_LIB", "default"), "workload": a.workload + (" aimed" if a.aimed else ""), "key_bits": cs.stats()["key_bits"], "colliders": s.n_colliders, "rays": R, "ms": ms, "mrays_s": R / ms / 1e3,
                       "hit_fraction": float((out[:, 32] != 0).float().mean().item()), "checksum": int(out[:, 24:28].contiguous().view(torch.int32).to(torch.int64).sum().item())}))
 
 if __name__ == "__main__":
