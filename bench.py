@@ -221,10 +221,8 @@ def measure_rebuild(cs, scene, args, torch):
     peak, _ = measured_peak_gbs()
     algo = 280.0 * N  # refit 140 B + build 140 B per collider
     cs.set_scene(scene)
-    cs.on_update()
-    for _ in range(max(args.warmup, 3)):
-        cs.on_update(wait=False)
-    cs.sync()
+    for _ in range(max(args.warmup, 3) + 2):
+        cs.on_update()  # synchronous: the key-width and Morton-plan policies read what the previous builds reported and settle within four frames
     K = max(args.steps, 10)
     l0 = cs.stats()["kernel_launches"]
     cs.event_record(0)

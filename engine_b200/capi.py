@@ -37,7 +37,7 @@ class Stats(C.Structure):
         ("n_entities", C.c_uint32), ("n_colliders", C.c_uint32), ("n_levels", C.c_uint32), ("n_internal_nodes", C.c_uint32),
         ("root", C.c_uint32), ("sort_passes", C.c_uint32), ("kernel_launches", C.c_uint64), ("bvh_bytes", C.c_uint64),
         ("full_builds", C.c_uint64), ("refits", C.c_uint64), ("graph_replays", C.c_uint64),
-        ("scene_min", C.c_float * 3), ("scene_max", C.c_float * 3), ("key_bits", C.c_uint32), ("reserved0", C.c_uint32),
+        ("scene_min", C.c_float * 3), ("scene_max", C.c_float * 3), ("key_bits", C.c_uint32), ("fused_keys", C.c_uint32),
     ]
 
 

@@ -28,6 +28,21 @@ static_assert(sizeof(b2col_ray) == 24 && sizeof(b2col_raycast) == 36 && sizeof(b
 // =================================================================================================
 // device-side policy for the shared kernel bodies in b2col_bvh.cuh
 // =================================================================================================
+// 32 bytes as ONE store (sm_100a STG.E.ENL2.256): a lane that writes a whole 32-byte sector sends one full-sector write down the
+// L1 -> L2 path instead of two half-filled ones (B2_STORE256=0: two 16-byte stores, A/B timing)
+#ifndef B2_STORE256
+#define B2_STORE256 1
+#endif
+__device__ __forceinline__ void store32(void* p, const float4& a, const float4& b)
+{
+#if B2_STORE256
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+#else
+    reinterpret_cast<float4*>(p)[0] = a;
+    reinterpret_cast<float4*>(p)[1] = b;
+#endif
+}
+
 struct DevOps {
     static __device__ __forceinline__ void store_slot(Slot* p, const Slot& s)
     {
@@ -114,9 +129,7 @@ struct DevOps {
     }
     static __device__ __forceinline__ void store_leaf(LeafRec* p, const LeafRec& r)
     {
-        float4* q = reinterpret_cast<float4*>(p);
-        q[0] = make_float4(r.lo[0], r.lo[1], r.lo[2], r.hi[0]);
-        q[1] = make_float4(r.hi[1], r.hi[2], __uint_as_float(r.entity), __uint_as_float(r.prim));
+        store32(p, make_float4(r.lo[0], r.lo[1], r.lo[2], r.hi[0]), make_float4(r.hi[1], r.hi[2], __uint_as_float(r.entity), __uint_as_float(r.prim)));
     }
     static __device__ __forceinline__ QNode load_qnode(const QNode* p)
     {
@@ -182,6 +195,27 @@ constexpr uint32_t NO_COLLIDER = 0xFFFFFFFFu;
 // world matrix of entity e (reference src/system_transform.cpp:22-36): local T*R*S, times the parent's world matrix
 // root_level: every entity of hierarchy level 0 has parent 0 (b2col_set_hierarchy), so the parent load — and with it the only
 // data-dependent branch of the level — is skipped there.
+// the arithmetic half: TRS values and parent ID in hand (the bulk-copy kernel reads them from shared memory)
+__device__ __forceinline__ void entity_world_from(const float* p, const float4& q4, const float* s, uint32_t par, const float4* world, float* W)
+{
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+    float L[16];
+    local_matrix(p, q, s, L);
+    if (par != 0u) {
+        float P[16];
+        const float4* pw = world + 4 * (size_t)par;  // written by the previous launch
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float4 v = __ldcg(pw + c);
+            P[4 * c] = v.x; P[4 * c + 1] = v.y; P[4 * c + 2] = v.z; P[4 * c + 3] = v.w;
+        }
+        mat_mul(P, L, W);
+    }
+    else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) W[k] = L[k];
+    }
+}
 __device__ __forceinline__ void entity_world(uint32_t e, const uint32_t* __restrict__ parent, const float* __restrict__ pos3, const float4* __restrict__ rot4,
                                              const float* __restrict__ scl3, const float4* world, float* W, bool root_level = false)
 {
@@ -225,29 +259,28 @@ __device__ __forceinline__ LocalBox load_local_box(const Aabb24* __restrict__ co
     l.c = __ldg(lp + 2);
     return l;
 }
-__device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const float* M, const LocalBox& l, LeafRec* __restrict__ world_rec, float* cmin, float* cmax)
+__device__ __forceinline__ Box refit_one(uint32_t c, uint32_t entity, const float* M, const LocalBox& l, LeafRec* __restrict__ world_rec, float* cmin, float* cmax)
 {
     const float lmin[3] = {l.a.x, l.a.y, l.b.x}, lmax[3] = {l.b.y, l.c.x, l.c.y};
     const Box b = transform_box(lmin, lmax, M);
-    float4* op = reinterpret_cast<float4*>(world_rec + c);
-    op[0] = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
-    op[1] = make_float4(b.hi[1], b.hi[2], __uint_as_float(entity), __uint_as_float(c));
+    store32(world_rec + c, make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]), make_float4(b.hi[1], b.hi[2], __uint_as_float(entity), __uint_as_float(c)));
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float ctr = B2_MUL(B2_ADD(b.lo[k], b.hi[k]), 0.5f);
         if (grid_coord_ok(ctr)) {  // NaN, +-inf and |x| > 1e37 stay out of the grids (such boxes become wild leaves)
-            cmin[k] = ctr;
-            cmax[k] = ctr;
+            cmin[k] = fminf(cmin[k], ctr);  // running bounds: a thread of the grid-stride kernel folds several colliders
+            cmax[k] = fmaxf(cmax[k], ctr);
         }
         if (grid_coord_ok(b.lo[k])) {
-            cmin[3 + k] = b.lo[k];
-            cmax[3 + k] = b.lo[k];
+            cmin[3 + k] = fminf(cmin[3 + k], b.lo[k]);
+            cmax[3 + k] = fmaxf(cmax[3 + k], b.lo[k]);
         }
         if (grid_coord_ok(b.hi[k])) {
             cmin[3 + k] = fminf(cmin[3 + k], b.hi[k]);
             cmax[3 + k] = fmaxf(cmax[3 + k], b.hi[k]);
         }
     }
+    return b;
 }
 
 #ifndef B2_REFIT_BLOCK
@@ -257,6 +290,7 @@ __device__ __forceinline__ void refit_one(uint32_t c, uint32_t entity, const flo
 // promised to the compiler), 160 -> 166 / 1514, 192 -> 167 / 1526, 256 -> 168 / 1534, 512 -> 182
 constexpr int REFIT_BLOCK = B2_REFIT_BLOCK;
 // block reduction of the per-thread bounds: warp shuffles, then one atomic per block and word
+template <int BLOCK = REFIT_BLOCK>
 __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t* bounds)
 {
 #pragma unroll
@@ -267,7 +301,7 @@ __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t
             cmax[k] = fmaxf(cmax[k], __shfl_xor_sync(0xffffffffu, cmax[k], o));
         }
     }
-    __shared__ float smin[REFIT_BLOCK / 32][6], smax[REFIT_BLOCK / 32][6];
+    __shared__ float smin[BLOCK / 32][6], smax[BLOCK / 32][6];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) {
 #pragma unroll
@@ -280,7 +314,7 @@ __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t
     if (threadIdx.x < 6) {
         const int k = threadIdx.x;
         float a = smin[0][k], b = smax[0][k];
-        for (int w = 1; w < REFIT_BLOCK / 32; ++w) {
+        for (int w = 1; w < BLOCK / 32; ++w) {
             a = fminf(a, smin[w][k]);
             b = fmaxf(b, smax[w][k]);
         }
@@ -342,7 +376,8 @@ k_propagate_refit_level(const uint32_t* __restrict__ level_entities, const uint3
         entity_world(e, parent, pos3, rot4, scl3, world, W, root_level != 0);
         float4* ow = world + 4 * (size_t)e;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) ow[k] = make_float4(W[4 * k], W[4 * k + 1], W[4 * k + 2], W[4 * k + 3]);
+        for (int k = 0; k < 4; k += 2)
+            store32(ow + k, make_float4(W[4 * k], W[4 * k + 1], W[4 * k + 2], W[4 * k + 3]), make_float4(W[4 * k + 4], W[4 * k + 5], W[4 * k + 6], W[4 * k + 7]));
         if (c != NO_COLLIDER) refit_one(c, e, W, lb, world_rec, cmin, cmax);
     }
     bounds_reduce(cmin, cmax, bounds);
@@ -447,6 +482,22 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
         }
         s_plan = make_morton_plan(cmin, cmax, key_bits);
     }
+    if (blockIdx.x == 0 && threadIdx.x == 32) {
+        // (beside thread 0's plan arithmetic) key-width statistic of the PREVIOUS full build — k_build's counters; hdr still describes that
+        // build until the end of this kernel — and this frame's centroid bounds: 16-byte stores into page-locked host memory, read by the
+        // host's policies before a later build (b2col_update); the counters start this frame at zero
+        uint32_t dc = 0u, dn = 0u;
+        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) {
+            dc += __ldcg(key_ctr + 8u * sl);
+            dn += __ldcg(key_ctr + 8u * sl + 1u);
+        }
+        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) *reinterpret_cast<uint2*>(key_ctr + 8u * sl) = make_uint2(0u, 0u);
+        if (host_stat) {
+            if (hdr->magic == BLOB_MAGIC) host_stat[0] = make_uint4(dc, dn, hdr->n_leaves, hdr->key_bits);
+            host_stat[1] = make_uint4(~bounds[0], ~bounds[1], ~bounds[2], n);
+            host_stat[2] = make_uint4(bounds[3], bounds[4], bounds[5], n);
+        }
+    }
     __syncthreads();
     const MortonPlan plan = s_plan;
     // A modest grid (4 blocks per SM: every block ends with up to 1024 atomics on the same 1024 global counters, and 8 blocks
@@ -491,17 +542,292 @@ k_morton(uint32_t n, const LeafRec* __restrict__ world_rec, BlobHeader* hdr, con
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        // key-width statistic of the PREVIOUS full build (k_build's counters; hdr still describes that build): one 16-byte store into
-        // page-locked host memory, read by the host's policy before a later build (b2col_update); the counters start this frame at zero
-        uint32_t dc = 0u, dn = 0u;
-        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) {
-            dc += __ldcg(key_ctr + 8u * sl);
-            dn += __ldcg(key_ctr + 8u * sl + 1u);
-        }
-        for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) *reinterpret_cast<uint2*>(key_ctr + 8u * sl) = make_uint2(0u, 0u);
-        if (host_stat && hdr->magic == BLOB_MAGIC) *host_stat = make_uint4(dc, dn, hdr->n_leaves, hdr->key_bits);
         finish_header(hdr, bounds, n, T);
         hdr->key_bits = (uint32_t)key_bits;
+    }
+}
+
+// ---- the frame's first kernel(s) when the Morton plan is known BEFORE the refit: propagate + refit + keys + histograms ---------
+// k_morton exists because the exact plan needs the centroid bounds of ALL boxes of the frame; but a plan only steers tree
+// topology (any keys give a valid tree), so a frame may just as well use a plan made from the bounds of an EARLIER frame
+// (b2col_update's plan policy: bounds reported by the previous frames, widened by 1/32, kept while the scene stays inside
+// them and fills at least half of them; centroids outside clamp to the edge cells).  The key is then computed while the world
+// box is still in registers: one kernel and a 32-byte re-read per collider less per frame.
+//
+// Grid-stride form (a few blocks per SM, every thread folds several entities): the twelve-value bounds reduction — 120 of
+// the ~390 instructions a one-entity thread executes — and the histogram flush run once per thread / block, not per entity.
+// The LAST block of the last level's launch to finish (ticket through tail.done) finds the frame's bounds complete and does
+// what thread 0 of k_morton does: statistics of the previous build, header, quantisation grid.
+struct KeyGen {
+    MortonPlan plan;
+    int passes, hist_lo, packed;
+};
+struct FrameTail {
+    BlobHeader* hdr;
+    uint32_t* key_ctr;
+    uint4* host_stat;       // page-locked, mapped: [0] key statistic of the previous build, [1] / [2] centroid bounds of this frame
+    uint32_t* done;         // zero when the frame starts (per-frame scratch)
+    uint32_t n;             // colliders of the frame
+    float T;
+    int key_bits;           // > 0: a full build with keys of this width (hdr->key_bits, report the previous build's statistic)
+    int last_level;         // this launch completes the frame's bounds
+    uint32_t plan_min_inv[3], plan_max[3];  // KEYS: what the header records as the Morton bounds (ordered encoding) — the plan's, not the frame's
+};
+
+__device__ __noinline__ void frame_tail(const FrameTail& t, const uint32_t* bounds_in, bool keys)  // not inlined: its IEEE divisions (make_grid) are the only FFMA-containing code near the refit arithmetic, and tests/test_capi_cpu.py keeps them apart
+{
+    uint32_t b[BOUNDS_WORDS];
+    for (int k = 0; k < BOUNDS_WORDS; ++k) b[k] = __ldcg(bounds_in + k);
+    uint32_t dc = 0u, dn = 0u;
+    for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) {
+        dc += __ldcg(t.key_ctr + 8u * sl);
+        dn += __ldcg(t.key_ctr + 8u * sl + 1u);
+    }
+    for (uint32_t sl = 0; sl < KEY_CTR_SLOTS; ++sl) *reinterpret_cast<uint2*>(t.key_ctr + 8u * sl) = make_uint2(0u, 0u);
+    if (t.host_stat) {
+        if (t.key_bits > 0 && t.hdr->magic == BLOB_MAGIC) t.host_stat[0] = make_uint4(dc, dn, t.hdr->n_leaves, t.hdr->key_bits);
+        t.host_stat[1] = make_uint4(~b[0], ~b[1], ~b[2], t.n);  // ordered(min centroid) / ordered(max centroid) of THIS frame: the plan policy's input
+        t.host_stat[2] = make_uint4(b[3], b[4], b[5], t.n);
+    }
+    if (keys) {
+        for (int k = 0; k < 3; ++k) {
+            b[k] = t.plan_min_inv[k];
+            b[3 + k] = t.plan_max[k];
+        }
+    }
+    else if (t.key_bits == 0 && t.hdr->magic == BLOB_MAGIC) {  // refit-only frame: the keys of the tree are still those of its build
+        for (int k = 0; k < 3; ++k) {
+            b[k] = t.hdr->bounds_min_inv[k];
+            b[3 + k] = t.hdr->bounds_max[k];
+        }
+    }
+    finish_header(t.hdr, b, t.n, t.T);
+    if (t.key_bits > 0) t.hdr->key_bits = (uint32_t)t.key_bits;
+}
+
+#ifndef B2_RK_BLOCK
+#define B2_RK_BLOCK 256
+#endif
+constexpr int RK_BLOCK = B2_RK_BLOCK;
+#ifndef B2_RK_MIN_BLOCKS
+#define B2_RK_MIN_BLOCKS (1024 / B2_RK_BLOCK)
+#endif
+template <bool DENSE, bool KEYS>
+__global__ void __launch_bounds__(RK_BLOCK, B2_RK_MIN_BLOCKS)
+k_refit_keys(const uint32_t* __restrict__ level_entities, const uint32_t* __restrict__ level_col, uint32_t e0, uint32_t c0, uint32_t count, int root_level,
+             const uint32_t* __restrict__ parent, const float* __restrict__ pos3, const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world,
+             const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec, uint32_t* bounds, KeyGen kg, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+             uint32_t* ghist, FrameTail tail)
+{
+    pdl_wait();
+    __shared__ uint32_t shist[KEYS ? RS_MAX_PASSES : 1][RS_RADIX];
+    __shared__ bool s_last;
+    if (KEYS) {
+        for (int p = kg.hist_lo; p < kg.passes; ++p)
+            for (int d = threadIdx.x; d < RS_RADIX; d += RK_BLOCK) shist[p][d] = 0u;
+        __syncthreads();
+    }
+    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
+    const uint32_t stride = gridDim.x * RK_BLOCK;
+    for (uint32_t i = blockIdx.x * RK_BLOCK + threadIdx.x; i < count; i += stride) {
+        const uint32_t e = DENSE ? e0 + i : level_entities[i];
+        const uint32_t c = DENSE ? c0 + i : level_col[i];
+        LocalBox lb;
+        lb.a = lb.b = lb.c = make_float2(0.0f, 0.0f);
+        if (c != NO_COLLIDER) lb = load_local_box(col_local, c);
+        float W[16];
+        entity_world(e, parent, pos3, rot4, scl3, world, W, root_level != 0);
+        float4* ow = world + 4 * (size_t)e;
+#pragma unroll
+        for (int k = 0; k < 4; k += 2)
+            store32(ow + k, make_float4(W[4 * k], W[4 * k + 1], W[4 * k + 2], W[4 * k + 3]), make_float4(W[4 * k + 4], W[4 * k + 5], W[4 * k + 6], W[4 * k + 7]));
+        if (c != NO_COLLIDER) {
+            const Box b = refit_one(c, e, W, lb, world_rec, cmin, cmax);
+            if (KEYS) {
+                const uint64_t key = morton_key(b.lo, b.hi, kg.plan);
+                if (kg.packed) {
+                    keys[c] = (key << 32) | c;
+                }
+                else {
+                    keys[c] = key;
+                    vals[c] = c;
+                }
+                for (int p = kg.hist_lo; p < kg.passes; ++p) atomicAdd(&shist[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+            }
+        }
+    }
+    bounds_reduce<RK_BLOCK>(cmin, cmax, bounds);
+    if (KEYS) {
+        __syncthreads();
+        for (int p = kg.hist_lo; p < kg.passes; ++p)
+            for (int d = threadIdx.x; d < RS_RADIX; d += RK_BLOCK) {
+                const uint32_t cnt = shist[p][d];
+                if (cnt) atomicAdd(&ghist[p * RS_RADIX + d], cnt);
+            }
+    }
+    if (!tail.last_level) return;
+    // the last block to get here sees every block's bounds (atomics, performed at L2, ordered before the ticket by the fence)
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        frame_tail(tail, bounds, KEYS);
+    }
+}
+
+// ---- the same kernel for DENSE levels, inputs moved by the TMA unit -------------------------------------------------------------
+// On a dense level (entities e0 + i, colliders c0 + i) everything a tile of RK_BLOCK entities reads is five contiguous byte
+// ranges: rotations (16 B / entity), positions and scales (12 B), parent IDs (4 B) and local boxes (24 B / collider).  One thread
+// asks the bulk-copy engine (cp.async.bulk global -> shared, completion counted on an mbarrier) for the NEXT tile's ranges while
+// the block computes the current one out of shared memory: two stages, no registers spent on prefetching, no load instructions
+// in the compute warps besides the parent-matrix gather of non-root levels.  A grid-stride kernel whose threads load, compute
+// and store in lock step leaves the memory system idle while it computes; with the ranges in flight a tile ahead it does not
+// (measured at 1M colliders: profiles/r2_experiments.txt).
+// cp.async.bulk wants 16-byte aligned addresses and sizes: a range starts at the 16-byte boundary below its first byte (`lead`
+// bytes early) and is rounded up (<= 30 bytes of neighbouring rows; every array carries allocation slack, see ensure()).
+namespace bulk {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tB2_MBAR_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra B2_MBAR_DONE;\n\tbra B2_MBAR_WAIT;\n\tB2_MBAR_DONE:\n\t}" ::"r"(
+            smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void g2s(void* sdst, const void* gsrc16, uint32_t bytes16, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(sdst)), "l"(gsrc16), "r"(bytes16),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+// the 16-byte aligned range that covers [p, p + bytes): lead = bytes between its start and p
+__device__ __forceinline__ uint32_t lead_of(const void* p) { return (uint32_t)(reinterpret_cast<uintptr_t>(p) & 15u); }
+__device__ __forceinline__ uint32_t span_of(const void* p, uint32_t bytes) { return (lead_of(p) + bytes + 15u) & ~15u; }
+}  // namespace bulk
+
+struct alignas(16) RkStage {
+    unsigned char rot[RK_BLOCK * 16];
+    unsigned char pos[RK_BLOCK * 12 + 32];
+    unsigned char scl[RK_BLOCK * 12 + 32];
+    unsigned char box[RK_BLOCK * 24 + 32];
+    unsigned char par[RK_BLOCK * 4 + 32];
+};
+static_assert(sizeof(RkStage) % 16 == 0 && (RK_BLOCK * 12) % 16 == 0 && (RK_BLOCK * 24) % 16 == 0 && (RK_BLOCK * 4) % 16 == 0, "stage ranges are 16-byte multiples");
+
+template <bool KEYS>
+__global__ void __launch_bounds__(RK_BLOCK, B2_RK_MIN_BLOCKS)
+k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, const uint32_t* __restrict__ parent, const float* __restrict__ pos3,
+                  const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec,
+                  uint32_t* bounds, KeyGen kg, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* ghist, FrameTail tail)
+{
+    __shared__ RkStage stage[2];
+    __shared__ alignas(8) uint64_t full[2];
+    __shared__ uint32_t shist[KEYS ? RS_MAX_PASSES : 1][RS_RADIX];
+    __shared__ bool s_last;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        bulk::mbar_init(&full[0], 1u);
+        bulk::mbar_init(&full[1], 1u);
+        bulk::mbar_init_fence();
+    }
+    if (KEYS) {
+        for (int p = kg.hist_lo; p < kg.passes; ++p)
+            for (int d = tid; d < RS_RADIX; d += RK_BLOCK) shist[p][d] = 0u;
+    }
+    __syncthreads();
+    pdl_wait();  // the arrays below are written by work earlier in the stream
+    const uint32_t n_tiles = (count + RK_BLOCK - 1u) / RK_BLOCK;
+    // ranges of tile t (all threads can name them; thread 0 requests them)
+    auto request = [&](uint32_t t, int st) {
+        const uint32_t i0 = t * RK_BLOCK, valid = min((uint32_t)RK_BLOCK, count - i0);
+        const size_t e = (size_t)e0 + i0, c = (size_t)c0 + i0;
+        const void* g_rot = rot4 + e;
+        const void* g_pos = pos3 + 3 * e;
+        const void* g_scl = scl3 + 3 * e;
+        const void* g_box = col_local + c;
+        const void* g_par = parent + e;
+        const uint32_t b_rot = valid * 16u, b_pos = bulk::span_of(g_pos, valid * 12u), b_scl = bulk::span_of(g_scl, valid * 12u), b_box = bulk::span_of(g_box, valid * 24u),
+                       b_par = root_level ? 0u : bulk::span_of(g_par, valid * 4u);
+        bulk::mbar_arrive_expect_tx(&full[st], b_rot + b_pos + b_scl + b_box + b_par);
+        RkStage& sg = stage[st];
+        bulk::g2s(sg.rot, g_rot, b_rot, &full[st]);
+        bulk::g2s(sg.pos, static_cast<const char*>(g_pos) - bulk::lead_of(g_pos), b_pos, &full[st]);
+        bulk::g2s(sg.scl, static_cast<const char*>(g_scl) - bulk::lead_of(g_scl), b_scl, &full[st]);
+        bulk::g2s(sg.box, static_cast<const char*>(g_box) - bulk::lead_of(g_box), b_box, &full[st]);
+        if (!root_level) bulk::g2s(sg.par, static_cast<const char*>(g_par) - bulk::lead_of(g_par), b_par, &full[st]);
+    };
+    float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
+    uint32_t t = blockIdx.x;
+    if (tid == 0 && t < n_tiles) request(t, 0);
+    for (uint32_t k = 0; t < n_tiles; t += gridDim.x, ++k) {
+        const int st = (int)(k & 1u);
+        if (tid == 0 && t + gridDim.x < n_tiles) request(t + gridDim.x, st ^ 1);  // that stage was last read in iteration k - 1, which ended with a barrier
+        bulk::mbar_wait(&full[st], (k >> 1) & 1u);
+        const uint32_t i0 = t * RK_BLOCK, i = i0 + (uint32_t)tid;
+        if (i < count) {
+            const RkStage& sg = stage[st];
+            const size_t ef = (size_t)e0 + i0, cf = (size_t)c0 + i0;
+            const uint32_t e = e0 + i, c = c0 + i;
+            const float4 q4 = *reinterpret_cast<const float4*>(sg.rot + 16 * tid);
+            const float* sp = reinterpret_cast<const float*>(sg.pos + bulk::lead_of(pos3 + 3 * ef) + 12 * tid);
+            const float* ss = reinterpret_cast<const float*>(sg.scl + bulk::lead_of(scl3 + 3 * ef) + 12 * tid);
+            const float2* sb = reinterpret_cast<const float2*>(sg.box + bulk::lead_of(col_local + cf) + 24 * tid);
+            const float p[3] = {sp[0], sp[1], sp[2]}, sc[3] = {ss[0], ss[1], ss[2]};
+            LocalBox lb;
+            lb.a = sb[0];
+            lb.b = sb[1];
+            lb.c = sb[2];
+            const uint32_t par = root_level ? 0u : *reinterpret_cast<const uint32_t*>(sg.par + bulk::lead_of(parent + ef) + 4 * tid);
+            float W[16];
+            entity_world_from(p, q4, sc, par, world, W);
+            float4* ow = world + 4 * (size_t)e;
+#pragma unroll
+            for (int j = 0; j < 4; j += 2)
+                store32(ow + j, make_float4(W[4 * j], W[4 * j + 1], W[4 * j + 2], W[4 * j + 3]), make_float4(W[4 * j + 4], W[4 * j + 5], W[4 * j + 6], W[4 * j + 7]));
+            const Box b = refit_one(c, e, W, lb, world_rec, cmin, cmax);
+            if (KEYS) {
+                const uint64_t key = morton_key(b.lo, b.hi, kg.plan);
+                if (kg.packed) {
+                    keys[c] = (key << 32) | c;
+                }
+                else {
+                    keys[c] = key;
+                    vals[c] = c;
+                }
+                for (int pp = kg.hist_lo; pp < kg.passes; ++pp) atomicAdd(&shist[pp][(uint32_t)(key >> (8 * pp)) & 255u], 1u);
+            }
+        }
+        __syncthreads();  // the stage is free for the request of iteration k + 1
+    }
+    bounds_reduce<RK_BLOCK>(cmin, cmax, bounds);
+    if (KEYS) {
+        __syncthreads();
+        for (int p = kg.hist_lo; p < kg.passes; ++p)
+            for (int d = tid; d < RS_RADIX; d += RK_BLOCK) {
+                const uint32_t cnt = shist[p][d];
+                if (cnt) atomicAdd(&ghist[p * RS_RADIX + d], cnt);
+            }
+    }
+    if (!tail.last_level) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    __syncthreads();
+    if (s_last && tid == 0) {
+        __threadfence();
+        frame_tail(tail, bounds, KEYS);
     }
 }
 
@@ -994,6 +1320,7 @@ struct b2col_ctx {
     size_t blob_bytes = 0;
     uint32_t tree_leaves = 0;  // leaves of the tree currently in the blob
     int tree_key_bits = 0;     // Morton key width that tree was built with (b2col_update; 0: imported / received)
+    bool tree_fused_keys = false;  // ... with keys from a plan made before the frame (k_refit_keys)
     bool have_tree = false;
     bool topology_valid = false;  // keys / leaf order in d_keys/d_vals[sorted_side] describe the tree in the blob and the current collider set (b2col_refit)
     uint64_t full_builds = 0, refits = 0;
@@ -1029,8 +1356,24 @@ struct b2col_ctx {
     // sorted leaves its keys failed to separate — at the current width and at a width one radix pass (8 bits) narrower — into this
     // page-locked, mapped block {dup_cur, dup_narrow, leaves, key_bits}; the NEXT full build narrows or widens its keys accordingly.
     DevBuf d_key_ctr;             // k_build's counters (KEY_CTR_SLOTS sectors), summed and cleared by the next k_morton
-    uint32_t* h_key_stat = nullptr;
+    uint32_t* h_key_stat = nullptr;  // 48 bytes: [0..3] key statistic, [4..7] / [8..11] ordered centroid bounds of the last frame + its collider count
     void* d_key_stat = nullptr;   // device address of the same block
+    // Morton plan known before the refit (k_refit_keys): made from centroid bounds the device reported for EARLIER frames
+    // (h_key_stat[4..11]), widened by 1/32; kept while the reported bounds stay inside it and fill at least half of it
+    struct PlanState {
+        bool valid = false;
+        float pmin[3] = {0, 0, 0}, pmax[3] = {0, 0, 0};
+        int key_bits = 0;
+        uint32_t n = 0;
+        uint64_t gen = 0;
+        MortonPlan plan{};
+    } plan_state;
+    bool fuse_keys = true;        // B2COL_FUSE_KEYS=0: always the exact plan (k_morton after the refit)
+    bool use_fused_keys = false;  // this frame's choice (part of the graph key)
+    bool refit_bulk = true;       // B2COL_TMA=0: dense levels through k_refit_keys (per-thread loads) instead of k_refit_keys_bulk (A/B timing)
+    bool stride_always = false;   // dev: B2COL_REFIT=stride: the grid-stride kernel for frames without fused keys too (measured slower: 43.2 vs 40.3 us at 1M)
+    int rk_waves = 1;             // dev: B2COL_RK_WAVES: grid of k_refit_keys in resident waves (1 = persistent)
+    bool refit_stride = true;     // B2COL_REFIT=classic: one thread per entity (k_propagate_refit_level) instead of the grid-stride kernel (A/B timing)
     int adapt_key_bits = 0;       // width chosen by the policy (0: none yet, the static width by collider count)
     bool adaptive_keys = true;    // B2COL_ADAPTIVE_KEYS=0: always the static width
     bool no_packed_sort = false;  // B2COL_NO_PACKED_SORT=1: separate key / value arrays for keys of <= 32 bits too (A/B timing)
@@ -1314,8 +1657,15 @@ b2col_status b2col_create(b2col_ctx** out, const b2col_config* cfg)
             return fail(nullptr, B2COL_ERR_CUDA, "cudaMalloc of the key statistic counters failed");
         }
         c->d_key_ctr.cap = KEY_CTR_SLOTS * 32;
-        if (cudaHostAlloc((void**)&c->h_key_stat, 16, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&c->d_key_stat, c->h_key_stat, 0) == cudaSuccess) {
-            memset(c->h_key_stat, 0, 16);
+        if (const char* e = getenv("B2COL_FUSE_KEYS")) c->fuse_keys = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_REFIT")) {
+            c->refit_stride = strcmp(e, "classic") != 0;
+            c->stride_always = strcmp(e, "stride") == 0;
+        }
+        if (const char* e = getenv("B2COL_TMA")) c->refit_bulk = atoi(e) != 0;
+        if (const char* e = getenv("B2COL_RK_WAVES")) c->rk_waves = std::min(64, std::max(1, atoi(e)));
+        if (cudaHostAlloc((void**)&c->h_key_stat, 48, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&c->d_key_stat, c->h_key_stat, 0) == cudaSuccess) {
+            memset(c->h_key_stat, 0, 48);
         }
         else {
             cudaGetLastError();
@@ -1599,6 +1949,11 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n, const uint32_t* h_e
     ctx->topology_valid = false;  // a new collider set needs a new tree
     if (ctx->h_sort_stat) *ctx->h_sort_stat = 0u;  // ... and gets a fresh try at the MSD sort pipeline
     ctx->adapt_key_bits = 0;                       // ... and starts from the static key width again
+    ctx->plan_state.valid = false;                 // ... and from the exact Morton plan
+    if (ctx->h_key_stat) {
+        CU(cudaStreamSynchronize(ctx->stream));    // a frame in flight may still report into the block
+        memset(ctx->h_key_stat, 0, 48);
+    }
     return B2COL_OK;
 }
 
@@ -1713,10 +2068,74 @@ b2col_status prepare_fuse_map(b2col_ctx* ctx)
 }
 
 // a1 + a2: world matrices and world AABBs of the frame (+ scene bounds into the scratch)
-b2col_status enqueue_transform_refit(b2col_ctx* ctx)
+// `tail` (out): true when the refit kernel itself finished the frame's header (k_refit_keys' last block): the caller then
+// launches neither k_morton (full build with fused keys) nor k_header (refit-only frame)
+b2col_status enqueue_transform_refit(b2col_ctx* ctx, bool full, bool* tail_done)
 {
     const uint32_t n = ctx->n_colliders;
     const bool propagate = !ctx->world_external && !ctx->world_fresh;
+    *tail_done = false;
+    if (propagate && ctx->fusable && !ctx->no_fuse && ctx->refit_stride && ((full && ctx->use_fused_keys) || ctx->stride_always)) {
+        // grid-stride kernel: with the frame's keys when the plan is known (full && use_fused_keys), and — fused keys or refit-only frame —
+        // with the header written by its last block
+        const bool keys = full && ctx->use_fused_keys;
+        const bool tail = keys || !full;
+        const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
+        size_t last = n_levels;
+        for (size_t k = 0; k < n_levels; ++k)
+            if (ctx->level_offsets[k + 1] > ctx->level_offsets[k]) last = k;
+        KeyGen kg{};
+        FrameTail ft{};
+        ft.hdr = blob_hdr(ctx);
+        ft.key_ctr = ctx->d_key_ctr.as<uint32_t>();
+        ft.host_stat = static_cast<uint4*>(ctx->d_key_stat);
+        ft.done = scratch_tickets(ctx) + 13;
+        ft.n = n;
+        ft.T = ctx->T;
+        const bool packed = 3 * ctx->bits - ctx->drop <= 32 && !ctx->no_packed_sort;
+        if (keys) {
+            kg.plan = ctx->plan_state.plan;
+            kg.passes = ctx->passes;
+            kg.hist_lo = 0;
+            kg.packed = (int)packed;
+            ft.key_bits = 3 * ctx->bits - ctx->drop;
+            for (int k = 0; k < 3; ++k) {
+                ft.plan_min_inv[k] = ~float_to_ordered(ctx->plan_state.pmin[k]);
+                ft.plan_max[k] = float_to_ordered(ctx->plan_state.pmax[k]);
+            }
+        }
+        for (size_t k = 0; k < n_levels; ++k) {
+            const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
+            if (!cnt) continue;
+            const b2col_ctx::LevelRun run = k < ctx->level_runs.size() ? ctx->level_runs[k] : b2col_ctx::LevelRun();
+            ft.last_level = (tail && k == last) ? 1 : 0;
+            const uint32_t grid = std::min<uint32_t>(cdiv(cnt, RK_BLOCK), (uint32_t)(ctx->n_sm * B2_RK_MIN_BLOCKS * ctx->rk_waves));
+#define B2_REFIT_KEYS(D, K)                                                                                                                                   \
+    LAUNCH_FRAME(ctx, (k_refit_keys<D, K>), grid, RK_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, ctx->d_level_col.as<uint32_t>() + off, run.e0, run.c0, \
+                 cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), \
+                 ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx), kg, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), \
+                 scratch_ghist(ctx), ft)
+            const bool dense = run.dense && !ctx->no_dense_refit;
+            if (dense && ctx->refit_bulk) {  // inputs through the TMA unit, a tile ahead (k_refit_keys_bulk)
+#define B2_REFIT_BULK(K)                                                                                                                                       \
+    LAUNCH_FRAME(ctx, (k_refit_keys_bulk<K>), grid, RK_BLOCK, 0, run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(),       \
+                 ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(),      \
+                 scratch_bounds(ctx), kg, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), scratch_ghist(ctx), ft)
+                if (keys) B2_REFIT_BULK(true);
+                else B2_REFIT_BULK(false);
+#undef B2_REFIT_BULK
+                continue;
+            }
+            if (dense && keys) B2_REFIT_KEYS(true, true);
+            else if (dense) B2_REFIT_KEYS(true, false);
+            else if (keys) B2_REFIT_KEYS(false, true);
+            else B2_REFIT_KEYS(false, false);
+#undef B2_REFIT_KEYS
+        }
+        *tail_done = tail && last < n_levels;
+        PHASE(ctx);
+        return B2COL_OK;
+    }
     if (propagate && ctx->fusable && !ctx->no_fuse) {
         const size_t n_levels = ctx->level_offsets.empty() ? 0 : ctx->level_offsets.size() - 1;
         for (size_t k = 0; k < n_levels; ++k) {
@@ -1752,10 +2171,11 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
     // n_records != 0: the world records (and the scene bounds, in the blob header) were received from another rank
     // (b2col_comm_replicate_records): Morton + sort + hierarchy only
     const uint32_t n = n_records ? n_records : ctx->n_colliders;
+    bool tail_done = false;  // the refit kernel's last block has written the header (and, in a full build, keys + histograms)
     if (n_records) LAUNCH_FRAME(ctx, k_bounds_from_header, 1, 32, 0, (const BlobHeader*)blob_hdr_n(ctx), scratch_bounds(ctx));
-    else GUARD(enqueue_transform_refit(ctx));  // one phase when fused, two otherwise
+    else GUARD(enqueue_transform_refit(ctx, full, &tail_done));  // one phase when fused, two otherwise
     if (!full) {
-        LAUNCH_FRAME(ctx, k_header, 1, 64, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T, ctx->d_key_ctr.as<uint32_t>());
+        if (!tail_done) LAUNCH_FRAME(ctx, k_header, 1, 64, 0, n, blob_hdr(ctx), scratch_bounds(ctx), ctx->T, ctx->d_key_ctr.as<uint32_t>());
         GUARD(launch_build(ctx, n, ctx->sorted_side));
         PHASE(ctx);
         return B2COL_OK;
@@ -1765,7 +2185,7 @@ b2col_status enqueue_frame(b2col_ctx* ctx, bool full, uint32_t n_records = 0)
     uint32_t* ghist = scratch_ghist(ctx);
     const bool packed = 3 * ctx->bits - ctx->drop <= 32 && !ctx->no_packed_sort;  // key << 32 | index in one word through the sort
     const bool msd = ctx->sort_msd;  // chosen by b2col_update
-    {
+    if (!tail_done) {
         // 4 blocks per SM up to 2M colliders (fewer end-of-block atomics on the shared counters: -4 us at 1M), 8 beyond (the
         // stream dominates: 125 -> 119 us at 10M)
         const int per_sm = ctx->morton_blocks_per_sm > 0 ? ctx->morton_blocks_per_sm : (n <= (1u << 21) ? 4 : 8);
@@ -1839,7 +2259,8 @@ b2col_status run_frame(b2col_ctx* ctx, bool full)
     const bool propagate = !ctx->world_external && !ctx->world_fresh;
     const uint64_t key[4] = {ctx->buffers_gen, ctx->shape_gen,
                              (uint64_t)propagate | ((uint64_t)(ctx->fusable && !ctx->no_fuse) << 1) | ((uint64_t)ctx->passes << 8) | ((uint64_t)ctx->bits << 16) |
-                                 ((uint64_t)ctx->drop << 24) | ((uint64_t)ctx->sorted_side << 32) | ((uint64_t)ctx->sort_msd << 33),
+                                 ((uint64_t)ctx->drop << 24) | ((uint64_t)ctx->sorted_side << 32) | ((uint64_t)ctx->sort_msd << 33) |
+                                 ((uint64_t)(full && ctx->use_fused_keys) << 34) | ((full && ctx->use_fused_keys ? ctx->plan_state.gen & 0xFFFFFFull : 0ull) << 35),
                              ((uint64_t)ctx->n_colliders << 32) | ctx->n_entities};
     if (g.exec && memcmp(g.key, key, sizeof key) == 0) {
         CU(cudaGraphLaunch(g.exec, ctx->stream));
@@ -1876,6 +2297,51 @@ b2col_status run_frame(b2col_ctx* ctx, bool full)
 }
 
 }  // namespace
+
+// Plan policy of the fused key generation (k_refit_keys): this frame's keys come from a Morton plan made BEFORE the frame's boxes
+// exist, from the centroid bounds the device reported for earlier frames (h_key_stat[4..11], written by whichever kernel
+// finished that frame's header).  The plan is kept while the reported bounds stay inside its own and span more than half of
+// them on every axis; otherwise it is re-made around the reported bounds widened by 1/32 of their extent per side.  A plan is
+// only about tree quality — centroids outside it clamp to its edge cells — so a scene that outruns it costs one frame of
+// slightly coarser keys at the rim.  No report for this collider count yet (the first frames of a collider set), a
+// communicator (replicas rebuild from the exact bounds in the header), the MSD pipeline, the list-per-entity kernel or a
+// scene the fused kernel cannot take: the exact plan, i.e. k_morton after the refit.
+static void choose_morton_plan(b2col_ctx* ctx, uint32_t n)
+{
+    ctx->use_fused_keys = false;
+    const bool propagate = !ctx->world_external && !ctx->world_fresh;
+    if (!ctx->fuse_keys || !ctx->refit_stride || !ctx->h_key_stat || ctx->comm || ctx->sort_msd || !(propagate && ctx->fusable && !ctx->no_fuse)) return;
+    const volatile uint32_t* st = ctx->h_key_stat;
+    uint32_t w[8];
+    for (int k = 0; k < 8; ++k) w[k] = st[4 + k];
+    if (w[3] != n || w[7] != n) return;
+    float amin[3], amax[3];
+    for (int k = 0; k < 3; ++k) {
+        amin[k] = ordered_to_float(w[k]);
+        amax[k] = ordered_to_float(w[4 + k]);
+    }
+    b2col_ctx::PlanState& ps = ctx->plan_state;
+    const int key_bits = 3 * ctx->bits - ctx->drop;
+    bool remake = !ps.valid || ps.n != n || ps.key_bits != key_bits;
+    for (int k = 0; k < 3 && !remake; ++k) {
+        if (!(amin[k] <= amax[k])) continue;  // no finite centroid on this axis
+        const float pext = ps.pmax[k] - ps.pmin[k], aext = amax[k] - amin[k];
+        if (!(ps.pmin[k] <= ps.pmax[k]) || amin[k] < ps.pmin[k] || amax[k] > ps.pmax[k] || !(pext <= 2.0f * aext || pext == 0.0f)) remake = true;
+    }
+    if (remake) {
+        for (int k = 0; k < 3; ++k) {
+            const float margin = (amin[k] <= amax[k]) ? (amax[k] - amin[k]) * 0.03125f : 0.0f;
+            ps.pmin[k] = (margin < B2_INF) ? amin[k] - margin : amin[k];
+            ps.pmax[k] = (margin < B2_INF) ? amax[k] + margin : amax[k];
+        }
+        ps.plan = make_morton_plan(ps.pmin, ps.pmax, key_bits);
+        ps.key_bits = key_bits;
+        ps.n = n;
+        ps.valid = true;
+        ++ps.gen;
+    }
+    ctx->use_fused_keys = true;
+}
 
 // buffers, key width and scratch of a full build of n colliders (everything but the blob, which the callers size first)
 static b2col_status prepare_build_inner(b2col_ctx* ctx, uint32_t n)
@@ -1997,6 +2463,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     GUARD(prepare_build(ctx, n));
     if (!ctx->world_external && !ctx->world_fresh) GUARD(prepare_fuse_map(ctx));
     if (!ctx->world_external) GUARD(ensure(ctx, ctx->d_world, ((size_t)E + 1) * 64));
+    choose_morton_plan(ctx, n);
     PHASE(ctx);  // 1: set-up
     // from here on the blob is being overwritten: until the frame is enqueued in full there is no tree
     ctx->have_tree = false;
@@ -2006,6 +2473,7 @@ b2col_status b2col_update(b2col_ctx* ctx)
     ctx->blob_bytes = blob_bytes;
     ctx->tree_leaves = n;
     ctx->tree_key_bits = 3 * ctx->bits - ctx->drop;
+    ctx->tree_fused_keys = ctx->use_fused_keys;
     ctx->have_tree = true;
     ctx->topology_valid = true;
     ++ctx->full_builds;
@@ -2423,6 +2891,7 @@ b2col_status b2col_get_stats(b2col_ctx* ctx, b2col_stats* out)
     out->n_levels = ctx->level_offsets.empty() ? 0 : (uint32_t)ctx->level_offsets.size() - 1;
     out->sort_passes = (uint32_t)ctx->passes;
     out->key_bits = (uint32_t)ctx->tree_key_bits;
+    out->fused_keys = ctx->tree_fused_keys ? 1u : 0u;
     out->kernel_launches = ctx->launches;
     out->full_builds = ctx->full_builds;
     out->refits = ctx->refits;

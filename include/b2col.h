@@ -117,7 +117,7 @@ typedef struct b2col_stats {
     uint64_t graph_replays;     /* frames that ran as a replay of a captured CUDA graph (cfg.use_cuda_graph) */
     float scene_min[3], scene_max[3]; /* centroid bounds used for the Morton grid */
     uint32_t key_bits;          /* Morton key width of the last full build (b2col_update adapts it to the scene: one radix pass per 8 bits) */
-    uint32_t reserved0;
+    uint32_t fused_keys;        /* 1: the last full build took its keys from a Morton plan made before the frame (scene_min / scene_max are that plan's bounds) */
 } b2col_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------ */

@@ -72,7 +72,8 @@ void emu_refit(uint32_t n, const uint32_t* col_entity, const Aabb24* col_local, 
 // `order` (optional, n entries): visit the leaf "threads" in this order instead of 0..n-1, to show
 // that the result does not depend on thread scheduling.
 void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity, int bits, int drop, float T, Node* nodes, QNode* qnodes, LeafRec* leaves,
-               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order, int* mismatch, uint32_t* has_wild)
+               Grid* grid_out, uint32_t* sorted_prim, uint64_t* sorted_keys, uint32_t* root, const uint32_t* order, int* mismatch, uint32_t* has_wild,
+               const float* plan_bounds)  // optional, 6 floats: min.xyz, max.xyz the Morton plan is made from instead of this frame's centroid bounds (b2col_update's plan policy)
 {
     if (n == 0) return;
     float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -88,7 +89,7 @@ void emu_build(uint32_t n, const Aabb24* world_aabb, const uint32_t* col_entity,
             if (grid_coord_ok(lo)) { bmin[k] = fminf(bmin[k], lo); bmax[k] = fmaxf(bmax[k], lo); }
             if (grid_coord_ok(hi)) { bmin[k] = fminf(bmin[k], hi); bmax[k] = fmaxf(bmax[k], hi); }
         }
-    const MortonPlan plan = make_morton_plan(smin, smax, 3 * bits - drop);
+    const MortonPlan plan = plan_bounds ? make_morton_plan(plan_bounds, plan_bounds + 3, 3 * bits - drop) : make_morton_plan(smin, smax, 3 * bits - drop);
     const Grid grid = make_grid(bmin, bmax, T);
     *grid_out = grid;
     std::vector<uint64_t> keys(n);

@@ -55,7 +55,7 @@ class Emu:
         bits = (key_bits + 2) // 3
         return bits, 3 * bits - key_bits
 
-    def build(self, world_aabb, entity, bits=0, order=None, T=1000.0, key_bits=0):
+    def build(self, world_aabb, entity, bits=0, order=None, T=1000.0, key_bits=0, plan_bounds=None):
         """bits: bits per axis (cfg.morton_bits_per_axis); key_bits: total key width, as b2col_update's key-width policy picks it; neither: the static width"""
         world_aabb = np.ascontiguousarray(world_aabb, np.float32).reshape(-1, 6)
         entity = np.ascontiguousarray(entity, np.uint32)
@@ -76,8 +76,10 @@ class Emu:
         has_wild = C.c_uint32(0)
         if order is not None:
             order = np.ascontiguousarray(order, np.uint32)
+        if plan_bounds is not None:  # (min.xyz, max.xyz) of the Morton plan, as b2col_get_stats reports them (scene_min / scene_max)
+            plan_bounds = np.ascontiguousarray(np.concatenate([np.asarray(plan_bounds[0], np.float32), np.asarray(plan_bounds[1], np.float32)]), np.float32)
         self.lib.emu_build(C.c_uint32(n), _p(world_aabb), _p(entity), C.c_int(bits), C.c_int(drop), C.c_float(T), _p(nodes), _p(qnodes), _p(leaves), _p(grid),
-                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order), C.byref(mismatch), C.byref(has_wild))
+                           _p(sorted_prim), _p(sorted_keys), C.byref(root), _p(order), C.byref(mismatch), C.byref(has_wild), _p(plan_bounds))
         assert mismatch.value == 0, f"grid-space builder disagrees with the exact builder (flags {mismatch.value})"
         return dict(n=n, nodes=nodes, qnodes=qnodes, leaves=leaves, grid=grid, leaf_entity=leaves["entity"].copy(), sorted_prim=sorted_prim,
                     sorted_keys=sorted_keys, root=root.value, world_aabb=world_aabb, has_wild=int(has_wild.value))

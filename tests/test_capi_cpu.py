@@ -62,7 +62,15 @@ def test_sass_is_sm100a_without_fma_in_parity_kernels():
     # 3x 1/d expand to Newton steps) — a fixed, small count.  k_trace_lbvh additionally uses explicit fmaf in
     # its conservative 15-bit grid filter, which only prunes; its exact leaf tests go through
     # __fmul_rn/__fadd_rn/__fsub_rn (b2col_math.cuh), which ptxas never contracts.
-    bad = {k: v for k, v in ffma.items() if any(t in k for t in ("k_refit", "k_propagate"))}
+    # k_refit_keys ends with the frame's header arithmetic (frame_tail -> finish_header -> make_grid: three IEEE divisions and
+    # three reciprocals, whose Newton steps are FFMAs).  k_header is exactly that arithmetic and nothing else, so every
+    # instantiation of k_refit_keys must contain precisely as many FFMAs as k_header: one contracted multiply-add in the
+    # transform / refit / key arithmetic would show up as a surplus.
+    header = [v for k, v in ffma.items() if "k_header" in k]
+    assert len(header) == 1, ffma
+    fused = {k: v for k, v in ffma.items() if "k_refit_keys" in k}
+    assert len(fused) == 6 and all(v == header[0] for v in fused.values()), f"k_refit_keys holds FFMAs beyond the header arithmetic ({header[0]}): {fused}"
+    bad = {k: v for k, v in ffma.items() if any(t in k for t in ("k_refit", "k_propagate")) and "k_refit_keys" not in k}
     assert not bad, f"FFMA found in parity-critical kernels: {bad}"
     ref = [v for k, v in ffma.items() if "k_trace_reftopo" in k]
     assert len(ref) == 1 and ref[0] <= 48, ffma

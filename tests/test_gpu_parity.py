@@ -337,15 +337,17 @@ def test_adaptive_key_width(CollisionSystem, port, emu):
     cs.set_scene(s)
     cs.on_update()
     st = cs.stats()
-    assert st["key_bits"] == 32 and st["sort_passes"] == 4
+    assert st["key_bits"] == 32 and st["sort_passes"] == 4 and st["fused_keys"] == 0  # first build: static width, exact Morton plan (k_morton)
     wide = cs.get_raycasts(rays)
     seen = []
     for frame in range(5):  # the statistic of build k is collected by frame k+1 and read by the host before build k+2
         cs.on_update()
         seen.append(cs.stats()["key_bits"])
     assert seen[0] == 32 and seen[-3:] == [24, 24, 24] and sorted(seen, reverse=True) == seen, f"the uniform scene should narrow to 24-bit keys once and stay there: {seen}"
-    assert cs.stats()["sort_passes"] == 3
-    tree = emu.build(cs.world_aabbs(), s.collider_entity, key_bits=24)
+    st = cs.stats()
+    # later builds also take their keys from a plan made BEFORE the frame (k_refit_keys: no Morton kernel), whose bounds the header records
+    assert st["sort_passes"] == 3 and st["fused_keys"] == 1
+    tree = emu.build(cs.world_aabbs(), s.collider_entity, key_bits=24, plan_bounds=(st["scene_min"], st["scene_max"]))
     assert (cs.leaf_order() == tree["sorted_prim"]).all(), "leaf order at 24 bits"
     exported = cs.bvh
     assert (exported.view(np.uint8) == emu.export(tree).view(np.uint8)).all(), "24-bit tree differs from the host restatement"
@@ -364,7 +366,9 @@ def test_adaptive_key_width(CollisionSystem, port, emu):
         cs.on_update()
         seen.append(cs.stats()["key_bits"])
     assert seen[0] == 32 and seen[-3:] == [40, 40, 40] and sorted(seen) == seen, f"the clustered scene (28 % of the leaves in long runs at 32 bits) should widen to 40-bit keys once: {seen}"
-    tree = emu.build(cs.world_aabbs(), c.collider_entity, key_bits=40)
+    st = cs.stats()
+    assert st["fused_keys"] == 1
+    tree = emu.build(cs.world_aabbs(), c.collider_entity, key_bits=40, plan_bounds=(st["scene_min"], st["scene_max"]))
     assert (cs.leaf_order() == tree["sorted_prim"]).all(), "leaf order at 40 bits"
     assert_raycast_equal(cs.get_raycasts(crays), reference_walk(cs.bvh, crays, port), "clustered scene")
     cs.close()

@@ -18,7 +18,7 @@ for name, scene in ((f"flat {n}", synth.uniform_boxes(n)), (f"hier {n}", synth.h
     cs = CollisionSystem()
     cs.set_scene(scene)
     acc = []
-    for it in range(30):
+    for it in range(30):  # synchronous updates: the key-width / plan policies settle within the first five
         cs.on_update()
         buf = np.zeros(16, np.float32)
         k = lib.b2col_debug_phase_ms(cs.h, buf.ctypes.data, 16)
@@ -29,7 +29,10 @@ for name, scene in ((f"flat {n}", synth.uniform_boxes(n)), (f"hier {n}", synth.h
     fused = len(a) - cs.stats()["sort_passes"] == 4
     names = ["setup"] + (["propagate+refit(%d launches)" % levels] if fused else ["propagate(%d launches)" % levels, "refit"]) + ["morton"]
     names += [f"radix{p}" for p in range(len(a) - len(names) - 1)] + ["build"]
-    if os.environ.get("B2COL_SORT", "") != "lsd":  # MSD pipeline: [setup, transform/refit phases..., morton, msd pass, local sort, build]
+    st = cs.stats()
+    if st["fused_keys"]:
+        names = ["setup", "propagate+refit+keys(%d launches)" % levels, "(no morton)"] + [f"radix{p}" for p in range(st["sort_passes"])] + ["build"]
+    elif os.environ.get("B2COL_SORT", "") != "lsd":  # MSD pipeline: [setup, transform/refit phases..., morton, msd pass, local sort, build]
         names = [f"p{i}" for i in range(len(a) - 4)] + ["morton", "msd", "local", "build"]
-    print(name, " ".join(f"{nm}={v:.1f}" for nm, v in zip(names, a)), f"sum={a.sum():.1f} us")
+    print(name, f"[{st['key_bits']}-bit keys]", " ".join(f"{nm}={v:.1f}" for nm, v in zip(names, a)), f"sum={a.sum():.1f} us")
     cs.close()
