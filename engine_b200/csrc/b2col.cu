@@ -871,6 +871,17 @@ __global__ void k_header(uint32_t n, BlobHeader* hdr, const uint32_t* bounds, fl
 #ifndef B2_BUILD_BLOCK
 #define B2_BUILD_BLOCK 128
 #endif
+// the one thread that completes the root: header fields of the finished tree
+__device__ __noinline__ void build_finish_root(BlobHeader* hdr, uint32_t root, bool wild)
+{
+    hdr->root = root;
+    hdr->trace_root = root;  // k_top_layout, when it runs, redirects the traversal to its compact copy
+    hdr->top_count = 0u;
+    hdr->has_wild = wild ? 1u : 0u;
+}
+#ifndef B2_BUILD_COMPACT
+#define B2_BUILD_COMPACT 1  // (measured at 1M colliders: 0 -> 138.6, 1 -> 136.0, 2 -> 137.2, 3 -> 138.5 us per update) levels after which the block's surviving climbers are packed into its first warps (0: never)
+#endif
 constexpr int BUILD_BLOCK = B2_BUILD_BLOCK;  // update at 1M: 64 -> 170.4 us, 96 -> 168.4, 128 -> 167.8, 256 -> 170.1, 512 -> 178.9, 1024 -> 204.0
 __global__ void __launch_bounds__(BUILD_BLOCK)
 k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ sorted_prim, const LeafRec* __restrict__ world_rec, Xch* xch, QNode* qnodes, LeafRec* leaves, BlobHeader* hdr, uint32_t* scratch, uint32_t scratch_words,
@@ -964,13 +975,18 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         if (n_dup_cur) atomicAdd(slot, (uint32_t)n_dup_cur);
         if (n_dup_narrow) atomicAdd(slot + 1, (uint32_t)n_dup_narrow);
     }
-    if (!valid) return;
 
     // ---- climb
+    // The loop below is bound by instruction issue and half of the climbers retire at every level: after two levels a warp
+    // executes the ~110-instruction step for a quarter of its lanes.  So the block's surviving climbers are packed into its
+    // first warps after each of the first BUILD_COMPACT levels (their state — range, outer levels, box, ref: 32 bytes — moves
+    // through shared memory; who carries a climber is irrelevant to the arrival protocol): 128 leaves then cost 4 + 2 + 1 + 1 + ...
+    // warp-steps instead of 4 + 4 + 4 + 4 + ...  Same exchanges, same stores, same tree.
     uint32_t l = i, r = i;
-    uint32_t lev_r = s_lev[tid + 1];
+    uint32_t lev_r = valid ? s_lev[tid + 1] : LEVEL_END;
     uint32_t ref = LEAF_BIT | i;
-    for (;;) {
+    bool active = valid;
+    auto step = [&]() {  // one level; clears `active` when this climber parks (first to arrive) or has finished the root
         const bool is_left = lev_r < lev_l;  // join the neighbour beyond the LOWER split; array ends never win
         const uint32_t p = is_left ? r : l - 1u;
         const uint32_t j = p - (b0 - 1u);  // split index inside the block (wraps to a huge value left of the block)
@@ -979,18 +995,38 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         uint32_t bound, level;
         bool sib_wild;
         DevOps::store_ref(&qnodes[p], is_left ? 0 : 1, ref | (wild ? WILD_BIT : 0u));
-        const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r, wild);
-        Xch got;
-        if (local) {  // same 128-bit exchange, in shared memory (ATOMS.EXCH.128): the message is the atomic's operand, no fences
-            got = DevOps::exchange_shared(&s_xch[j], mine);
-            if (got.w[3] == UNVISITED) return;  // first to arrive: the sibling's thread finishes this node
+        if (local) {
+            // 128-bit exchange in shared memory (ATOMS.EXCH.128): the message is the atomic's operand, no fences.  A block-local node's
+            // outer splits lie inside the block (or are its boundary splits), so the level beyond the sibling's far bound is read from
+            // s_lev instead of travelling in the message: no packing of the 7 level bits into / out of the boxes' flag bits — 24 of the
+            // ~120 instructions of a step
+            Xch mine;
+            mine.w[0] = box.w[0];
+            mine.w[1] = box.w[1];
+            mine.w[2] = box.w[2];
+            mine.w[3] = (is_left ? l : r) | (wild ? WILD_BIT : 0u);  // < 2^31: never UNVISITED
+            const Xch got = DevOps::exchange_shared(&s_xch[j], mine);
+            if (got.w[3] == UNVISITED) {  // first to arrive: the sibling's climber finishes this node
+                active = false;
+                return;
+            }
+            sib.w[0] = got.w[0];
+            sib.w[1] = got.w[1];
+            sib.w[2] = got.w[2];
+            bound = got.w[3] & REF_INDEX_MASK;
+            sib_wild = (got.w[3] & WILD_BIT) != 0u;
+            level = s_lev[is_left ? bound - (b0 - 1u) : bound - b0];  // split `bound` (right of the new range) / `bound - 1` (left of it)
         }
         else {
-            got = DevOps::exchange(&xch[p], mine);
-            if (got.w[3] == UNVISITED) return;
+            const Xch mine = xch_pack(box, is_left ? l : r, is_left ? lev_l : lev_r, wild);
+            const Xch got = DevOps::exchange(&xch[p], mine);
+            if (got.w[3] == UNVISITED) {
+                active = false;
+                return;
+            }
             *reinterpret_cast<uint4*>(&xch[p]) = make_uint4(0u, 0u, 0u, UNVISITED);  // self-cleaning: ready for the next frame
+            xch_unpack(got, sib, bound, level, sib_wild);
         }
-        xch_unpack(got, sib, bound, level, sib_wild);
         wild = wild || sib_wild;
         DevOps::store_qboxes(&qnodes[p], is_left ? box.w : sib.w, is_left ? sib.w : box.w);
         if (is_left) {
@@ -1005,12 +1041,53 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
         for (int k = 0; k < 3; ++k) box.w[k] = qplane_merge(box.w[k], sib.w[k]);
         ref = p;
         if (lev_l == LEVEL_END && lev_r == LEVEL_END) {  // the range is the whole array
-            hdr->root = p;
-            hdr->trace_root = p;  // k_top_layout, when it runs, redirects the traversal to its compact copy
-            hdr->top_count = 0u;
-            hdr->has_wild = wild ? 1u : 0u;
-            return;
+            build_finish_root(hdr, p, wild);  // (a call: kept out of the loop's instruction stream)
+            active = false;
         }
+    };
+#if B2_BUILD_COMPACT > 0
+    __shared__ uint4 s_state[BUILD_BLOCK][2];
+    __shared__ uint32_t s_cnt[BUILD_BLOCK / 32];
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int round = 0; round < B2_BUILD_COMPACT; ++round) {
+        if (active) step();
+        const unsigned alive = __ballot_sync(0xffffffffu, active);
+        if (lane == 0) s_cnt[warp] = (uint32_t)__popc(alive);
+        __syncthreads();
+        uint32_t before = 0u, total = 0u;
+#pragma unroll
+        for (int w = 0; w < BUILD_BLOCK / 32; ++w) {
+            const uint32_t c = s_cnt[w];
+            if (w < warp) before += c;
+            total += c;
+        }
+        if (active) {
+            const uint32_t slot = before + (uint32_t)__popc(alive & lt_mask);
+            s_state[slot][0] = make_uint4(l, r, ref, lev_l | (lev_r << 8) | (wild ? 0x10000u : 0u));
+            s_state[slot][1] = make_uint4(box.w[0], box.w[1], box.w[2], 0u);
+        }
+        __syncthreads();
+        active = (uint32_t)tid < total;
+        if (active) {
+            const uint4 a = s_state[tid][0], c = s_state[tid][1];
+            l = a.x;
+            r = a.y;
+            ref = a.z;
+            lev_l = a.w & 0xFFu;
+            lev_r = (a.w >> 8) & 0xFFu;
+            wild = (a.w & 0x10000u) != 0u;
+            box.w[0] = c.x;
+            box.w[1] = c.y;
+            box.w[2] = c.z;
+        }
+        // (the next round writes s_cnt / s_state only after its own first barrier, which every reader above has then passed)
+    }
+#endif
+    if (!active) return;
+    for (;;) {
+        step();
+        if (!active) return;
     }
 }
 

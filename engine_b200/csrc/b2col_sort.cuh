@@ -33,7 +33,10 @@ enum : uint32_t {
 constexpr int LB_BATCH = B2_LB_BATCH;
 // Tiles per look-back group, a template parameter of the pass: 8 from 128 tiles up (-2.8 us per update at 1M, -25 us at 10M),
 // 16 below (200k colliders: 70.8 vs 73.6 us with 8).  The status array is sized for the smaller group.
-constexpr uint32_t LB_GROUP_SMALL = 8, LB_GROUP_LARGE = 16;
+#ifndef B2_LB_GROUP_SMALL
+#define B2_LB_GROUP_SMALL 8
+#endif
+constexpr uint32_t LB_GROUP_SMALL = B2_LB_GROUP_SMALL, LB_GROUP_LARGE = 16;
 static_assert(RS_THREADS == RS_RADIX, "one thread per digit in the scan phases");
 
 #ifdef B2_SORT_TIMING  // dev builds only: per-tile phase timestamps (ns, %globaltimer) of the LAST pass launched
