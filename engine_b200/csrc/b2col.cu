@@ -293,35 +293,36 @@ constexpr int REFIT_BLOCK = B2_REFIT_BLOCK;
 template <int BLOCK = REFIT_BLOCK>
 __device__ __forceinline__ void bounds_reduce(float* cmin, float* cmax, uint32_t* bounds)
 {
+    // warp level: one REDUX per value on the order-preserving integer image of the float (twelve REDUX.MAX instead of sixty
+    // shuffle + min/max pairs: a third of the instructions a one-entity thread of k_propagate_refit_level executes);
+    // min = max of the complemented image — the form the scratch words hold anyway
+    uint32_t umin_inv[6], umax[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            cmin[k] = fminf(cmin[k], __shfl_xor_sync(0xffffffffu, cmin[k], o));
-            cmax[k] = fmaxf(cmax[k], __shfl_xor_sync(0xffffffffu, cmax[k], o));
-        }
+        umin_inv[k] = __reduce_max_sync(0xffffffffu, ~float_to_ordered(cmin[k]));
+        umax[k] = __reduce_max_sync(0xffffffffu, float_to_ordered(cmax[k]));
     }
-    __shared__ float smin[BLOCK / 32][6], smax[BLOCK / 32][6];
+    __shared__ uint32_t smin_inv[BLOCK / 32][6], smax[BLOCK / 32][6];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) {
-            smin[warp][k] = cmin[k];
-            smax[warp][k] = cmax[k];
+            smin_inv[warp][k] = umin_inv[k];
+            smax[warp][k] = umax[k];
         }
     }
     __syncthreads();
     if (threadIdx.x < 6) {
         const int k = threadIdx.x;
-        float a = smin[0][k], b = smax[0][k];
+        uint32_t a = smin_inv[0][k], b = smax[0][k];
         for (int w = 1; w < BLOCK / 32; ++w) {
-            a = fminf(a, smin[w][k]);
-            b = fmaxf(b, smax[w][k]);
+            a = max(a, smin_inv[w][k]);
+            b = max(b, smax[w][k]);
         }
-        if (a <= b) {  // false when the block saw no finite value
+        if (~a <= b) {  // ordered(min) <= ordered(max); false when the block saw no finite value (min = +inf, max = -inf)
             const int base = k < 3 ? 0 : 6, kk = k < 3 ? k : k - 3;
-            atomicMax(&bounds[base + kk], ~float_to_ordered(a));
-            atomicMax(&bounds[base + 3 + kk], float_to_ordered(b));
+            atomicMax(&bounds[base + kk], a);
+            atomicMax(&bounds[base + 3 + kk], b);
         }
     }
 }

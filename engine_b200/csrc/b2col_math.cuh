@@ -281,6 +281,7 @@ struct MortonPlan {
     int axis[3];             // a, b, c: original axis indices by decreasing extent
     int shift_a;             // axis a is quantised to at most 21 bits; the code wants na = qbits_a + shift_a
     int nc, d2, drop;
+    int fast32;              // plain three-way interleave of at most 11 bits per axis into at most 32 key bits: morton_key's 32-bit path
 };
 
 constexpr int MORTON_AXIS_BITS = 21;  // spread3 / float quantisation limit per axis
@@ -334,6 +335,7 @@ B2_HD MortonPlan make_morton_plan(const float* cmin, const float* cmax, int key_
     p.nc = nc;
     p.d2 = d2;
     p.drop = total > key_bits ? total - key_bits : 0;
+    p.fast32 = (d1 == 0 && d2 == 0 && p.shift_a == 0 && na == nc && nc >= 1 && nc <= 11 && p.drop <= 2 && 3 * nc - p.drop <= 32) ? 1 : 0;
     const int qbits[3] = {qa, nc + d2, nc};
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -343,6 +345,17 @@ B2_HD MortonPlan make_morton_plan(const float* cmin, const float* cmax, int key_
         p.qmax[k] = B2_SUB(cells, 1.0f);
     }
     return p;
+}
+
+// spread3 for values below 2^11, in 32-bit arithmetic (the same steps as spread3 with the masks' low halves; bit 10 lands on bit 30)
+B2_HD uint32_t spread3_11(uint32_t v)
+{
+    uint32_t x = v & 0x7FFu;
+    x = (x | (x << 16)) & 0xFF0000FFu;
+    x = (x | (x << 8)) & 0x0F00F00Fu;
+    x = (x | (x << 4)) & 0xC30C30C3u;
+    x = (x | (x << 2)) & 0x49249249u;
+    return x;
 }
 
 // Centroid (GetBoxCentroid, src/system_collisions.cpp:43-50: (min+max)*0.5f) -> key
@@ -359,6 +372,15 @@ B2_HD uint64_t morton_key(const float* lo, const float* hi, const MortonPlan& p)
     const uint32_t qa32 = p.axis[0] == 0 ? q[0] : (p.axis[0] == 1 ? q[1] : q[2]);
     const uint32_t qb = p.axis[1] == 0 ? q[0] : (p.axis[1] == 1 ? q[1] : q[2]);
     const uint32_t qc = p.axis[2] == 0 ? q[0] : (p.axis[2] == 1 ? q[1] : q[2]);
+    if (p.fast32) {
+        // cubic scene, key of at most 32 bits (every packed-key build): the code is the plain interleave a b c a b c ... with the lowest
+        // `drop` bits cut — c's bit 0, then b's — which 32-bit arithmetic can form directly: a third of the instructions of the
+        // general 64-bit path below, bit for bit the same key (tests/test_emu_logic.py checks both against an independent interleave)
+        const uint32_t k32 = p.drop == 0   ? (spread3_11(qa32) << 2) | (spread3_11(qb) << 1) | spread3_11(qc)
+                             : p.drop == 1 ? (spread3_11(qa32) << 1) | spread3_11(qb) | (spread3_11(qc >> 1) << 2)
+                                           : spread3_11(qa32) | (spread3_11(qb >> 1) << 2) | (spread3_11(qc >> 1) << 1);
+        return (uint64_t)k32;
+    }
     const uint64_t qa = (uint64_t)qa32 << p.shift_a;
     const uint32_t mc = (1u << p.nc) - 1u, m2 = (1u << p.d2) - 1u;
     const uint64_t low = (spread3((uint32_t)qa & mc) << 2) | (spread3(qb & mc) << 1) | spread3(qc);

@@ -204,7 +204,7 @@ def test_morton_plan_cubic_scene_is_the_plain_interleave(emu):
     rng = np.random.default_rng(1)
     c = rng.uniform(-100, 100, (5000, 3)).astype(np.float32)
     cmin, cmax = c.min(0), c.max(0)
-    for key_bits, bits in ((32, 11), (30, 10), (40, 14), (48, 16), (63, 21)):
+    for key_bits, bits in ((32, 11), (30, 10), (40, 14), (48, 16), (63, 21), (24, 8), (31, 11), (26, 9), (25, 9), (33, 11), (16, 6)):  # <= 32 bits: the 32-bit path, every `drop`
         plan, keys = emu.morton(c, cmin, cmax, key_bits)
         assert plan["d2"] == 0 and plan["shift_a"] == 0 and plan["nc"] == bits and plan["drop"] == 3 * bits - key_bits
         order = [plan["a"], plan["b"], plan["c"]]

@@ -372,6 +372,47 @@ def test_adaptive_key_width(CollisionSystem, port, emu):
     assert (cs.leaf_order() == tree["sorted_prim"]).all(), "leaf order at 40 bits"
     assert_raycast_equal(cs.get_raycasts(crays), reference_walk(cs.bvh, crays, port), "clustered scene")
     cs.close()
+def test_morton_plan_follows_the_scene(CollisionSystem, port, emu):
+    """The keys of frame k come from a Morton plan made BEFORE frame k, from bounds earlier frames reported (k_refit_keys,
+    choose_morton_plan).  A scene that outruns its plan (everything scaled up 8x between two frames: most centroids clamp to the
+    plan's edge cells), shrinks far inside it (the plan is re-made one frame later) or drifts away must answer every ray like the
+    reference walking the exported tree in EVERY frame — a stale plan may only cost tree quality — and the tree must be the host
+    restatement's tree for the plan bounds the header records."""
+    s = synth.hierarchy_scene(60_000, 80, extent=300)  # three hierarchy levels: the header is written by the LAST level's last block
+    cs = CollisionSystem()
+    cs.set_scene(s)
+    base = s.pos.copy()
+    rng = np.random.default_rng(91)
+    rays0 = np.concatenate([synth.random_rays(20_000, seed=92, extent=300), synth.axis_rays(2_000, seed=93, extent=300)])
+    plans = []
+    #            scale  shift
+    script = [(1.0, 0.0), (1.0, 0.0), (1.0, 0.0), (8.0, 0.0), (8.0, 0.0), (8.0, 0.0), (0.05, 0.0), (0.05, 0.0), (0.05, 0.0), (1.0, 5000.0), (1.0, 5000.0), (1.0, 5000.0)]
+    for frame, (scale, shift) in enumerate(script):
+        s.pos[:] = base
+        s.pos[1:81] = base[1:81] * np.float32(scale) + np.float32(shift) + rng.uniform(-0.5, 0.5, (80, 3)).astype(np.float32)  # the roots carry everything below them
+        cs.set_trs(s.pos, s.rot, s.scl)
+        cs.on_update()
+        st = cs.stats()
+        plans.append((st["fused_keys"], tuple(st["scene_min"]), tuple(st["scene_max"])))
+        rays = rays0.copy()
+        rays[:, 0:3] = rays0[:, 0:3] * np.float32(scale if scale >= 1.0 else 1.0) + np.float32(shift)
+        boxes = cs.world_aabbs()
+        pick = rng.integers(0, boxes.shape[0], 10_000)  # ... and rays aimed at colliders, wherever the scene is now
+        target = (boxes[pick, 0:3] + boxes[pick, 3:6]) * np.float32(0.5)
+        origin = target + rng.standard_normal((10_000, 3)).astype(np.float32) * np.float32(40.0)
+        rays = np.concatenate([rays, np.concatenate([origin, target - origin], axis=1).astype(np.float32)])
+        got = cs.get_raycasts(rays)
+        exported = cs.bvh
+        assert_raycast_equal(got, reference_walk(exported, rays, port), f"frame {frame} (scale {scale}, shift {shift}) vs the reference's GetRaycast on the exported tree")
+        if frame in (2, 3, 6, 9, 11):  # settled, first frame after each jump (stale plan), settled again
+            tree = emu.build(cs.world_aabbs(), s.collider_entity, key_bits=st["key_bits"], plan_bounds=(st["scene_min"], st["scene_max"]) if st["fused_keys"] else None)
+            assert (cs.leaf_order() == tree["sorted_prim"]).all(), f"frame {frame}: leaf order differs from the host restatement under the recorded plan"
+            assert (exported.view(np.uint8) == emu.export(tree).view(np.uint8)).all(), f"frame {frame}: exported tree"
+        assert got["hit"].sum() > 8000, f"frame {frame}: the aimed rays should hit ({int(got['hit'].sum())})"
+    assert plans[0][0] == 0 and all(p[0] == 1 for p in plans[1:]), f"exact plan on the first frame, plan-before-frame afterwards: {[p[0] for p in plans]}"
+    assert plans[3][1:] == plans[2][1:], "the first frame after the scene grew still runs on the old plan"
+    assert plans[5][1:] != plans[2][1:] and plans[8][1:] != plans[5][1:] and plans[11][1:] != plans[8][1:], "the plan must follow the scene within two frames"
+    cs.close()
 
 
 def test_duplicate_boxes_and_ties(CollisionSystem, port):
