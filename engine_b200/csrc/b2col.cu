@@ -1092,7 +1092,10 @@ k_build(uint32_t n, const uint64_t* __restrict__ keys, const uint32_t* __restric
     }
 }
 
+#if B2_BUILD_BLOCK == 128  // the two measured-and-rejected alternatives assume 128 leaves per block (dev sweeps of B2_BUILD_BLOCK build without them)
+#define B2_HAVE_BUILD_VARIANTS 1
 #include "b2col_build.inl"  // k_build_direct: the same hierarchy, block-local nodes computed from range queries instead of climbed
+#endif
 
 // Compact copy of the top levels of the tree, for trees larger than L2.
 //
@@ -2042,6 +2045,7 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
         LAUNCH_FRAME(ctx, k_build, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
                ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4), ctx->d_key_ctr.as<uint32_t>());
+#ifdef B2_HAVE_BUILD_VARIANTS
     else if (ctx->build_variant == 2)
         LAUNCH_FRAME(ctx, k_build_warp, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
@@ -2050,6 +2054,9 @@ static b2col_status launch_build(b2col_ctx* ctx, uint32_t n, int side)
         LAUNCH_FRAME(ctx, k_build_direct, cdiv(n, BUILD_BLOCK), BUILD_BLOCK, 0, n, ctx->d_keys[side].as<uint64_t>(), ctx->d_vals[side].as<uint32_t>(),
                ctx->d_world_aabb.as<LeafRec>(), ctx->d_xch.as<Xch>(), blob_qnodes(ctx), blob_leaves(ctx, n), blob_hdr(ctx),
                ctx->d_zero.as<uint32_t>(), (uint32_t)(ctx->zero_bytes / 4));
+#else
+    else return fail(ctx, B2COL_ERR_UNSUPPORTED, "B2COL_BUILD variants are not part of this build");
+#endif
     ctx->scratch_clean = true;  // k_build leaves every scratch word zero
     // Trees that do not fit L2: compact copy of the top levels (see k_top_layout).  Below ~2M colliders the whole tree is
     // L2-resident and the copy buys nothing (measured at 1M: 1875 Mrays/s either way) but would cost the frame ~15 us.
