@@ -718,14 +718,24 @@ __device__ __forceinline__ uint32_t lead_of(const void* p) { return (uint32_t)(r
 __device__ __forceinline__ uint32_t span_of(const void* p, uint32_t bytes) { return (lead_of(p) + bytes + 15u) & ~15u; }
 }  // namespace bulk
 
+// One pipeline per block (tile = its 256 entities, a __syncthreads per tile).  B2_RK_WARP_TILES: one pipeline PER WARP (tile = the
+// warp's 32 entities, its own pair of mbarriers, no block barrier inside the loop, so that the warps drift apart) — measured equal
+// (136.9 vs 136.1 us per update, profiles/r2_experiments.txt): this kernel does not wait for its inputs either way.
+#ifdef B2_RK_WARP_TILES
+constexpr int RK_TILE = 32;
+constexpr int RK_PIPES = RK_BLOCK / 32;
+#else
+constexpr int RK_TILE = RK_BLOCK;
+constexpr int RK_PIPES = 1;
+#endif
 struct alignas(16) RkStage {
-    unsigned char rot[RK_BLOCK * 16];
-    unsigned char pos[RK_BLOCK * 12 + 32];
-    unsigned char scl[RK_BLOCK * 12 + 32];
-    unsigned char box[RK_BLOCK * 24 + 32];
-    unsigned char par[RK_BLOCK * 4 + 32];
+    unsigned char rot[RK_TILE * 16];
+    unsigned char pos[RK_TILE * 12 + 32];
+    unsigned char scl[RK_TILE * 12 + 32];
+    unsigned char box[RK_TILE * 24 + 32];
+    unsigned char par[RK_TILE * 4 + 32];
 };
-static_assert(sizeof(RkStage) % 16 == 0 && (RK_BLOCK * 12) % 16 == 0 && (RK_BLOCK * 24) % 16 == 0 && (RK_BLOCK * 4) % 16 == 0, "stage ranges are 16-byte multiples");
+static_assert(sizeof(RkStage) % 16 == 0 && (RK_TILE * 12) % 16 == 0 && (RK_TILE * 24) % 16 == 0 && (RK_TILE * 4) % 16 == 0, "stage ranges are 16-byte multiples");
 
 template <bool KEYS>
 __global__ void __launch_bounds__(RK_BLOCK, B2_RK_MIN_BLOCKS)
@@ -733,14 +743,17 @@ k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, cons
                   const float4* __restrict__ rot4, const float* __restrict__ scl3, float4* world, const Aabb24* __restrict__ col_local, LeafRec* __restrict__ world_rec,
                   uint32_t* bounds, KeyGen kg, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* ghist, FrameTail tail)
 {
-    __shared__ RkStage stage[2];
-    __shared__ alignas(8) uint64_t full[2];
+    __shared__ RkStage stage[2][RK_PIPES];
+    __shared__ alignas(8) uint64_t full[2][RK_PIPES];
     __shared__ uint32_t shist[KEYS ? RS_MAX_PASSES : 1][RS_RADIX];
     __shared__ bool s_last;
     const int tid = threadIdx.x;
+    const int pipe = RK_PIPES == 1 ? 0 : tid >> 5;        // which pipeline this thread reads from
+    const int slot = RK_PIPES == 1 ? tid : (tid & 31);    // its entity inside the tile
+    const bool issuer = slot == 0;                        // the thread that requests the pipeline's copies
     if (tid == 0) {
-        bulk::mbar_init(&full[0], 1u);
-        bulk::mbar_init(&full[1], 1u);
+        for (int st = 0; st < 2; ++st)
+            for (int w = 0; w < RK_PIPES; ++w) bulk::mbar_init(&full[st][w], 1u);
         bulk::mbar_init_fence();
     }
     if (KEYS) {
@@ -749,10 +762,11 @@ k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, cons
     }
     __syncthreads();
     pdl_wait();  // the arrays below are written by work earlier in the stream
-    const uint32_t n_tiles = (count + RK_BLOCK - 1u) / RK_BLOCK;
-    // ranges of tile t (all threads can name them; thread 0 requests them)
+    const uint32_t n_tiles = (count + RK_TILE - 1u) / RK_TILE;
+    const uint32_t t_stride = gridDim.x * RK_PIPES;
+    // ranges of tile t (every thread can name them; the pipeline's issuer requests them)
     auto request = [&](uint32_t t, int st) {
-        const uint32_t i0 = t * RK_BLOCK, valid = min((uint32_t)RK_BLOCK, count - i0);
+        const uint32_t i0 = t * RK_TILE, valid = min((uint32_t)RK_TILE, count - i0);
         const size_t e = (size_t)e0 + i0, c = (size_t)c0 + i0;
         const void* g_rot = rot4 + e;
         const void* g_pos = pos3 + 3 * e;
@@ -761,36 +775,38 @@ k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, cons
         const void* g_par = parent + e;
         const uint32_t b_rot = valid * 16u, b_pos = bulk::span_of(g_pos, valid * 12u), b_scl = bulk::span_of(g_scl, valid * 12u), b_box = bulk::span_of(g_box, valid * 24u),
                        b_par = root_level ? 0u : bulk::span_of(g_par, valid * 4u);
-        bulk::mbar_arrive_expect_tx(&full[st], b_rot + b_pos + b_scl + b_box + b_par);
-        RkStage& sg = stage[st];
-        bulk::g2s(sg.rot, g_rot, b_rot, &full[st]);
-        bulk::g2s(sg.pos, static_cast<const char*>(g_pos) - bulk::lead_of(g_pos), b_pos, &full[st]);
-        bulk::g2s(sg.scl, static_cast<const char*>(g_scl) - bulk::lead_of(g_scl), b_scl, &full[st]);
-        bulk::g2s(sg.box, static_cast<const char*>(g_box) - bulk::lead_of(g_box), b_box, &full[st]);
-        if (!root_level) bulk::g2s(sg.par, static_cast<const char*>(g_par) - bulk::lead_of(g_par), b_par, &full[st]);
+        uint64_t* bar = &full[st][pipe];
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the stage's earlier reads (generic proxy) before the copies' writes (async proxy)
+        bulk::mbar_arrive_expect_tx(bar, b_rot + b_pos + b_scl + b_box + b_par);
+        RkStage& sg = stage[st][pipe];
+        bulk::g2s(sg.rot, g_rot, b_rot, bar);
+        bulk::g2s(sg.pos, static_cast<const char*>(g_pos) - bulk::lead_of(g_pos), b_pos, bar);
+        bulk::g2s(sg.scl, static_cast<const char*>(g_scl) - bulk::lead_of(g_scl), b_scl, bar);
+        bulk::g2s(sg.box, static_cast<const char*>(g_box) - bulk::lead_of(g_box), b_box, bar);
+        if (!root_level) bulk::g2s(sg.par, static_cast<const char*>(g_par) - bulk::lead_of(g_par), b_par, bar);
     };
     float cmin[6] = {B2_INF, B2_INF, B2_INF, B2_INF, B2_INF, B2_INF}, cmax[6] = {-B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF, -B2_INF};
-    uint32_t t = blockIdx.x;
-    if (tid == 0 && t < n_tiles) request(t, 0);
-    for (uint32_t k = 0; t < n_tiles; t += gridDim.x, ++k) {
+    uint32_t t = blockIdx.x * RK_PIPES + (uint32_t)pipe;
+    if (issuer && t < n_tiles) request(t, 0);
+    for (uint32_t k = 0; t < n_tiles; t += t_stride, ++k) {
         const int st = (int)(k & 1u);
-        if (tid == 0 && t + gridDim.x < n_tiles) request(t + gridDim.x, st ^ 1);  // that stage was last read in iteration k - 1, which ended with a barrier
-        bulk::mbar_wait(&full[st], (k >> 1) & 1u);
-        const uint32_t i0 = t * RK_BLOCK, i = i0 + (uint32_t)tid;
+        if (issuer && t + t_stride < n_tiles) request(t + t_stride, st ^ 1);  // that stage was last read in iteration k - 1, which ended with a barrier of the pipeline's threads
+        bulk::mbar_wait(&full[st][pipe], (k >> 1) & 1u);
+        const uint32_t i0 = t * RK_TILE, i = i0 + (uint32_t)slot;
         if (i < count) {
-            const RkStage& sg = stage[st];
+            const RkStage& sg = stage[st][pipe];
             const size_t ef = (size_t)e0 + i0, cf = (size_t)c0 + i0;
             const uint32_t e = e0 + i, c = c0 + i;
-            const float4 q4 = *reinterpret_cast<const float4*>(sg.rot + 16 * tid);
-            const float* sp = reinterpret_cast<const float*>(sg.pos + bulk::lead_of(pos3 + 3 * ef) + 12 * tid);
-            const float* ss = reinterpret_cast<const float*>(sg.scl + bulk::lead_of(scl3 + 3 * ef) + 12 * tid);
-            const float2* sb = reinterpret_cast<const float2*>(sg.box + bulk::lead_of(col_local + cf) + 24 * tid);
+            const float4 q4 = *reinterpret_cast<const float4*>(sg.rot + 16 * slot);
+            const float* sp = reinterpret_cast<const float*>(sg.pos + bulk::lead_of(pos3 + 3 * ef) + 12 * slot);
+            const float* ss = reinterpret_cast<const float*>(sg.scl + bulk::lead_of(scl3 + 3 * ef) + 12 * slot);
+            const float2* sb = reinterpret_cast<const float2*>(sg.box + bulk::lead_of(col_local + cf) + 24 * slot);
             const float p[3] = {sp[0], sp[1], sp[2]}, sc[3] = {ss[0], ss[1], ss[2]};
             LocalBox lb;
             lb.a = sb[0];
             lb.b = sb[1];
             lb.c = sb[2];
-            const uint32_t par = root_level ? 0u : *reinterpret_cast<const uint32_t*>(sg.par + bulk::lead_of(parent + ef) + 4 * tid);
+            const uint32_t par = root_level ? 0u : *reinterpret_cast<const uint32_t*>(sg.par + bulk::lead_of(parent + ef) + 4 * slot);
             float W[16];
             entity_world_from(p, q4, sc, par, world, W);
             float4* ow = world + 4 * (size_t)e;
@@ -810,8 +826,11 @@ k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, cons
                 for (int pp = kg.hist_lo; pp < kg.passes; ++pp) atomicAdd(&shist[pp][(uint32_t)(key >> (8 * pp)) & 255u], 1u);
             }
         }
-        __syncthreads();  // the stage is free for the request of iteration k + 1
+        // the stage is free for the request of iteration k + 1 once every thread of the pipeline has read it
+        if (RK_PIPES == 1) __syncthreads();
+        else __syncwarp();
     }
+    if (RK_PIPES != 1) __syncthreads();  // the warps ran at their own pace: meet before the block-level reductions
     bounds_reduce<RK_BLOCK>(cmin, cmax, bounds);
     if (KEYS) {
         __syncthreads();
