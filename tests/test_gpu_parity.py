@@ -413,6 +413,48 @@ def test_morton_plan_follows_the_scene(CollisionSystem, port, emu):
     assert plans[3][1:] == plans[2][1:], "the first frame after the scene grew still runs on the old plan"
     assert plans[5][1:] != plans[2][1:] and plans[8][1:] != plans[5][1:] and plans[11][1:] != plans[8][1:], "the plan must follow the scene within two frames"
     cs.close()
+def test_small_random_scenes_over_many_frames(CollisionSystem, port):
+    """The per-frame policies (key width, Morton plan, fused keys, dense / list-driven levels, the header written by the last block of
+    the last level's launch) on the scenes where their corner cases live: a handful of colliders, one collider, colliders on a
+    subset of the entities in shuffled order (no dense level), colliders only on inner entities (the LAST hierarchy level has none),
+    several hierarchy depths.  Every frame of every scene: world AABBs bit-exact vs the oracle and every ray equal to the reference's
+    GetRaycast on the exported tree."""
+    rng = np.random.default_rng(404)
+    for case in range(14):
+        n_roots = int(rng.integers(1, 6))
+        n_col = [1, 2, 3, 7, 33, 128, 129, 255, 257, 700, 2049, 4097, 9000, 20000][case]
+        s = synth.hierarchy_scene(n_col, n_roots, seed=500 + case, extent=60.0, deep_fraction=[0.0, 0.1, 0.5][case % 3])
+        keep = np.arange(n_col)
+        if case % 4 == 1:  # colliders on a shuffled subset of the entities: list-driven levels, entities without collider
+            keep = rng.permutation(n_col)[: max(1, n_col * 2 // 3)]
+        elif case % 4 == 2 and n_col > 4:  # only the first (inner) collider entities: the deepest level may hold no collider at all
+            keep = np.arange(max(1, n_col // 2))
+        s.collider_entity = np.ascontiguousarray(s.collider_entity[keep])
+        s.collider_aabb = np.ascontiguousarray(s.collider_aabb[keep])
+        rays = np.concatenate([synth.random_rays(3000, seed=600 + case, extent=70.0), synth.axis_rays(300, seed=700 + case, extent=60.0)])
+        cs = CollisionSystem(use_cuda_graph=bool(case % 2))
+        cs.set_scene(s)
+        seen = []
+        for frame in range(6):
+            if frame:
+                synth.perturb_roots(s, n_roots, frame, seed=800 + case)
+                if frame == 4:
+                    s.pos[1 : n_roots + 1] *= np.float32(3.0)  # the scene outruns the plan of the frames before
+                cs.set_trs(s.pos, s.rot, s.scl)
+            if frame == 3:
+                cs.on_update_refit()
+            else:
+                cs.on_update()
+            world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+            want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+            assert (bits(cs.world_aabbs()) == bits(want_boxes)).all(), f"case {case} frame {frame}: world AABBs"
+            assert (bits(cs.world_matrices()) == bits(world[1:])).all(), f"case {case} frame {frame}: world matrices"
+            got = cs.get_raycasts(rays)
+            assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), f"case {case} ({len(keep)} colliders, {n_roots} roots) frame {frame}")
+            st = cs.stats()
+            seen.append((st["key_bits"], st["fused_keys"]))
+        assert seen[0][1] == 0 and seen[5][1] == 1, f"case {case}: exact plan first, plan-before-frame later: {seen}"
+        cs.close()
 
 
 def test_duplicate_boxes_and_ties(CollisionSystem, port):
