@@ -126,6 +126,7 @@ struct b2col_comm_state {
     //          transfers that overlap the following chunks' traversal; only the last chunk's copy is exposed.
     int gather_bulk = -1;        // -1: bulk when n_ranks > 4
     size_t gather_chunk = (size_t)2 << 20;  // rays per chunk of the bulk gather (B2COL_GATHER_CHUNK)
+    bool gather_tail = true;                // halving chunk sizes at the end of a slice (B2COL_GATHER_TAIL=0: equal chunks)
     uint64_t gathers = 0, replications = 0;
 };
 
@@ -170,6 +171,8 @@ b2col_status comm_attach(b2col_ctx* ctx, b2_ncclComm_t comm, int n_ranks, int ra
         if (!strcmp(e, "fused")) c->gather_bulk = 0;
     }
     if (const char* e = getenv("B2COL_GATHER_CHUNK")) c->gather_chunk = std::max<size_t>(65536, (size_t)atoll(e));
+    c->gather_tail = n_ranks > 4;  // measured: 8 ranks 12 924 -> 13 374 Mrays/s with the gather inside the timed region; 2 ranks (bulk forced) 3 407 -> 3 364
+    if (const char* e = getenv("B2COL_GATHER_TAIL")) c->gather_tail = atoi(e) != 0;
     c->stage_remote = n_ranks > 2;  // one peer's per-lane stores beat the staged form (3665 vs 3605 Mrays/s on 2 GPUs); from three peers on staging wins
     if (const char* e = getenv("B2COL_REMOTE_STAGE")) c->stage_remote = atoi(e) != 0;
     return B2COL_OK;
@@ -278,7 +281,40 @@ b2col_status comm_enqueue_shard(b2col_ctx* ctx, const b2col_ray* d_rays_shard, s
         const size_t n = hi - lo;
         // at most gather_chunk rays per chunk, at least four chunks per slice (the last chunk's copy is what stays exposed), never tiny ones
         const size_t chunk = std::min(c->gather_chunk, std::max<size_t>((size_t)256 << 10, (n / 4 + 65535) & ~(size_t)65535));
-        const size_t n_chunks = (n + chunk - 1) / chunk;
+        // chunk schedule: full chunks, then a halving tail (chunk/2, chunk/4, ... down to 256K rays): what stays exposed at the end of
+        // the step is the LAST chunk's copy into the window — seven peers' worth of it on the destination's inbound links — so the last
+        // chunks are small; the two alternating trace streams hide the extra kernel boundaries (B2COL_GATHER_TAIL=0: equal chunks)
+        std::vector<size_t> sizes;
+        {
+            size_t left = n;
+            const size_t floor_chunk = (size_t)256 << 10;
+            if (c->gather_tail && chunk >= 4 * floor_chunk && n >= 3 * chunk) {
+                size_t tail_total = 0;
+                std::vector<size_t> tail;
+                for (size_t t = chunk / 2; t >= floor_chunk; t /= 2) {
+                    tail.push_back(t);
+                    tail_total += t;
+                }
+                tail.push_back(floor_chunk);
+                tail_total += floor_chunk;
+                while (left > tail_total + chunk / 2) {
+                    const size_t m = std::min(chunk, left - tail_total);
+                    sizes.push_back(m);
+                    left -= m;
+                }
+                for (size_t t : tail) {
+                    const size_t m = std::min(t, left);
+                    if (m) sizes.push_back(m);
+                    left -= m;
+                }
+            }
+            while (left) {
+                const size_t m = std::min(chunk, left);
+                sizes.push_back(m);
+                left -= m;
+            }
+        }
+        const size_t n_chunks = sizes.size();
         GUARD(ensure(ctx, ctx->d_hits, n * sizeof(b2col_raycast)));
         if (!ctx->stream_in) {
             CU(cudaStreamCreateWithFlags(&ctx->stream_in, cudaStreamNonBlocking));
@@ -300,8 +336,9 @@ b2col_status comm_enqueue_shard(b2col_ctx* ctx, const b2col_ray* d_rays_shard, s
         CU(cudaStreamWaitEvent(ctx->stream_out, ctx->pipe_start_ev, 0));  // also: behind the previous gather's completion step
         b2col_raycast* local = ctx->d_hits.as<b2col_raycast>();
         b2col_raycast* remote = static_cast<b2col_raycast*>(c->win) + lo;
-        for (size_t k = 0; k < n_chunks; ++k) {
-            const size_t off = k * chunk, m = std::min(chunk, n - off);
+        size_t off = 0;
+        for (size_t k = 0; k < n_chunks; off += sizes[k], ++k) {
+            const size_t m = sizes[k];
             cudaStream_t ts = (k & 1) ? ctx->stream_trace2 : ctx->stream;
             GUARD(enqueue_trace(ctx, d_rays_shard + off, m, local + off, B2COL_MODE_LBVH, false, false, ts, ctx->d_pipe_counters.as<unsigned long long>() + 2 * k));
             CU(cudaEventRecord(ctx->pipe_events[k], ts));
