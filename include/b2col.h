@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B2COL_ABI_VERSION 2
+#define B2COL_ABI_VERSION 3 /* 3: b2col_stats grew by key_bits, fused_keys */
 
 typedef struct b2col_ctx b2col_ctx;
 
@@ -166,7 +166,12 @@ b2col_status b2col_set_colliders(b2col_ctx* ctx, uint32_t n_colliders, const uin
  * CollisionSystem::onUpdate (src/system_collisions.cpp:112-158): propagate world matrices, refit
  * world AABBs, rebuild the BVH from scratch (the reference rebuilds every frame, :121).
  * Enqueued on the ctx stream; returns without waiting.  n_colliders == 0 yields an empty tree and
- * every query misses (the reference abort()s, :136 -> :208 — deliberate divergence). */
+ * every query misses (the reference abort()s, :136 -> :208 — deliberate divergence).
+ * Successive updates of one collider set adapt the build to the scene (same answers; only tree shape, i.e. the winner among
+ * exactly tied hits, and the frame time can differ from one frame to the next): the Morton key width follows the key
+ * collisions the previous build counted, and from the second frame on the keys are made inside the refit kernel from a plan
+ * based on the bounds earlier frames reported (b2col_stats.key_bits / fused_keys; B2COL_ADAPTIVE_KEYS=0, B2COL_FUSE_KEYS=0
+ * pin the static width / the exact per-frame plan; contexts with a communicator always use both). */
 b2col_status b2col_update(b2col_ctx* ctx);
 /* replaces: TransformSystem::onUpdate alone (src/system_transform.cpp:12-38) — for callers that replace the
  * reference's TransformSystem and CollisionSystem separately (engine_b200/shim/system_transform.cpp): world
