@@ -667,10 +667,15 @@ k_refit_keys(const uint32_t* __restrict__ level_entities, const uint32_t* __rest
             }
     }
     if (!tail.last_level) return;
-    // the last block to get here sees every block's bounds (atomics, performed at L2, ordered before the ticket by the fence)
-    __threadfence();
+    // The last block to get here sees every block's bounds: the block's atomics (threads < 6, bounds_reduce) are ordered before the
+    // barrier, thread 0's fence after it makes them — cumulatively — visible at GPU scope before its ticket.  (A fence in EVERY
+    // thread made each warp wait for the acknowledgement of all of its own stores before it could exit: MEMBAR + ERRBAR + CCTL.IVALL
+    // were 20 % of this kernel's stall samples, ncu source page.)
     __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    }
     __syncthreads();
     if (s_last && threadIdx.x == 0) {
         __threadfence();
@@ -841,9 +846,11 @@ k_refit_keys_bulk(uint32_t e0, uint32_t c0, uint32_t count, int root_level, cons
             }
     }
     if (!tail.last_level) return;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    __syncthreads();  // (see k_refit_keys: one fence, in the thread that takes the ticket)
+    if (tid == 0) {
+        __threadfence();
+        s_last = atomicAdd(tail.done, 1u) == gridDim.x - 1u;
+    }
     __syncthreads();
     if (s_last && tid == 0) {
         __threadfence();
