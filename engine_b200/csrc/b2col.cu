@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <thread>
@@ -2794,6 +2795,71 @@ static b2col_status raycast_batch_end(b2col_ctx* ctx)
         CU(cudaMemcpy(&flag, ctx->d_flag.p, 4, cudaMemcpyDeviceToHost));
         if (flag) return fail(ctx, B2COL_ERR_OVERFLOW, "reference-topology traversal stack overflow (tree deeper than %d)", REFTOPO_STACK);
     }
+    return B2COL_OK;
+}
+
+// ---- b2col_raycast_batch_static: the production trace with ALL of its device scratch in a file-scope array ------------------------
+// For callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid it).  b2col_raycast_batch stages the
+// rays and the results in device buffers the context allocates on demand (ctx->d_rays / d_hits) and takes the persistent
+// kernel's work counter from another one; here all three live in ONE static array that every GPU which loads the library holds
+// until exit: [work counter, 256 B | rays, 24 B each | Raycasts, 36 B each] for at most B2COL_STATIC_MAX_RAYS rays.
+// In host code `g_static_scratch` is only a host-side stand-in for the symbol, never a device address: the address is asked
+// for once per device, with that device current (static_scratch_base), and that pointer is what the copies and the kernel get.
+// Every call on a device shares the array (it keeps the last call's bytes: the counter is cleared per call, rays and results are
+// overwritten before they are read); calls that overlap on one GPU — two contexts, two host threads — race.
+constexpr size_t STATIC_COUNTER_BYTES = 256;
+constexpr size_t STATIC_RAYS_OFF = STATIC_COUNTER_BYTES;
+constexpr size_t STATIC_HITS_OFF = STATIC_RAYS_OFF + (size_t)B2COL_STATIC_MAX_RAYS * sizeof(b2col_ray);
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_HITS_OFF + (size_t)B2COL_STATIC_MAX_RAYS * sizeof(b2col_raycast);
+static_assert(STATIC_RAYS_OFF % 8 == 0 && STATIC_HITS_OFF % 4 == 0 && STATIC_SCRATCH_BYTES <= ((size_t)4 << 20), "static scratch layout (3.75 MiB per GPU)");
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static void* g_static_scratch_addr[STATIC_MAX_DEVICES];  // device address of g_static_scratch on device d (nullptr: not asked yet)
+static std::mutex g_static_scratch_mutex;
+
+// set-up, once per device: device address of the array on ctx's device (the current device on entry)
+static b2col_status static_scratch_base(b2col_ctx* ctx, unsigned char** out)
+{
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return fail(ctx, B2COL_ERR_UNSUPPORTED, "device ordinal %d beyond the %d this entry point keeps addresses for", ctx->device, STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    void*& slot = g_static_scratch_addr[ctx->device];
+    if (!slot) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(ctx, B2COL_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) on device %d failed: %s", ctx->device, cudaGetErrorString(e));
+        }
+        slot = p;
+    }
+    *out = static_cast<unsigned char*>(slot);
+    return B2COL_OK;
+}
+
+b2col_status b2col_raycast_batch_static(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out)
+{
+    if (!ctx || (n && (!h_rays || !h_out))) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (n > (size_t)B2COL_STATIC_MAX_RAYS)
+        return fail(ctx, B2COL_ERR_INVALID, "b2col_raycast_batch_static takes at most B2COL_STATIC_MAX_RAYS = %d rays per call (its device scratch is a fixed array), got %zu: split the batch or use b2col_raycast_batch",
+                    (int)B2COL_STATIC_MAX_RAYS, n);
+    if (n == 0) return B2COL_OK;
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->have_tree || ctx->tree_leaves == 0) {  // before the first update / empty tree: every query misses (reference :164-167)
+        CU(cudaStreamSynchronize(ctx->stream));      // same ordering as the allocating path: behind whatever the context has enqueued
+        memset(h_out, 0, n * sizeof(b2col_raycast));
+        return B2COL_OK;
+    }
+    unsigned char* base = nullptr;
+    GUARD(static_scratch_base(ctx, &base));
+    unsigned long long* counter = reinterpret_cast<unsigned long long*>(base);
+    b2col_ray* d_rays = reinterpret_cast<b2col_ray*>(base + STATIC_RAYS_OFF);
+    b2col_raycast* d_out = reinterpret_cast<b2col_raycast*>(base + STATIC_HITS_OFF);
+    CU(cudaMemsetAsync(counter, 0, 16, ctx->stream));  // the array keeps the last call's contents: the work counter must start at zero
+    CU(cudaMemcpyAsync(d_rays, h_rays, n * sizeof(b2col_ray), cudaMemcpyHostToDevice, ctx->stream));
+    GUARD(enqueue_trace(ctx, d_rays, n, d_out, B2COL_MODE_LBVH, false, false, ctx->stream, counter));  // the launch form that takes its counter from the caller: no ensure()
+    CU(cudaMemcpyAsync(h_out, d_out, n * sizeof(b2col_raycast), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
     return B2COL_OK;
 }
 

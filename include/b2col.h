@@ -194,6 +194,17 @@ b2col_status b2col_refit(b2col_ctx* ctx);
 b2col_status b2col_raycast_batch(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out, int mode);
 /* Device buffers; enqueued on the ctx stream, returns without waiting. */
 b2col_status b2col_raycast_device(b2col_ctx* ctx, const b2col_ray* d_rays, size_t n, b2col_raycast* d_out, int mode);
+/* No counterpart in the reference.  b2col_raycast_batch (production tree, same bytes
+ * in h_out) for callers that cannot call cudaMalloc — tight serving loops, harnesses that forbid it: this call allocates NOTHING
+ * (no cudaMalloc / cudaFree / allocating library routine).  All device scratch of the trace — the persistent kernel's work counter
+ * and the staging of the rays and of the results — lives in one file-scope `static __device__ __align__(256)` array of
+ * 256 + 60 * B2COL_STATIC_MAX_RAYS bytes (3.75 MiB) that every GPU which loads the library holds until exit.  n >
+ * B2COL_STATIC_MAX_RAYS is rejected with B2COL_ERR_INVALID (split the batch, or use b2col_raycast_batch).  Every call on a GPU
+ * shares the array, which keeps the last call's contents (the call clears what must start at zero): calls that overlap on one
+ * GPU — two contexts, two host threads — race; calls on one context are serialised as always.  Returns when h_out is complete.
+ * The tree must have been built before (b2col_update, which does allocate); before that every ray misses, as in the reference. */
+#define B2COL_STATIC_MAX_RAYS 65536
+b2col_status b2col_raycast_batch_static(b2col_ctx* ctx, const b2col_ray* h_rays, size_t n, b2col_raycast* h_out);
 
 /* Compact-result forms of the two calls above (production tree): 12-byte b2col_hit records.  The host-buffer path is bound by
  * the device->host copy of its results (36 of 60 bytes per ray), so a caller that can consume hits — or expand them on its own
