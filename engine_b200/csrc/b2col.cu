@@ -611,8 +611,11 @@ __device__ __noinline__ void frame_tail(const FrameTail& t, const uint32_t* boun
 #define B2_RK_BLOCK 256
 #endif
 constexpr int RK_BLOCK = B2_RK_BLOCK;
+// resident blocks per SM = grid / SMs (persistent).  Measured, update at 1M flat / 3-level scene / 10M: 4 -> 135.8 / 163.8 / 1088 us,
+// 3 -> 135.6 / 157.6, 2 -> 132.8 / 155.4 / 1065 (kept), 1 -> 139.4 / 159.9 (profiles/r2_experiments.txt): every block flushes up to 768 histogram bins and twelve
+// bounds with global atomics, and the small levels of a hierarchy want few blocks; below two per SM the stream starves.
 #ifndef B2_RK_MIN_BLOCKS
-#define B2_RK_MIN_BLOCKS (1024 / B2_RK_BLOCK)
+#define B2_RK_MIN_BLOCKS 2
 #endif
 template <bool DENSE, bool KEYS>
 __global__ void __launch_bounds__(RK_BLOCK, B2_RK_MIN_BLOCKS)
