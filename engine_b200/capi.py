@@ -49,7 +49,7 @@ class CommInfo(C.Structure):
 # every symbol include/b2col.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "b2col_abi_version", "b2col_device_count", "b2col_create", "b2col_destroy", "b2col_last_error", "b2col_sync", "b2col_stream",
-    "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_update_trs_rows", "b2col_stage_trs_rows", "b2col_commit_trs_rows", "b2col_fetch_world_rows", "b2col_set_world_matrices", "b2col_set_colliders",
+    "b2col_set_hierarchy", "b2col_set_trs", "b2col_set_trs_device", "b2col_bind_trs_device", "b2col_update_trs_rows", "b2col_stage_trs_rows", "b2col_commit_trs_rows", "b2col_fetch_world_rows", "b2col_set_world_matrices", "b2col_set_colliders",
     "b2col_update", "b2col_propagate", "b2col_refit", "b2col_raycast_batch", "b2col_raycast_batch_static", "b2col_raycast_device", "b2col_raycast_hits_batch", "b2col_raycast_hits_device", "b2col_expand_hits", "b2col_upload_ref_bvh", "b2col_export_bitreenode",
     "b2col_get_world_matrices", "b2col_get_world_aabbs", "b2col_get_leaf_order", "b2col_get_stats", "b2col_get_trace_counters", "b2col_read_device",
     "b2col_bvh_blob", "b2col_bvh_export_blob", "b2col_bvh_import_blob", "b2col_event_record", "b2col_event_elapsed_ms",
@@ -90,6 +90,7 @@ def load() -> C.CDLL:
     lib.b2col_set_hierarchy.argtypes = [vp, u32, vp]
     lib.b2col_set_trs.argtypes = [vp, u32, vp, vp, vp]
     lib.b2col_set_trs_device.argtypes = [vp, u32, vp, vp, vp]
+    lib.b2col_bind_trs_device.argtypes = [vp, u32, vp, vp, vp]
     lib.b2col_set_world_matrices.argtypes = [vp, u32, vp]
     lib.b2col_update_trs_rows.argtypes = [vp, u32, vp, vp, vp, vp]
     lib.b2col_stage_trs_rows.argtypes = [vp, u32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]

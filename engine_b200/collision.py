@@ -101,6 +101,12 @@ class CollisionSystem:
         """torch CUDA tensors (float32, contiguous, (E+1,3)/(E+1,4)/(E+1,3)); enqueued, not waited for."""
         self._ck(self.lib.b2col_set_trs_device(self.h, self.n_entities, ptr(d_pos), ptr(d_rot_xyzw), ptr(d_scl)))
 
+    def bind_trs_device(self, d_pos, d_rot_xyzw, d_scl) -> None:
+        """zero-copy: the context reads these torch CUDA tensors in place at every update until the next set_trs* (keep them alive;
+        order your writes on self.stream or with events)"""
+        self._bound_trs = (d_pos, d_rot_xyzw, d_scl)  # keep the tensors alive as long as the binding
+        self._ck(self.lib.b2col_bind_trs_device(self.h, self.n_entities, ptr(d_pos), ptr(d_rot_xyzw), ptr(d_scl)))
+
     def set_world_matrices(self, world16) -> None:
         world16 = np.ascontiguousarray(world16, dtype=np.float32).reshape(-1, 16)
         self.n_entities = world16.shape[0] - 1

@@ -1403,6 +1403,14 @@ struct b2col_ctx {
     bool world_fresh = false;  // d_world already holds the matrices of the current hierarchy + TRS (b2col_propagate)
     std::vector<uint32_t> level_offsets;  // host; level k = [off[k], off[k+1]) in d_level_entities
     DevBuf d_parent, d_level_entities, d_pos, d_rot, d_scl, d_world;
+    // b2col_bind_trs_device: the frame's kernels read the CALLER's TRS arrays in place (no 44 B/entity hand-over copy per frame)
+    bool trs_bound = false;
+    const float* bound_pos = nullptr;
+    const float4* bound_rot = nullptr;
+    const float* bound_scl = nullptr;
+    const float* trs_pos() const { return trs_bound ? bound_pos : d_pos.as<float>(); }
+    const float4* trs_rot() const { return trs_bound ? bound_rot : d_rot.as<float4>(); }
+    const float* trs_scl() const { return trs_bound ? bound_scl : d_scl.as<float>(); }
     // colliders
     uint32_t n_colliders = 0, max_col_entity = 0;
     bool have_colliders = false;
@@ -1892,6 +1900,7 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
     ctx->n_entities = n_entities;
     ctx->have_hierarchy = true;
     ctx->have_trs = false;
+    ctx->trs_bound = false;  // a new hierarchy wants new TRS arrays (b2col_set_trs* / b2col_bind_trs_device)
     ctx->world_fresh = false;
     ctx->fuse_map_valid = false;
     ++ctx->shape_gen;
@@ -1911,6 +1920,10 @@ static b2col_status set_trs_common(b2col_ctx* ctx, uint32_t n_entities, const fl
     CU(cudaMemcpyAsync(ctx->d_pos.p, pos3, rows * 12, kind, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_rot.p, rot, rows * 16, kind, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_scl.p, scl3, rows * 12, kind, ctx->stream));
+    if (ctx->trs_bound) {  // back to the context's own copies
+        ctx->trs_bound = false;
+        ++ctx->buffers_gen;
+    }
     ctx->have_trs = true;
     ctx->world_external = false;
     ctx->world_fresh = false;
@@ -1927,6 +1940,36 @@ b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_p
 b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3)
 {
     return set_trs_common(ctx, n_entities, d_pos3, d_rot_xyzw, d_scl3, cudaMemcpyDeviceToDevice);
+}
+
+b2col_status b2col_bind_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3)
+{
+    if (!ctx || !d_pos3 || !d_rot_xyzw || !d_scl3) return fail(ctx, B2COL_ERR_INVALID, "null argument");
+    if (!ctx->have_hierarchy || n_entities != ctx->n_entities)
+        return fail(ctx, B2COL_ERR_STATE, "b2col_set_hierarchy must be called first with the same n_entities");
+    if ((reinterpret_cast<uintptr_t>(d_rot_xyzw) & 15u) || (reinterpret_cast<uintptr_t>(d_pos3) & 3u) || (reinterpret_cast<uintptr_t>(d_scl3) & 3u))
+        return fail(ctx, B2COL_ERR_INVALID, "bound TRS arrays: rotations must be 16-byte aligned (read as float4), positions and scales 4-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    {   // the arrays must be device (or managed) memory this context's device can read
+        cudaPointerAttributes at{};
+        for (const void* p : {(const void*)d_pos3, (const void*)d_rot_xyzw, (const void*)d_scl3}) {
+            const cudaError_t e = cudaPointerGetAttributes(&at, p);
+            if (e != cudaSuccess || (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged)) {
+                cudaGetLastError();
+                return fail(ctx, B2COL_ERR_INVALID, "b2col_bind_trs_device takes device memory (use b2col_set_trs for host arrays)");
+            }
+        }
+    }
+    const float4* rot = reinterpret_cast<const float4*>(d_rot_xyzw);
+    if (!ctx->trs_bound || ctx->bound_pos != d_pos3 || ctx->bound_rot != rot || ctx->bound_scl != d_scl3) ++ctx->buffers_gen;  // a captured frame holds the old pointers
+    ctx->trs_bound = true;
+    ctx->bound_pos = d_pos3;
+    ctx->bound_rot = rot;
+    ctx->bound_scl = d_scl3;
+    ctx->have_trs = true;
+    ctx->world_external = false;
+    ctx->world_fresh = false;  // and never becomes true while bound: the caller changes the arrays without telling us (b2col_propagate)
+    return B2COL_OK;
 }
 
 // page-locked staging of at least `bytes`, safe to overwrite (the copies that last used it have completed)
@@ -1952,6 +1995,7 @@ b2col_status b2col_stage_trs_rows(b2col_ctx* ctx, uint32_t n_rows, uint32_t** h_
 {
     if (!ctx || !h_entity || !h_pos3 || !h_rot_xyzw || !h_scl3) return fail(ctx, B2COL_ERR_INVALID, "null argument");
     if (!ctx->have_trs) return fail(ctx, B2COL_ERR_STATE, "b2col_set_trs must have uploaded the full arrays once");
+    if (ctx->trs_bound) return fail(ctx, B2COL_ERR_STATE, "the TRS arrays are the caller's (b2col_bind_trs_device): update them in place");
     CU(cudaSetDevice(ctx->device));
     GUARD(rows_staging(ctx, rows_bytes(n_rows)));
     char* base = static_cast<char*>(ctx->h_rows);
@@ -1967,6 +2011,7 @@ b2col_status b2col_commit_trs_rows(b2col_ctx* ctx, uint32_t n_rows)
 {
     if (!ctx) return B2COL_ERR_INVALID;
     if (n_rows > ctx->rows_staged) return fail(ctx, B2COL_ERR_STATE, "%u rows committed, %u staged", n_rows, ctx->rows_staged);
+    if (ctx->trs_bound) return fail(ctx, B2COL_ERR_STATE, "the TRS arrays are the caller's (b2col_bind_trs_device): update them in place");
     const uint32_t staged = ctx->rows_staged;
     ctx->rows_staged = 0;
     if (n_rows == 0) return B2COL_OK;
@@ -2107,7 +2152,7 @@ static b2col_status enqueue_propagate(b2col_ctx* ctx)
         const uint32_t off = ctx->level_offsets[k], cnt = ctx->level_offsets[k + 1] - off;
         if (!cnt) continue;
         LAUNCH_FRAME(ctx, k_propagate_level, cdiv(cnt, 256), 256, 0, ctx->d_level_entities.as<uint32_t>() + off, cnt, ctx->d_parent.as<uint32_t>(),
-               ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>());
+               ctx->trs_pos(), ctx->trs_rot(), ctx->trs_scl(), ctx->d_world.as<float4>());
     }
     return B2COL_OK;
 }
@@ -2118,7 +2163,7 @@ b2col_status b2col_propagate(b2col_ctx* ctx)
     if (!(ctx->have_hierarchy && ctx->have_trs)) return fail(ctx, B2COL_ERR_STATE, "need b2col_set_hierarchy + b2col_set_trs");
     CU(cudaSetDevice(ctx->device));
     GUARD(enqueue_propagate(ctx));
-    ctx->world_fresh = true;
+    ctx->world_fresh = !ctx->trs_bound;  // bound arrays change without notice: the next update propagates again
     return B2COL_OK;
 }
 
@@ -2227,14 +2272,14 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx, bool full, bool* tail_done)
             const uint32_t grid = std::min<uint32_t>(cdiv(cnt, RK_BLOCK), (uint32_t)(ctx->n_sm * B2_RK_MIN_BLOCKS * ctx->rk_waves));
 #define B2_REFIT_KEYS(D, K)                                                                                                                                   \
     LAUNCH_FRAME(ctx, (k_refit_keys<D, K>), grid, RK_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, ctx->d_level_col.as<uint32_t>() + off, run.e0, run.c0, \
-                 cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), \
+                 cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->trs_pos(), ctx->trs_rot(), ctx->trs_scl(), ctx->d_world.as<float4>(), \
                  ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx), kg, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), \
                  scratch_ghist(ctx), ft)
             const bool dense = run.dense && !ctx->no_dense_refit;
-            if (dense && ctx->refit_bulk) {  // inputs through the TMA unit, a tile ahead (k_refit_keys_bulk)
+            if (dense && ctx->refit_bulk && !ctx->trs_bound) {  // inputs through the TMA unit, a tile ahead (k_refit_keys_bulk); its 16-byte granular copies read up to 30 bytes around a range: only inside the context's own, padded arrays
 #define B2_REFIT_BULK(K)                                                                                                                                       \
-    LAUNCH_FRAME(ctx, (k_refit_keys_bulk<K>), grid, RK_BLOCK, 0, run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(),       \
-                 ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(), ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(),      \
+    LAUNCH_FRAME(ctx, (k_refit_keys_bulk<K>), grid, RK_BLOCK, 0, run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->trs_pos(),               \
+                 ctx->trs_rot(), ctx->trs_scl(), ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(),      \
                  scratch_bounds(ctx), kg, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), scratch_ghist(ctx), ft)
                 if (keys) B2_REFIT_BULK(true);
                 else B2_REFIT_BULK(false);
@@ -2259,7 +2304,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx, bool full, bool* tail_done)
             const b2col_ctx::LevelRun run = k < ctx->level_runs.size() ? ctx->level_runs[k] : b2col_ctx::LevelRun();
 #define B2_REFIT_LEVEL(D)                                                                                                                                              \
     LAUNCH_FRAME(ctx, k_propagate_refit_level<D>, cdiv(cnt, REFIT_BLOCK), REFIT_BLOCK, 0, ctx->d_level_entities.as<uint32_t>() + off, ctx->d_level_col.as<uint32_t>() + off, \
-                 run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->d_pos.as<float>(), ctx->d_rot.as<float4>(), ctx->d_scl.as<float>(),                 \
+                 run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->trs_pos(), ctx->trs_rot(), ctx->trs_scl(),                                           \
                  ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx))
             if (run.dense && !ctx->no_dense_refit) B2_REFIT_LEVEL(true);
             else B2_REFIT_LEVEL(false);

@@ -143,6 +143,13 @@ b2col_status b2col_set_hierarchy(b2col_ctx* ctx, uint32_t n_entities, const uint
 b2col_status b2col_set_trs(b2col_ctx* ctx, uint32_t n_entities, const float* h_pos3, const float* h_rot_xyzw, const float* h_scl3);
 /* Same, from device memory (async on the ctx stream; buffers must stay valid until b2col_sync). */
 b2col_status b2col_set_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3);
+/* Zero-copy form for callers whose TransformComponent data already lives on the GPU (a simulation that animates it there):
+ * the context does not copy (b2col_set_trs_device: 44 bytes per entity read and written again every frame — 0.05 ms at 1M
+ * entities, a third of the update it feeds) but READS THE CALLER'S ARRAYS IN PLACE in every b2col_update / b2col_refit /
+ * b2col_propagate until the next b2col_set_trs* / b2col_set_hierarchy.  The arrays (rows 0..n_entities; rotations 16-byte
+ * aligned) must stay valid for that long, and the caller orders its writes before the update and the update before its next
+ * writes (same stream as b2col_stream, or events).  The sparse row calls below return B2COL_ERR_STATE while arrays are bound. */
+b2col_status b2col_bind_trs_device(b2col_ctx* ctx, uint32_t n_entities, const float* d_pos3, const float* d_rot_xyzw, const float* d_scl3);
 /* Sparse TRS update for frames in which few entities moved (dirty tracking through
  * TransformComponent::is_static, reference include/component_transform.h:24): row h_entity[i] of the device arrays takes
  * pos / rot / scl [i]; everything else keeps the values of the last b2col_set_trs.  44 bytes per moved entity cross PCIe

@@ -455,6 +455,65 @@ def test_small_random_scenes_over_many_frames(CollisionSystem, port):
             seen.append((st["key_bits"], st["fused_keys"]))
         assert seen[0][1] == 0 and seen[5][1] == 1, f"case {case}: exact plan first, plan-before-frame later: {seen}"
         cs.close()
+def test_bound_device_trs_arrays(CollisionSystem, port):
+    """b2col_bind_trs_device: the context reads the caller's device TRS arrays in place (no per-frame hand-over copy).  Frames in
+    which the arrays are changed on the device between updates: world matrices and world AABBs bit-exact vs the oracle, every ray
+    equal to the reference walking the exported tree, and everything bitwise equal to a second context fed through b2col_set_trs.
+    Flat (dense, list-free kernel) and three-level scenes, with and without the captured graph."""
+    for case, s, roots in ((0, synth.uniform_boxes(50_000, extent=300.0), 0), (1, synth.hierarchy_scene(60_000, 70, extent=300), 70)):
+        cs = CollisionSystem(use_cuda_graph=bool(case))
+        twin = CollisionSystem()
+        cs.set_scene(s)
+        twin.set_scene(s)
+        d_pos, d_rot, d_scl = (torch.from_numpy(a.copy()).cuda() for a in (s.pos, s.rot, s.scl))
+        torch.cuda.synchronize()
+        cs.bind_trs_device(d_pos, d_rot, d_scl)
+        rays = np.concatenate([synth.random_rays(20_000, seed=61, extent=320), synth.axis_rays(2_000, seed=62, extent=300)])
+        rng = np.random.default_rng(63 + case)
+        for frame in range(6):
+            if frame:
+                n_move = roots if roots else s.pos.shape[0] - 1
+                s.pos[1 : n_move + 1] += rng.uniform(-1.0, 1.0, (n_move, 3)).astype(np.float32)
+                if roots:
+                    s.rot[1 : roots + 1] = synth.random_unit_quats(rng, roots)
+                d_pos.copy_(torch.from_numpy(s.pos))  # the caller's own device-side update of its arrays (default stream) ...
+                d_rot.copy_(torch.from_numpy(s.rot))
+                torch.cuda.synchronize()              # ... ordered before the update
+                twin.set_trs(s.pos, s.rot, s.scl)
+            if frame == 4:
+                cs.on_update_refit()
+                twin.on_update_refit()
+            else:
+                cs.on_update()
+                twin.on_update()
+            world = port.transform_update(s.parent, s.pos, s.rot, s.scl)
+            want_boxes = port.refit(s.collider_entity, s.collider_aabb, world).view(np.float32).reshape(-1, 6)
+            assert (bits(cs.world_matrices()) == bits(world[1:])).all(), f"case {case} frame {frame}: world matrices"
+            assert (bits(cs.world_aabbs()) == bits(want_boxes)).all(), f"case {case} frame {frame}: world AABBs"
+            got = cs.get_raycasts(rays)
+            assert_raycast_equal(got, reference_walk(cs.bvh, rays, port), f"case {case} frame {frame}: bound arrays vs the reference on the exported tree")
+            assert (got.view(np.uint8) == twin.get_raycasts(rays).view(np.uint8)).all(), f"case {case} frame {frame}: bound arrays vs b2col_set_trs"
+            assert cs.stats()["key_bits"] == twin.stats()["key_bits"] and cs.stats()["fused_keys"] == twin.stats()["fused_keys"]
+        # while bound: no sparse row updates, no host arrays; b2col_propagate alone works and stays in step with the arrays
+        with pytest.raises(capi.B2ColError) as ei:
+            cs.update_trs_rows(np.array([1], np.uint32), s.pos[1:2], s.rot[1:2], s.scl[1:2])
+        assert ei.value.status == capi.ERR_STATE
+        assert cs.lib.b2col_bind_trs_device(cs.h, cs.n_entities, capi.ptr(s.pos), capi.ptr(s.rot), capi.ptr(s.scl)) == capi.ERR_INVALID  # host memory
+        d_pos[1:] += 0.25
+        torch.cuda.synchronize()
+        s.pos[1:] += np.float32(0.25)
+        cs.propagate()
+        assert (bits(cs.world_matrices()) == bits(port.transform_update(s.parent, s.pos, s.rot, s.scl)[1:])).all(), "b2col_propagate on bound arrays"
+        # b2col_set_trs takes the context back to its own copy: the caller's arrays are no longer read
+        cs.set_trs(s.pos, s.rot, s.scl)
+        d_pos.zero_()
+        torch.cuda.synchronize()
+        cs.on_update()
+        twin.set_trs(s.pos, s.rot, s.scl)
+        twin.on_update()
+        assert (cs.get_raycasts(rays).view(np.uint8) == twin.get_raycasts(rays).view(np.uint8)).all(), "after unbinding"
+        cs.close()
+        twin.close()
 
 
 def test_duplicate_boxes_and_ties(CollisionSystem, port):

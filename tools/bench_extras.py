@@ -63,21 +63,25 @@ def config4(torch, frames=100):
     torch.cuda.synchronize()
     out = {}
     with torch.cuda.stream(ext):
-        for mode in ("rebuild", "refit_only"):
+        for mode in ("rebuild", "refit_only", "rebuild_bound"):
             evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(frames + 5)]
+            if mode == "rebuild_bound":
+                cs.bind_trs_device(d_pos, d_rot, d_scl)  # zero-copy: the update reads these tensors in place; [0] -> [1] below is the animation alone
             for f in range(frames + 5):
                 evs[f][0].record(ext)
                 d_pos[1 : roots + 1] += dpos[f % 8]
                 d_rot[1 : roots + 1] = q[f % 8]
-                cs.set_trs_device(d_pos, d_rot, d_scl)  # 44 B/entity device-to-device into the context's SoA
+                if mode != "rebuild_bound":
+                    cs.set_trs_device(d_pos, d_rot, d_scl)  # 44 B/entity device-to-device into the context's SoA
                 evs[f][1].record(ext)
-                (cs.on_update if mode == "rebuild" else cs.on_update_refit)(wait=False)
+                (cs.on_update_refit if mode == "refit_only" else cs.on_update)(wait=False)
                 evs[f][2].record(ext)
             cs.sync()
             t = np.array([[e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2])] for e in evs[5:]])
             out[mode] = {"frame_ms_median": float(np.median(t.sum(1))), "frame_ms_p99": float(np.percentile(t.sum(1), 99)),
                          "trs_handover_ms_median": float(np.median(t[:, 0])), "update_ms_median": float(np.median(t[:, 1])),
                          "update_ms_p99": float(np.percentile(t[:, 1], 99))}
+    cs.set_trs_device(d_pos, d_rot, d_scl)  # back to the context's own copy
     cs.on_update()
     st = cs.stats()
     rays = np.concatenate([synth.camera_rays(2048, 1024, eye=(0.0, 0.0, 300.0), look=(1.0, 0.2, -0.3)), synth.random_rays(2 << 20, seed=44)])
@@ -87,6 +91,8 @@ def config4(torch, frames=100):
                        "(set_trs_device) + b2col_update (propagate, refit, full LBVH rebuild), per-frame CUDA events",
            "frames": frames, "entities": st["n_entities"], "colliders": st["n_colliders"], "levels": st["n_levels"], "sort_passes": st["sort_passes"],
            "rebuild": out["rebuild"], "refit_only": out["refit_only"],
+           "rebuild_bound_trs": dict(out["rebuild_bound"], what="the same frames with the caller's TRS tensors bound (b2col_bind_trs_device: read in place, no hand-over copy); "
+                                                                 "trs_handover_ms = the root animation alone"),
            "roofline": {"bound": "hbm", "algorithmic_bytes": 280.0 * n, "achieved": 280.0 * n / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": 280.0 * n / (ms * 1e-3) / 1e9 / peak},
            "rays_4m": _trace(cs, torch, rays)}
