@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B2COL_ABI_VERSION 3 /* 3: b2col_stats grew by key_bits, fused_keys */
+#define B2COL_ABI_VERSION 4 /* 3: b2col_stats grew by key_bits, fused_keys; 4: + b2col_raycast_batch_static, b2col_bind_trs_device */
 
 typedef struct b2col_ctx b2col_ctx;
 

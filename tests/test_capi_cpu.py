@@ -30,7 +30,7 @@ def test_header_symbols_exported(lib):
     assert sorted(capi.SYMBOLS) == names, "capi.SYMBOLS must list exactly what include/b2col.h declares"
     for n in names:
         assert hasattr(lib, n), f"libb2col.so does not export {n}"
-    assert lib.b2col_abi_version() == 3
+    assert lib.b2col_abi_version() == 4
 
 
 def test_pod_sizes_match_reference():
