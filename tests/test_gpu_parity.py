@@ -228,6 +228,20 @@ def test_degenerate_colliders(CollisionSystem, port, emu, with_nan):
     # refit-only frame keeps the flags
     cs.on_update_refit()
     assert_raycast_equal(cs.get_raycasts(rays), got, "refit frame", nan_equal=True)
+    # later builds of the same collider set: adapted key width, keys made inside the refit kernel from a plan based on the bounds the
+    # earlier frames reported (non-finite centroids stay out of those bounds and clamp into the plan's edge cells): same answers,
+    # and the tree is the host restatement's for that width and plan
+    for frame in range(4):
+        cs.on_update()
+    st = cs.stats()
+    assert st["fused_keys"] == 1
+    assert nan_eq_bits(cs.world_aabbs(), want_boxes).all(), "world AABBs of the fused-keys frame"
+    tree = emu.build(boxes, s.collider_entity, key_bits=st["key_bits"], plan_bounds=(st["scene_min"], st["scene_max"]))
+    assert tree["has_wild"] == 1 and np.array_equal(cs.leaf_order(), tree["sorted_prim"])
+    qnodes, _ = read_blob(cs, s.n_colliders)
+    assert np.array_equal(qnodes, tree["qnodes"]["w"]), "fused-keys frame: quantised nodes differ from the host restatement"
+    order = cs.leaf_order()
+    assert_raycast_equal(cs.get_raycasts(rays), port.raycast_brute(s.collider_entity[order], boxes[order], rays, nthreads=8), "fused-keys frame vs brute force", nan_equal=True)
 
 
 def test_degenerate_rays_vs_live_reference(CollisionSystem, port):
