@@ -13,6 +13,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <utility>
 #include <thread>
 #include <vector>
 
@@ -1405,6 +1406,7 @@ struct b2col_ctx {
     DevBuf d_parent, d_level_entities, d_pos, d_rot, d_scl, d_world;
     // b2col_bind_trs_device: the frame's kernels read the CALLER's TRS arrays in place (no 44 B/entity hand-over copy per frame)
     bool trs_bound = false;
+    bool bound_padded = false;  // the bound arrays' allocations extend >= 16 bytes behind them: the bulk-copy kernel may read them
     const float* bound_pos = nullptr;
     const float4* bound_rot = nullptr;
     const float* bound_scl = nullptr;
@@ -1960,7 +1962,31 @@ b2col_status b2col_bind_trs_device(b2col_ctx* ctx, uint32_t n_entities, const fl
             }
         }
     }
+    // May the bulk-copy kernel read the arrays?  Its 16-byte granular copies end up to 15 bytes behind a range's last row: allowed when
+    // the ALLOCATION each array lives in (cuMemGetAddressRange; a framework's pool block counts) extends that far behind the array
+    bool padded = false;
+    {
+        typedef int (*PFN_range)(unsigned long long*, size_t*, unsigned long long);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &qr) == cudaSuccess && fn && qr == cudaDriverEntryPointSuccess) {
+            padded = true;
+            const size_t rows = (size_t)n_entities + 1;
+            const std::pair<const void*, size_t> arrays[3] = {{d_pos3, rows * 12}, {d_rot_xyzw, rows * 16}, {d_scl3, rows * 12}};
+            for (const auto& a : arrays) {
+                unsigned long long base = 0;
+                size_t size = 0;
+                const unsigned long long p = reinterpret_cast<unsigned long long>(a.first);
+                if (reinterpret_cast<PFN_range>(fn)(&base, &size, p) != 0 || p + a.second + 16 > base + size) padded = false;
+            }
+        }
+        else {
+            cudaGetLastError();
+        }
+    }
     const float4* rot = reinterpret_cast<const float4*>(d_rot_xyzw);
+    if (ctx->bound_padded != padded) ++ctx->buffers_gen;  // the captured frame holds the kernel choice
+    ctx->bound_padded = padded;
     if (!ctx->trs_bound || ctx->bound_pos != d_pos3 || ctx->bound_rot != rot || ctx->bound_scl != d_scl3) ++ctx->buffers_gen;  // a captured frame holds the old pointers
     ctx->trs_bound = true;
     ctx->bound_pos = d_pos3;
@@ -2276,7 +2302,7 @@ b2col_status enqueue_transform_refit(b2col_ctx* ctx, bool full, bool* tail_done)
                  ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(), scratch_bounds(ctx), kg, ctx->d_keys[0].as<uint64_t>(), ctx->d_vals[0].as<uint32_t>(), \
                  scratch_ghist(ctx), ft)
             const bool dense = run.dense && !ctx->no_dense_refit;
-            if (dense && ctx->refit_bulk && !ctx->trs_bound) {  // inputs through the TMA unit, a tile ahead (k_refit_keys_bulk); its 16-byte granular copies read up to 30 bytes around a range: only inside the context's own, padded arrays
+            if (dense && ctx->refit_bulk && (!ctx->trs_bound || ctx->bound_padded)) {  // inputs through the TMA unit, a tile ahead (k_refit_keys_bulk); its 16-byte granular copies read up to 30 bytes around a range: the context's own, padded arrays, or bound arrays whose allocations were checked (b2col_bind_trs_device)
 #define B2_REFIT_BULK(K)                                                                                                                                       \
     LAUNCH_FRAME(ctx, (k_refit_keys_bulk<K>), grid, RK_BLOCK, 0, run.e0, run.c0, cnt, (int)(k == 0), ctx->d_parent.as<uint32_t>(), ctx->trs_pos(),               \
                  ctx->trs_rot(), ctx->trs_scl(), ctx->d_world.as<float4>(), ctx->d_col_local.as<Aabb24>(), ctx->d_world_aabb.as<LeafRec>(),      \
