@@ -116,6 +116,34 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
     uint32_t val[RS_ITEMS];
     uint32_t rank[RS_ITEMS];
     const uint32_t wbase = (uint32_t)warp * (RS_ITEMS * 32u) + (uint32_t)lane;
+#ifdef B2_RS_BULK_LOAD
+    // dev variant: the tile's keys are ONE contiguous range of up to 32 KB — moved into shared memory by the
+    // bulk-copy engine (cp.async.bulk + mbarrier), then read from there in warp-striped order (tiles start 32 KB apart: 16-byte aligned;
+    // the size is rounded up to 16 bytes: at most one key beyond the array's last, inside the buffer's allocation slack)
+    {
+        __shared__ alignas(8) uint64_t s_bar;
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            const uint32_t bytes = (valid * 8u + 15u) & ~15u;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"((uint32_t)__cvta_generic_to_shared(skeys)),
+                         "l"(kin + tile_base), "r"(bytes), "r"(bar)
+                         : "memory");
+        }
+        __syncthreads();  // the barrier is initialised
+        asm volatile("{\n\t.reg .pred P1;\n\tRS_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n\t@P1 bra RS_DONE;\n\tbra RS_WAIT;\n\tRS_DONE:\n\t}" ::"r"(bar) : "memory");
+#pragma unroll
+        for (int k = 0; k < RS_ITEMS; ++k) {
+            const uint32_t idx = wbase + (uint32_t)k * 32u;
+            const bool ok = idx < valid;
+            key[k] = ok ? skeys[idx] : ~0ull;
+            if (MODE == 0) val[k] = ok ? vin[tile_base + idx] : 0u;
+        }
+        __syncthreads();  // skeys is reused by the scatter
+    }
+#else
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
         const uint32_t idx = wbase + (uint32_t)k * 32u;
@@ -123,6 +151,7 @@ k_onesweep(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, u
         key[k] = ok ? kin[tile_base + idx] : ~0ull;
         if (MODE == 0) val[k] = ok ? vin[tile_base + idx] : 0u;
     }
+#endif
 
 #ifdef B2_SORT_TIMING
     if (key[0] == 0x123456789abcdefull && key[RS_ITEMS - 1] == 77ull) s_tile = 0;  // wait for the loads
